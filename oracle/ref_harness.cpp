@@ -1,0 +1,224 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.
+// C harness around the REFERENCE'S OWN planner classes, compiled unmodified from
+// /root/reference/src/*.cpp against oracle/stubs (see oracle/Makefile).  It drives
+//   SSPP::PathPlanner::generateRegularGrid   src/pathplanner.cpp:90-201
+//   SSPP::SearchSpace::insertNode            src/searchspace.cpp:64-105
+//   SSPP::PathPlanner::connectNodes          src/pathplanner.cpp:527-567
+//   SSPP::PathPlanner::startSearch/Astar     src/pathplanner.cpp:502-525, src/astar.cpp:220-373
+//   SSPP::DistanceHeuristic                  src/distance_heuristic.cpp
+// exactly as src/distance_heuristic_test.cpp:40-117 and src/reactive_planner_server.cpp:83-129 do,
+// and returns nodes (list order), adjacency (as list indices) and the A* path.  The octomap behind
+// DistanceHeuristic is the restated one (octomap_world/octomap_manager.h stub).
+#include <cstdint>
+#include <iostream>
+#include <map>
+#include <sstream>
+#include <vector>
+
+#include "sspp/pathplanner.h"
+#include "sspp/distance_heuristic.h"
+
+// src/rviz_drawing_tools.cpp builds RViz markers; headless stand-ins (no graphics on this box)
+visualization_msgs::Marker drawLines(std::vector<geometry_msgs::Point>, int, int, int, double) {
+  return visualization_msgs::Marker();
+}
+visualization_msgs::Marker drawPoints(std::vector<geometry_msgs::Point>, int, int) {
+  return visualization_msgs::Marker();
+}
+
+// src/sensors.cpp needs real Eigen 4x4 products, so it is not compiled; Sensors is restated here:
+// sensorPose = T_robot * T_mount * Rx(+90deg)   (src/sensors.cpp:47-92), products accumulated
+// left to right over k as Eigen's coefficient-wise evaluation does.
+Sensors::Sensors(double hfov, double vfov, double fl, double nearR, double farR, double width, double height,
+                 Eigen::Vector3f sP, Eigen::Vector3f sRPY)
+    : hFOV(hfov), vFOV(vfov), focalLength(fl), near(nearR), far(farR), resWidth(width), resHeight(height),
+      sensorPose(sP), sensorRPY(sRPY) {}
+Sensors::Sensors() {}
+Sensors::~Sensors() {}
+static void mat4mul(const double A[4][4], const double B[4][4], double C[4][4]) {
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) {
+      double acc = A[i][0] * B[0][j];
+      for (int k = 1; k < 4; ++k) acc = acc + A[i][k] * B[k][j];
+      C[i][j] = acc;
+    }
+}
+geometry_msgs::Pose Sensors::robot2sensorTransformation(geometry_msgs::Pose pose) {
+  double A[4][4] = {{0}}, B[4][4] = {{0}}, C[4][4], D[4][4];
+  tf::Matrix3x3 R1(tf::Quaternion(pose.orientation.x, pose.orientation.y, pose.orientation.z, pose.orientation.w));
+  tf::Matrix3x3 R2(tf::createQuaternionFromRPY(sensorRPY[0], sensorRPY[1], sensorRPY[2]));
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) { A[i][j] = R1.m[i][j]; B[i][j] = R2.m[i][j]; }
+  A[0][3] = pose.position.x; A[1][3] = pose.position.y; A[2][3] = pose.position.z; A[3][3] = 1;
+  B[0][3] = sensorPose[0]; B[1][3] = sensorPose[1]; B[2][3] = sensorPose[2]; B[3][3] = 1;
+  mat4mul(A, B, C);
+  const double S[4][4] = {{1, 0, 0, 0}, {0, 0, -1, 0}, {0, 1, 0, 0}, {0, 0, 0, 1}};
+  mat4mul(C, S, D);
+  tf::Matrix3x3 R3;
+  for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) R3.m[i][j] = D[i][j];
+  tf::Quaternion qt;
+  R3.getRotation(qt);
+  geometry_msgs::Pose p;
+  p.position.x = D[0][3]; p.position.y = D[1][3]; p.position.z = D[2][3];
+  p.orientation.x = qt.getX(); p.orientation.y = qt.getY(); p.orientation.z = qt.getZ(); p.orientation.w = qt.getW();
+  return p;
+}
+
+namespace {
+struct Quiet {  // the reference narrates on std::cout; keep test logs clean
+  std::streambuf* old;
+  std::ostringstream sink;
+  Quiet() : old(std::cout.rdbuf(sink.rdbuf())) {}
+  ~Quiet() { std::cout.rdbuf(old); }
+};
+
+struct RefPlanner {
+  ros::NodeHandle nh;
+  Robot* robot;
+  SSPP::PathPlanner* planner;
+  SSPP::DistanceHeuristic* heuristic;
+  volumetric_mapping::OctomapManager* manager;
+  std::string last_log;
+};
+
+geometry_msgs::Pose mkpose(const double p[7]) {
+  geometry_msgs::Pose q;
+  q.position.x = p[0]; q.position.y = p[1]; q.position.z = p[2];
+  q.orientation.x = p[3]; q.orientation.y = p[4]; q.orientation.z = p[5]; q.orientation.w = p[6];
+  return q;
+}
+}  // namespace
+
+extern "C" {
+
+// world: an orc::OctomapWorld* made by orc_world_create in THIS library, or NULL (manager == NULL)
+void* ref_planner_create(double con_radius, void* world) {
+  Quiet q;
+  RefPlanner* R = new RefPlanner;
+  R->robot = NULL;  // PathPlanner only stores the pointer (src/astar.cpp:29)
+  R->planner = new SSPP::PathPlanner(R->nh, R->robot, con_radius, -1);
+  R->planner->setDebugDelay(0.0);
+  R->manager = world ? new volumetric_mapping::OctomapManager((orc::OctomapWorld*)world) : NULL;
+  R->heuristic = new SSPP::DistanceHeuristic(R->nh, false, R->manager);
+  R->planner->setHeuristicFucntion(R->heuristic);
+  return R;
+}
+
+void ref_planner_destroy(void* h) {
+  Quiet q;
+  RefPlanner* R = (RefPlanner*)h;
+  delete R->planner;
+  delete R->heuristic;
+  delete R->manager;
+  delete R;
+}
+
+void ref_set_goal(void* h, const double end_pose[7], double tolerance) {
+  RefPlanner* R = (RefPlanner*)h;
+  R->heuristic->setEndPose(mkpose(end_pose));
+  R->heuristic->setTolerance2Goal(tolerance);
+}
+
+void ref_generate_grid(void* h, const double start[3], const double size[3], float res, int sample_orient,
+                       float orient_res) {
+  Quiet q;
+  RefPlanner* R = (RefPlanner*)h;
+  geometry_msgs::Pose gs;
+  gs.position.x = start[0]; gs.position.y = start[1]; gs.position.z = start[2];
+  geometry_msgs::Vector3 sz;
+  sz.x = size[0]; sz.y = size[1]; sz.z = size[2];
+  R->planner->generateRegularGrid(gs, sz, res, sample_orient != 0, orient_res, false, true);
+}
+
+void ref_insert_node(void* h, const double pose[7]) {
+  RefPlanner* R = (RefPlanner*)h;
+  R->planner->insertNode(mkpose(pose));
+}
+
+long ref_num_nodes(void* h) {
+  RefPlanner* R = (RefPlanner*)h;
+  long n = 0;
+  for (SSPP::SearchSpaceNode* t = R->planner->searchspace; t; t = t->next) ++n;
+  return n;
+}
+
+// poses: n x 7 doubles in LIST order (head first); ids: SearchSpaceNode::id
+void ref_get_nodes(void* h, double* poses, int32_t* ids) {
+  RefPlanner* R = (RefPlanner*)h;
+  long i = 0;
+  for (SSPP::SearchSpaceNode* t = R->planner->searchspace; t; t = t->next, ++i) {
+    poses[7 * i + 0] = t->location.position.x; poses[7 * i + 1] = t->location.position.y;
+    poses[7 * i + 2] = t->location.position.z; poses[7 * i + 3] = t->location.orientation.x;
+    poses[7 * i + 4] = t->location.orientation.y; poses[7 * i + 5] = t->location.orientation.z;
+    poses[7 * i + 6] = t->location.orientation.w;
+    if (ids) ids[i] = t->id;
+  }
+}
+
+void ref_disconnect(void* h) { ((RefPlanner*)h)->planner->disconnectNodes(); }
+
+// runs the reference's O(N^2) connectNodes; returns MAXNODES (= connection count it printed)
+long ref_connect(void* h) {
+  Quiet q;
+  RefPlanner* R = (RefPlanner*)h;
+  R->planner->connectNodes();
+  return R->planner->MAXNODES;
+}
+
+long ref_collision_calls(void* h) {
+  RefPlanner* R = (RefPlanner*)h;
+  return R->manager ? R->manager->calls : 0;
+}
+
+// children vectors -> CSR over list indices; returns E (col filled up to cap)
+long ref_get_csr(void* h, int64_t* row_ptr, int32_t* col, long cap) {
+  RefPlanner* R = (RefPlanner*)h;
+  std::map<SSPP::SearchSpaceNode*, int32_t> index;
+  int32_t i = 0;
+  for (SSPP::SearchSpaceNode* t = R->planner->searchspace; t; t = t->next) index[t] = i++;
+  long E = 0;
+  i = 0;
+  for (SSPP::SearchSpaceNode* t = R->planner->searchspace; t; t = t->next, ++i) {
+    row_ptr[i] = E;
+    for (size_t c = 0; c < t->children.size(); ++c) {
+      if (E < cap) col[E] = index[t->children[c]];
+      ++E;
+    }
+  }
+  row_ptr[i] = E;
+  return E;
+}
+
+// PathPlanner::startSearch(start).  path: cap x 10 doubles (pose7, g, h, f) from root to goal.
+// Returns the number of path nodes (0 = no path).  stats[0] = nodes created (Astar::globalID),
+// stats[1] = nodes expanded (parsed from the reference's own log line, -1 if absent).
+long ref_astar(void* h, const double start_pose[7], double* path, long cap, long* stats) {
+  RefPlanner* R = (RefPlanner*)h;
+  std::string log;
+  SSPP::Node* p;
+  {
+    Quiet q;
+    Pose s;
+    s.p = mkpose(start_pose);
+    s.phi = 0;
+    p = R->planner->startSearch(s);
+    log = q.sink.str();
+  }
+  if (stats) {
+    stats[0] = R->planner->globalID;
+    stats[1] = -1;
+    size_t k = log.find("nodes created and :");
+    if (k != std::string::npos) stats[1] = atol(log.c_str() + k + 19);
+  }
+  long n = 0;
+  for (SSPP::Node* t = p; t; t = t->next, ++n) {
+    if (n < cap) {
+      double* o = path + 10 * n;
+      o[0] = t->pose.p.position.x; o[1] = t->pose.p.position.y; o[2] = t->pose.p.position.z;
+      o[3] = t->pose.p.orientation.x; o[4] = t->pose.p.orientation.y; o[5] = t->pose.p.orientation.z;
+      o[6] = t->pose.p.orientation.w; o[7] = t->g_value; o[8] = t->h_value; o[9] = t->f_value;
+    }
+  }
+  return n;
+}
+
+}  // extern "C"
