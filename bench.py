@@ -1,0 +1,495 @@
+#!/usr/bin/env python
+"""bench.py — the sspp hot path on BASELINE.json's headline workload.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (config.workload = "S4a"): synthetic 512^3-voxel map at 0.3 m (seed 42) + 10^6 nodes on a
+100^3 lattice at 1.0 m, radius-connect R = 1.5 with the swept-robot collision test, box
+(0.5, 0.5, 0.3) -> 27 rays per pair (SURVEY.md §8 d, BASELINE.json configs[3]).
+
+One "step" = one PathPlanner::connectNodes pass over all nodes.
+  value  collision-checked edges/s = pairs handed to the collision test / device time, nodes and map
+         already resident in HBM (whole pipeline: binning, count, edge test, CSR compaction)
+  e2e    the same through the C ABI with HOST buffers (sspp_gpu_connect_nodes_host): pinned node array
+         in, CSR out, copies inside the timed region
+  roofline  the dominant kernel (k_edges): algorithmic bytes per launch / its CUDA-event duration
+  cpu_baseline  the oracle's restated connectNodes (O(N^2), one thread) on a bounded sub-lattice
+  visibility    the second half of the metric: occlusion rays/s of the visibility pass
+With --impl reference the reference's own CPU connectNodes (oracle/_ref, else the oracle port) is
+timed on the host cores on bounded samples of the same scene.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+REPO = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, REPO)
+
+RES = 0.3
+N_VOX = 512
+LATTICE = 100
+RADIUS = 1.5
+BOX = (0.5, 0.5, 0.3)
+METRIC = "collision-checked edges/s (connectNodes graph build, 1M nodes / 512^3 voxels)"
+UNIT = "edges/s"
+
+
+def workload_config(n_gpus):
+    return {"workload": "S4a: 512^3 voxels @0.3 m (seed 42, 400 boxes + 200 spheres), 10^6 nodes on a 100^3 lattice @1.0 m, "
+                        "R=1.5, box (0.5,0.5,0.3) -> 27 rays/pair, treat_unknown_as_occupied",
+            "nodes": LATTICE ** 3, "voxels": N_VOX ** 3, "radius": RADIUS, "box": list(BOX),
+            "parallelism": "rows%d" % n_gpus,
+            "l2": "flushed between timed steps (256 MiB write, outside the timed events); per-step scratch (~0.4 GB) also exceeds L2"}
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs (oracle = checker; here it is the thing timed as the BASELINE, never the product)
+# ------------------------------------------------------------------------------------------------
+def sub_scene(occ, known, key_min, lattice_n, centre_idx):
+    """A sub-lattice of the S4a scene with a map window just large enough for its reach."""
+    from sspp_b200 import scenes
+    full_axis = (np.arange(LATTICE) - (LATTICE - 1) / 2.0)
+    lo = [int(c - lattice_n // 2) for c in centre_idx]
+    ax = [full_axis[lo[a]:lo[a] + lattice_n] for a in range(3)]
+    zz, xx, yy = np.meshgrid(ax[2], ax[0], ax[1], indexing="ij")
+    nodes = np.ascontiguousarray(np.stack([xx.ravel(), yy.ravel(), zz.ravel()], axis=1)[::-1])
+    # voxel window: nodes' bounding box grown by the reach (R + box/2) and two voxels
+    half = N_VOX // 2
+    w0, w1 = [], []
+    for a in range(3):
+        w0.append(int(np.floor((ax[a][0] - RADIUS - 0.5) / RES)) - 2 + half)
+        w1.append(int(np.floor((ax[a][-1] + RADIUS + 0.5) / RES)) + 3 + half)
+    vol_o = scenes.unpack_bits(occ, N_VOX)[w0[2]:w1[2], w0[1]:w1[1], w0[0]:w1[0]]
+    vol_k = scenes.unpack_bits(known, N_VOX)[w0[2]:w1[2], w0[1]:w1[1], w0[0]:w1[0]]
+    kmin = np.array([key_min[a] + w0[a] for a in range(3)], dtype=np.int32)
+    dims = np.array([w1[a] - w0[a] for a in range(3)], dtype=np.int32)
+    return nodes, kmin, dims, scenes.pack_bits(vol_o), scenes.pack_bits(vol_k)
+
+
+def cpu_port_sample(occ, known, key_min, lattice_n=28):
+    """cpu_baseline leg: the oracle's restated connectNodes, single thread, on a centred sub-lattice."""
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    import oracle_lib
+    O = oracle_lib.Oracle()
+    nodes, kmin, dims, so, sk = sub_scene(occ, known, key_min, lattice_n, (LATTICE // 2,) * 3)
+    w = O.world(RES, True)
+    w.build_dense(kmin, dims, so, sk)
+    t0 = time.perf_counter()
+    rp, col, cnt = O.connect(w, nodes, RADIUS, BOX)
+    dt = time.perf_counter() - t0
+    w.close()
+    return {"value": float(cnt[0]) / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "centred %d^3 sub-lattice of the S4a scene (%d nodes, %d tested pairs, %d voxel lookups), full O(N^2) "
+                      "connectNodes incl. the pair scan, %.2f s; at 10^6 nodes the reference's N^2 scan alone is ~1300x larger "
+                      "per pair" % (lattice_n, len(nodes), int(cnt[0]), int(cnt[2]), dt),
+            "seconds": dt}, (nodes, rp, col)
+
+
+_REF = {}
+
+
+def _ref_worker_init(centres, ln, have_ref, counter):
+    """One worker process per host thread: its own octree window + the reference's PathPlanner.
+    (Processes, not threads: the reference narrates on the process-wide std::cout.)"""
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    import oracle_lib
+    with counter.get_lock():
+        me = counter.value
+        counter.value += 1
+    O = oracle_lib.Oracle(oracle_lib.LIB_REF if have_ref else oracle_lib.LIB_ORACLE)
+    key_min, occ, known = _REF["scene"]
+    nodes, kmin, d, so, sk = sub_scene(occ, known, key_min, ln, centres[me % len(centres)])
+    w = O.world(RES, True)
+    w.build_dense(kmin, d, so, sk)
+    p = None
+    if have_ref:
+        p = O.planner(RADIUS, w)
+        poses = np.zeros((len(nodes), 7))
+        poses[:, :3] = nodes[::-1]  # insertion order = reverse list order (head insertion)
+        poses[:, 6] = 1.0
+        p.insert_nodes(poses)
+    _REF["job"] = (O, w, p, nodes)
+
+
+def _ref_worker_step(_):
+    O, w, p, nodes = _REF["job"]
+    t0 = time.perf_counter()
+    if p is not None:
+        p.disconnect()
+        c0 = p.collision_calls()
+        p.connect()  # PathPlanner::connectNodes, src/pathplanner.cpp:527-567, unmodified
+        c = p.collision_calls() - c0
+    else:
+        _, _, cnt = O.connect(w, nodes, RADIUS, BOX)
+        c = int(cnt[0])
+    return c, time.perf_counter() - t0
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference's own CPU connectNodes on the host cores (rank 0 only)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    sys.path.insert(0, os.path.join(REPO, "tests"))
+    import oracle_lib
+    from sspp_b200 import scenes
+    have_ref = os.path.exists(oracle_lib.LIB_REF)
+    key_min, dims, occ, known = scenes.synthetic_map(n_vox=N_VOX, res=RES, seed=42)
+    _REF["scene"] = (key_min, occ, known)
+    cores = os.cpu_count() or 1
+    procs = max(1, min(cores, 64))
+    ln = 16  # 4096 nodes per worker and step: ~1 s of the reference's single-threaded connectNodes
+    rng = np.random.RandomState(1)
+    centres = [tuple(int(x) for x in rng.randint(ln, LATTICE - ln, 3)) for _ in range(procs)]
+    ctx = mp.get_context("fork")
+    counter = ctx.Value("i", 0)
+    pool = ctx.Pool(procs, initializer=_ref_worker_init, initargs=(centres, ln, have_ref, counter))
+
+    def one_step():
+        t0 = time.perf_counter()
+        res = pool.map(_ref_worker_step, range(procs), chunksize=1)
+        return time.perf_counter() - t0, sum(r[0] for r in res)
+
+    for _ in range(max(args.warmup, 1)):
+        one_step()
+    total_t, total_c = 0.0, 0
+    for _ in range(args.steps):
+        dt, c = one_step()
+        total_t += dt
+        total_c += c
+    pool.close()
+    pool.join()
+    value = total_c / total_t
+    kind = "reference" if have_ref else "port"
+    sample = ("%d worker processes (one per host core) x one %d^3 sub-lattice (%d nodes) of the S4a scene per step, each running "
+              "%s connectNodes (O(N^2) pair scan + getLineStatusBoundingBox per pair) on its own octree window; %d tested pairs "
+              "per step" % (procs, ln, ln ** 3, "the reference's own single-threaded" if have_ref else "the oracle port of",
+                            total_c // max(args.steps, 1)))
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * total_t / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f64+f32 (CPU)", "data": "synthetic",
+            "config": workload_config(args.gpus),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="sspp_b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-visibility", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from sspp_b200 import scenes
+    from sspp_b200.engine import Engine
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    distributed = world > 1
+    if distributed:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n_gpus = world if distributed else 1
+    W = max(args.warmup, 3)
+    K = args.steps
+
+    # ---- scene (synthetic, identical on every rank: the map and the node set are replicated)
+    key_min, dims, occ, known = scenes.synthetic_map(n_vox=N_VOX, res=RES, seed=42)
+    nodes = scenes.lattice_nodes(LATTICE, 1.0)
+    n = len(nodes)
+    eng = Engine(local_rank)
+    eng.map_create(RES, key_min, dims, True)
+    eng.map_upload_dense(occ, known)
+    lo, hi = (n * rank) // world, (n * (rank + 1)) // world
+    rows = None if not distributed else (lo, hi)
+    ext_stream = torch.cuda.ExternalStream(eng.stream(), device=torch.device("cuda", local_rank))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def flush_l2():
+        flush.zero_()
+        torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        eng.synchronize()
+        if distributed:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- instrumented pass: Σsteps of the byte model (not timed)
+    eng.set_nodes(nodes)
+    st_cnt = eng.connect(radius=RADIUS, box=BOX, rows=rows, count_steps=True)
+    steps_total = st_cnt.voxel_steps
+
+    # ---- device-resident timing: `value`
+    gather_bufs = {}
+
+    def assemble_csr(st):
+        """N>1: all-gather the per-rank CSR blocks over NCCL (row counts, then padded column blocks)."""
+        if not distributed:
+            return
+        cnt = torch.tensor([st.rows, st.edges], dtype=torch.int64, device="cuda")
+        allc = [torch.empty_like(cnt) for _ in range(world)]
+        dist.all_gather(allc, cnt)
+        allc = torch.stack(allc).cpu().numpy()
+        max_e, max_r = int(allc[:, 1].max()), int(allc[:, 0].max())
+        key = (max_e, max_r)
+        if key not in gather_bufs:
+            gather_bufs.clear()
+            gather_bufs[key] = (torch.empty(max_r + 1, dtype=torch.int64, device="cuda"),
+                                torch.empty(max(max_e, 1), dtype=torch.int32, device="cuda"),
+                                torch.empty(world * (max_r + 1), dtype=torch.int64, device="cuda"),
+                                torch.empty(world * max(max_e, 1), dtype=torch.int32, device="cuda"))
+        rp_s, col_s, rp_all, col_all = gather_bufs[key]
+        eng.connect_fetch_device(rp_s.data_ptr(), col_s.data_ptr())
+        dist.all_gather_into_tensor(rp_all, rp_s)
+        dist.all_gather_into_tensor(col_all, col_s)
+        return rp_all, col_all, allc
+
+    def step_resident():
+        st = eng.connect(radius=RADIUS, box=BOX, rows=rows)
+        assemble_csr(st)
+        return st
+
+    for _ in range(W):
+        st = step_resident()
+    tested_local = st.tested_pairs
+    flush_l2()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    launches0 = eng.launch_count()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    kern_ms, phase_ms = [], []
+    wall = []
+    for k in range(K):
+        flush_l2()
+        if distributed:
+            dist.barrier()
+        t0 = time.perf_counter()
+        ev[k][0].record(ext_stream)
+        st = step_resident()
+        if distributed:
+            torch.cuda.current_stream().synchronize()
+        ev[k][1].record(ext_stream)
+        eng.synchronize()
+        wall.append(time.perf_counter() - t0)
+        t = eng.connect_timings()
+        kern_ms.append(float(t[3]))
+        phase_ms.append([float(x) for x in t])
+    barrier()
+    launches = eng.launch_count() - launches0
+    # device time per step: CUDA events on the engine's stream; the NCCL part (other stream) is
+    # covered by the host wall clock of the step, so take the larger of the two when distributed
+    step_ms = []
+    for k in range(K):
+        e = ev[k][0].elapsed_time(ev[k][1])
+        step_ms.append(max(e, wall[k] * 1e3) if distributed else e)
+    total_ms = float(sum(step_ms))
+    tot = torch.tensor([total_ms, float(tested_local), float(st.edges)], dtype=torch.float64, device="cuda")
+    if distributed:
+        mx = tot.clone()
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tot.clone()
+        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        total_ms = float(mx[0])
+        tested_all, edges_all = float(sm[1]), float(sm[2])
+    else:
+        tested_all, edges_all = float(tested_local), float(st.edges)
+    value = tested_all * K / (total_ms * 1e-3)
+
+    # ---- e2e: host buffers through the C ABI (pinned), copies inside the timed region
+    pin_nodes = torch.from_numpy(nodes).pin_memory()
+    rp_host = torch.empty(n + 1, dtype=torch.int64).pin_memory()
+    col_host = torch.empty(int(st.in_radius_pairs) + 64, dtype=torch.int32).pin_memory()
+    rp_np, col_np, nodes_np = rp_host.numpy(), col_host.numpy(), pin_nodes.numpy()
+
+    def step_e2e():
+        s = eng.connect_nodes_host(nodes_np, rp_np[: (hi - lo) + 1] if distributed else rp_np, col_np, radius=RADIUS, box=BOX,
+                                   rows=rows)
+        assemble_csr(s)
+        return s
+
+    for _ in range(2):
+        s2 = step_e2e()
+    barrier()
+    e2e_t = 0.0
+    for k in range(K):
+        flush_l2()
+        if distributed:
+            dist.barrier()
+        t0 = time.perf_counter()
+        s2 = step_e2e()
+        torch.cuda.synchronize()
+        e2e_t += time.perf_counter() - t0
+    barrier()
+    e2e_tot = torch.tensor([e2e_t], dtype=torch.float64, device="cuda")
+    if distributed:
+        dist.all_reduce(e2e_tot, op=dist.ReduceOp.MAX)
+    e2e_value = tested_all * K / float(e2e_tot[0])
+    h2d = n * 24
+    d2h = ((hi - lo) + 1) * 8 + int(s2.edges) * 4
+    clk = clocks.stop() if rank == 0 else None
+
+    # ---- correctness guard on the timed configuration: the pyramid skip must not change the CSR
+    if rank == 0 and not distributed:
+        sa = eng.connect(radius=RADIUS, box=BOX, use_pyramid=False)
+        rpa, cola = eng.connect_fetch(sa)
+        sb = eng.connect(radius=RADIUS, box=BOX, use_pyramid=True)
+        rpb, colb = eng.connect_fetch(sb)
+        assert np.array_equal(rpa, rpb) and np.array_equal(cola, colb), "pyramid skip changed the graph"
+
+    if rank != 0:
+        if distributed:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (k_edges), per launch, this rank's share
+    peaks_path = os.path.join(REPO, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak = float(json.load(open(peaks_path))["hbm_gbs"])
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    C_l, E_l, N_l = float(st.in_radius_pairs), float(st.edges), float(hi - lo)
+    alg_bytes = 24.0 * C_l + 4.0 * float(steps_total) + 4.0 * E_l + 32.0 * N_l
+    k_ms = float(np.mean(kern_ms))
+    achieved = alg_bytes / (k_ms * 1e-3) / 1e9
+    try:
+        l2_gbps = eng.l2_bandwidth(32 << 20, 30)
+    except Exception:
+        l2_gbps = None
+    ph = np.mean(np.array(phase_ms), axis=0)
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "kernel": "k_edges", "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (total_ms / K),
+                "algorithmic_bytes": alg_bytes, "peak_source": peak_src,
+                "bytes_model": "24*C + 4*steps + 4*E + 32*N with C=%d in-radius pairs, steps=%d voxel lookups (counted on the "
+                               "device by the instrumented run, reference semantics), E=%d, N=%d" % (C_l, steps_total, E_l, N_l),
+                "l2_read_gbps_measured": l2_gbps, "frac_of_l2": (achieved / l2_gbps) if l2_gbps else None,
+                "phase_ms": {"total": float(ph[0]), "binning": float(ph[1]), "count": float(ph[2]), "edges": float(ph[3]),
+                             "csr": float(ph[4])},
+                "pyramid_rows": int(st.pyramid_rows)}
+
+    # ---- visibility half of the metric (rank 0, one GPU): occlusion rays/s
+    vis = None
+    if not args.no_visibility:
+        try:
+            pts = scenes.surface_points(occ, known, key_min, dims, RES, 1_000_000, seed=45)
+            poses = scenes.viewpoints_near(pts, 4096, standoff=3.0, seed=46)
+            eng.set_model_points(pts)
+            eng.visibility(poses, 58.0, 45.0, 0.7, 6.0, fetch=False)
+            t0 = time.perf_counter()
+            reps = 3
+            for _ in range(reps):
+                vs = eng.visibility(poses, 58.0, 45.0, 0.7, 6.0, fetch=False)
+            eng.synchronize()
+            dtv = (time.perf_counter() - t0) / reps
+            vis = {"metric": "visibility rays/s", "value": vs.rays / dtv, "unit": "rays/s", "viewpoints": len(poses),
+                   "model_points": len(pts), "rays": int(vs.rays), "visible_pairs": int(vs.visible_pairs),
+                   "ms_per_pass": dtv * 1e3, "frustum": {"hfov": 58.0, "vfov": 45.0, "near": 0.7, "far": 6.0},
+                   "timing": "host wall clock around sspp_gpu_visibility (poses in, counts out), model points resident"}
+        except Exception as e:  # the headline line must still print
+            vis = {"error": str(e)}
+
+    # ---- CPU baseline (rank 0, N=1 only), bounded sample
+    cpu = None
+    if not distributed and not args.no_cpu_baseline:
+        cpu, (sub_nodes, rp_c, col_c) = cpu_port_sample(occ, known, key_min)
+        cpu.pop("seconds", None)
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": W,
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64 distances + f32/f64 DDA + u32 bit planes", "data": "synthetic",
+            "config": workload_config(n_gpus),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": float(e2e_tot[0]) * 1e3 / K},
+            "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "visibility": vis,
+            "tested_pairs_per_step": tested_all, "edges_per_step": edges_all}
+    print(json.dumps(line))
+    if distributed:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,189 @@
+/*
+ * sspp_gpu.h — C ABI of the B200 geometric-query engine behind the sspp planner API.
+ *
+ * One data-parallel hot path of kucars/sspp lives behind this boundary: batched segment / ray
+ * queries against the occupancy map (edge connection with swept-robot collision checks, node
+ * validity, coverage visibility).  Everything is `extern "C"`, plain pointers and sizes; every call
+ * returns an int status (0 = SSPP_OK) and never throws.  The text of the last failure is kept per
+ * context (sspp_gpu_last_error).  A context is bound to one CUDA device and one stream and is NOT
+ * thread-safe — the same contract as the reference, whose callbacks are serialised by ros::spin()
+ * (reference src/reactive_planner_server_node.cpp:42).
+ *
+ * Citations are `file:line` in the reference tree (kucars/sspp) unless marked "upstream", which
+ * means the un-vendored third-party code the reference calls (OctoMap, volumetric_mapping
+ * octomap_world; reference package.xml:26-27).
+ *
+ * Pointer conventions: unless a name ends in `_device`, pointers are HOST pointers and the call
+ * copies in/out itself (this is the path `bench.py` times as e2e).  `_device` variants take CUDA
+ * device addresses valid on the context's device and leave results resident.
+ */
+#ifndef SSPP_GPU_H
+#define SSPP_GPU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sspp_gpu_ctx sspp_gpu_ctx;
+
+enum {
+  SSPP_OK = 0,
+  SSPP_ERR_INVALID = 1, /* bad argument (null pointer, negative size, non-finite value) */
+  SSPP_ERR_CUDA = 2,    /* CUDA runtime failure; text in sspp_gpu_last_error */
+  SSPP_ERR_STATE = 3,   /* call made before its prerequisite (no map, no nodes, no result) */
+  SSPP_ERR_RANGE = 4    /* size beyond what the engine can index (int32 columns, key range) */
+};
+
+/* volumetric_mapping::WorldBase::CellStatus (upstream), as compared at src/distance_heuristic.cpp:111 */
+enum { SSPP_CELL_FREE = 0, SSPP_CELL_OCCUPIED = 1, SSPP_CELL_UNKNOWN = 2 };
+
+/* ---- context ------------------------------------------------------------------------------ */
+
+/* Replaces: construction of volumetric_mapping::OctomapManager (src/reactive_planner_server_node.cpp:40)
+ * as the world model handed to DistanceHeuristic (include/sspp/distance_heuristic.h:37). */
+int sspp_gpu_create(sspp_gpu_ctx** out, int device);
+void sspp_gpu_destroy(sspp_gpu_ctx* ctx);
+const char* sspp_gpu_last_error(const sspp_gpu_ctx* ctx);
+/* CUDA stream the context launches on (a cudaStream_t), for callers that time with CUDA events. */
+void* sspp_gpu_stream(sspp_gpu_ctx* ctx);
+/* Blocks until everything queued on the context's stream has finished. */
+int sspp_gpu_synchronize(sspp_gpu_ctx* ctx);
+
+/* ---- map ingest ---------------------------------------------------------------------------
+ * The octomap is flattened into a dense two-plane bit grid (known, occupied) over the key window
+ * [key_min, key_min + dims) plus a derived "blocked" plane and a 4x4x4 any-blocked pyramid.
+ * Keys are OctoMap keys: floor(coord / resolution) + 32768 (upstream OcTreeBaseImpl::coordToKey). */
+
+/* Allocates an all-unknown map.  dims are rounded up internally (x to 128, y/z to 4).
+ * Replaces: OctomapWorld construction with `resolution` (launch/reactive_planner_test.launch:14,25)
+ * and `treat_unknown_as_occupied` (launch/reactive_planner_test.launch:29). */
+int sspp_gpu_map_create(sspp_gpu_ctx* ctx, double resolution, const int32_t key_min[3], const int32_t dims[3],
+                        int treat_unknown_as_occupied);
+int sspp_gpu_map_set_treat_unknown(sspp_gpu_ctx* ctx, int treat_unknown_as_occupied);
+
+/* Leaf boxes (centre xyz, edge length) as OctomapManager::getAllOccupiedBoxes returns them
+ * (src/reactive_planner_server.cpp:60; include/sspp/reactive_planner_server.h:61) — and the free
+ * leaves in the same format.  occupied[i] != 0 marks box i occupied, 0 marks it known-free. */
+int sspp_gpu_map_upload_boxes(sspp_gpu_ctx* ctx, const double* centres_xyz, const double* sizes,
+                              const uint8_t* occupied, int64_t n);
+
+/* Replaces: OctomapManager::setFree(position, box) (src/reactive_planner_server.cpp:42) and its twin
+ * setOccupied: every voxel met by a resolution-spaced lattice over the box grown by 0.001. */
+int sspp_gpu_map_set_box(sspp_gpu_ctx* ctx, const double position[3], const double box[3], int occupied);
+
+/* Dense bit planes over the window given to map_create (its un-rounded dims), x fastest, rows of
+ * ceil(dims[0]/32) 32-bit words, then y, then z.  Bit = (word >> (x & 31)) & 1. */
+int sspp_gpu_map_upload_dense(sspp_gpu_ctx* ctx, const uint32_t* occupied_bits, const uint32_t* known_bits);
+int sspp_gpu_map_download_dense(sspp_gpu_ctx* ctx, uint32_t* occupied_bits, uint32_t* known_bits);
+
+/* ---- search-space nodes -------------------------------------------------------------------
+ * Node positions in LIST ORDER: index 0 is the head of SearchSpace::searchspace
+ * (include/sspp/searchspace.h:37; head insertion at src/searchspace.cpp:98-101).  xyz is n x 3
+ * doubles (geometry_msgs::Pose::position of SearchSpaceNode::location,
+ * include/sspp/searchspacenode.h:38). */
+int sspp_gpu_set_nodes(sspp_gpu_ctx* ctx, const double* xyz, int64_t n);
+int sspp_gpu_set_nodes_device(sspp_gpu_ctx* ctx, const double* xyz_device, int64_t n);
+
+/* ---- edge connection ----------------------------------------------------------------------
+ * Replaces: PathPlanner::connectNodes (src/pathplanner.cpp:527-567) [position_mode 0] and
+ * PathPlanner::connectClustersInternalNodes (src/pathplanner.cpp:612-656) [position_mode 1],
+ * with the per-pair test DistanceHeuristic::isConnectionConditionSatisfied
+ * (src/distance_heuristic.cpp:99-127) -> OctomapWorld::getLineStatusBoundingBox (upstream).
+ * Result: CSR adjacency over list indices, rows and columns both in list order. */
+typedef struct sspp_connect_params {
+  double radius;         /* regGridConRadius (include/sspp/pathplanner.h:60); pairs with Dist <= radius */
+  double box[3];         /* swept robot box; the reference hard-codes (0.5,0.5,0.3), distance_heuristic.cpp:107 */
+  int32_t use_map;       /* 0 = the manager==NULL case: every in-radius pair accepted (distance_heuristic.cpp:101,126) */
+  int32_t position_mode; /* 0: exact != on x,y,z (pathplanner.cpp:545); 1: isPositionEqual 1e-12 (pathplanner.cpp:630) */
+  int64_t row_begin;     /* source rows [row_begin,row_end) of the list; 0,0 = all rows (multi-GPU sharding) */
+  int64_t row_end;
+  int32_t use_pyramid;   /* 1: rows whose whole reach is free in the coarse pyramid skip the DDA (same result) */
+  int32_t count_steps;   /* 1: also count the voxel lookups the reference semantics require (instrumented run:
+                            disables the pyramid skip; for the byte model of the roofline, not for timing) */
+} sspp_connect_params;
+
+typedef struct sspp_connect_stats {
+  int64_t rows;            /* source rows processed */
+  int64_t edges;           /* accepted directed edges E (MAXNODES, pathplanner.cpp:566) */
+  int64_t in_radius_pairs; /* ordered pairs with Dist <= radius, self excluded */
+  int64_t tested_pairs;    /* of those, pairs at different positions = pairs handed to the collision test (pathplanner.cpp:547) */
+  int64_t rays_per_pair;   /* size of the ray lattice nx*ny*nz */
+  int64_t pyramid_rows;    /* rows answered by the pyramid */
+  int64_t voxel_steps;     /* with count_steps: lookups up to and including the first non-free voxel of the first
+                              failing ray (lattice order) of every tested pair — what getLineStatusBoundingBox performs */
+} sspp_connect_stats;
+
+/* Runs the whole connection pass on the device; the CSR stays resident until the next connect. */
+int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* params, sspp_connect_stats* stats);
+/* Copies the last CSR to host: row_ptr has rows+1 entries (relative to row_begin), col_idx has `edges`. */
+int sspp_gpu_connect_fetch(sspp_gpu_ctx* ctx, int64_t* row_ptr, int32_t* col_idx);
+/* Same, into DEVICE buffers of the caller (e.g. the send buffers of an NCCL all-gather). */
+int sspp_gpu_connect_fetch_device(sspp_gpu_ctx* ctx, int64_t* row_ptr_device, int32_t* col_idx_device);
+/* Device addresses of the last CSR (valid until the next connect on this context). */
+int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_device, const int32_t** col_idx_device);
+
+/* Convenience for the drop-in PathPlanner::connectNodes: set_nodes + connect + fetch in one call,
+ * host buffers in, host CSR out (col_idx capacity `col_capacity`; SSPP_ERR_RANGE if too small,
+ * with stats->edges telling the size needed). */
+int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n, const sspp_connect_params* params,
+                                int64_t* row_ptr, int32_t* col_idx, int64_t col_capacity, sspp_connect_stats* stats);
+
+/* ---- batched segment / cell / ray queries --------------------------------------------------- */
+
+/* Replaces: n calls of OctomapManager::getLineStatusBoundingBox(start,end,box) (upstream; called at
+ * src/distance_heuristic.cpp:109).  status[i] is the CellStatus of segment i. */
+int sspp_gpu_check_segments(sspp_gpu_ctx* ctx, const double* starts_xyz, const double* ends_xyz, int64_t n,
+                            const double box[3], uint8_t* status);
+
+/* Node validity.  Replaces: the hook Heuristic::isFilteringConditionSatisfied
+ * (include/sspp/heuristic_interface.h:44; called at src/pathplanner.cpp:160), which the only
+ * heuristic in the reference answers `true` (src/distance_heuristic.cpp:134-138).  Defined here as
+ * OctomapWorld::getCellStatusBoundingBox(point, box) in key space (DESIGN.md "validity spec"). */
+int sspp_gpu_validity(sspp_gpu_ctx* ctx, const double* points_xyz, int64_t n, const double box[3], uint8_t* status);
+
+/* Replaces: n calls of octomap::OcTree::castRay(origin, direction, end, ignoreUnknown, maxRange)
+ * (upstream).  hit[i]=1 when it returned true; hit_keys (n x 3, may be NULL) the key it stopped in;
+ * max_range may be NULL (= -1, unlimited). */
+int sspp_gpu_cast_rays(sspp_gpu_ctx* ctx, const float* origins_xyz, const float* directions_xyz, int64_t n,
+                       int ignore_unknown, const double* max_range, uint8_t* hit, int32_t* hit_keys);
+
+/* ---- coverage visibility ------------------------------------------------------------------
+ * Replaces: the per-viewpoint visible-surface extraction a CoverageHeuristic performs inside
+ * Heuristic::calculateHeuristic(Node*) (include/sspp/heuristic_interface.h:40; called at
+ * src/astar.cpp:131,318) with the sensor model of include/sspp/sensors.h:57-68.  The reference
+ * snapshot holds no CoverageHeuristic source; the semantics are the authored spec in DESIGN.md
+ * ("visibility spec v1"): six-plane frustum test in float, then one castRay per in-frustum point. */
+typedef struct sspp_frustum {
+  double hfov_deg, vfov_deg, near_dist, far_dist; /* Sensors::hFOV, vFOV, near, far (include/sspp/sensors.h:61) */
+} sspp_frustum;
+
+typedef struct sspp_visibility_stats {
+  int64_t visible_pairs; /* total (viewpoint, point) pairs visible */
+  int64_t rays;          /* occlusion rays cast = in-frustum pairs */
+} sspp_visibility_stats;
+
+/* Model points (float xyz), kept resident and binned for frustum queries. */
+int sspp_gpu_set_model_points(sspp_gpu_ctx* ctx, const float* xyz, int64_t n);
+/* sensor_poses: nv x 7 doubles (position xyz, quaternion xyzw) — the poses
+ * Sensors::robot2sensorTransformation yields (src/sensors.cpp:47-92). */
+int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* sensor_poses, int64_t nv, const sspp_frustum* frustum,
+                        sspp_visibility_stats* stats);
+/* view_ptr: nv+1 entries; point_idx: visible_pairs entries, ascending within a viewpoint. */
+int sspp_gpu_visibility_fetch(sspp_gpu_ctx* ctx, int64_t* view_ptr, int32_t* point_idx);
+
+/* ---- measurement helpers ------------------------------------------------------------------ */
+/* Reads `bytes` of an L2-resident buffer `iters` times and returns the achieved GB/s — the
+ * denominator north_star asks for ("achievable L2 bandwidth"), not in MEASURED_PEAKS.json. */
+int sspp_gpu_measure_l2_bandwidth(sspp_gpu_ctx* ctx, int64_t bytes, int iters, double* gbps);
+/* Milliseconds the kernels of the last sspp_gpu_connect spent on the stream (CUDA events):
+ * [0] total, [1] binning+scan, [2] count, [3] edge test (DDA), [4] CSR compaction. */
+int sspp_gpu_connect_timings(sspp_gpu_ctx* ctx, float ms[5]);
+/* Number of kernels this library has launched on the context since creation. */
+int64_t sspp_gpu_launch_count(const sspp_gpu_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSPP_GPU_H */

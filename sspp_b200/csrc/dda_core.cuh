@@ -1,0 +1,226 @@
+// dda_core.cuh — the voxel-walk arithmetic of the engine, written once for device and host.
+//
+// These routines reproduce, operation for operation, the float/double operand mix of the
+// un-vendored libraries the reference calls on its hot path (upstream = OctoMap,
+// volumetric_mapping octomap_world; reference call site src/distance_heuristic.cpp:109):
+//   line_status()  = OctomapWorld::getLineStatus  over  OcTreeBaseImpl::computeRayKeys
+//   cast_ray()     = OccupancyOcTreeBase::castRay
+// Every rounding step is spelled with a round-to-nearest intrinsic on the device so that no
+// multiply-add is ever fused (the reference builds for baseline x86-64: no FMA, SSE2 doubles;
+// CMakeLists.txt:6-8).  On the host the same functions compile as plain C++ (build with
+// -ffp-contract=off); tests/ use that build to check this file against the oracle without a GPU.
+#pragma once
+
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define SSPP_HD __host__ __device__ __forceinline__
+#else
+#define SSPP_HD inline
+#endif
+
+namespace sspp {
+
+enum { CELL_FREE = 0, CELL_OCCUPIED = 1, CELL_UNKNOWN = 2 };
+
+#if defined(__CUDA_ARCH__)
+SSPP_HD float f_add(float a, float b) { return __fadd_rn(a, b); }
+SSPP_HD float f_sub(float a, float b) { return __fsub_rn(a, b); }
+SSPP_HD float f_mul(float a, float b) { return __fmul_rn(a, b); }
+SSPP_HD float f_div(float a, float b) { return __fdiv_rn(a, b); }
+SSPP_HD double d_add(double a, double b) { return __dadd_rn(a, b); }
+SSPP_HD double d_sub(double a, double b) { return __dsub_rn(a, b); }
+SSPP_HD double d_mul(double a, double b) { return __dmul_rn(a, b); }
+SSPP_HD double d_div(double a, double b) { return __ddiv_rn(a, b); }
+SSPP_HD double d_sqrt(double a) { return __dsqrt_rn(a); }
+SSPP_HD float d2f(double a) { return __double2float_rn(a); }
+#else
+SSPP_HD float f_add(float a, float b) { return a + b; }
+SSPP_HD float f_sub(float a, float b) { return a - b; }
+SSPP_HD float f_mul(float a, float b) { return a * b; }
+SSPP_HD float f_div(float a, float b) { return a / b; }
+SSPP_HD double d_add(double a, double b) { return a + b; }
+SSPP_HD double d_sub(double a, double b) { return a - b; }
+SSPP_HD double d_mul(double a, double b) { return a * b; }
+SSPP_HD double d_div(double a, double b) { return a / b; }
+SSPP_HD double d_sqrt(double a) { return sqrt(a); }
+SSPP_HD float d2f(double a) { return (float)a; }
+#endif
+
+// Constants of one map, computed once on the host in double.
+struct KeySpace {
+  double res;         // OcTree::resolution
+  double res_factor;  // 1.0 / resolution
+  float half_res_f;   // (float)(resolution * 0.5): the border shift computeRayKeys narrows to float
+  double half_res_d;  // resolution * 0.5: the border shift castRay keeps in double
+};
+
+// upstream OcTreeBaseImpl::coordToKeyChecked(double): floor(res_factor * c) + 32768, valid in [0, 65536)
+SSPP_HD bool coord_to_key(const KeySpace& ks, double c, int& key) {
+  double s = floor(d_mul(ks.res_factor, c));
+  // out-of-range values (and NaN) must fail without an undefined double->int conversion
+  if (!(s >= -32768.0 && s < 32768.0)) return false;
+  key = (int)s + 32768;
+  return true;
+}
+// upstream OcTreeBaseImpl::keyToCoord(key_type): (double(key - 32768) + 0.5) * resolution
+SSPP_HD double key_to_coord(const KeySpace& ks, int key) { return d_mul(d_add((double)(key - 32768), 0.5), ks.res); }
+
+// Euclidean distance exactly as Dist() evaluates it (include/sspp/utils.h:356-359): double, left to right.
+SSPP_HD double dist3(double ax, double ay, double az, double bx, double by, double bz) {
+  double dx = d_sub(ax, bx), dy = d_sub(ay, by), dz = d_sub(az, bz);
+  return d_sqrt(d_add(d_add(d_mul(dx, dx), d_mul(dy, dy)), d_mul(dz, dz)));
+}
+
+// Vector3::norm(): float products and sums, double sqrt.
+SSPP_HD double norm3f(float x, float y, float z) {
+  float s = f_add(f_add(f_mul(x, x), f_mul(y, y)), f_mul(z, z));
+  return d_sqrt((double)s);
+}
+
+// One axis of the DDA set-up shared by computeRayKeys and castRay.
+SSPP_HD void dda_axis(const KeySpace& ks, float dir, float origin, int key, bool border_in_float, int& step, double& tmax,
+                      double& tdelta) {
+  if (dir > 0.0f) step = 1;
+  else if (dir < 0.0f) step = -1;
+  else step = 0;
+  if (step != 0) {
+    double border = key_to_coord(ks, key);
+    if (border_in_float) border = d_add(border, (double)(step > 0 ? ks.half_res_f : -ks.half_res_f));
+    else border = d_add(border, step > 0 ? ks.half_res_d : -ks.half_res_d);
+    tmax = d_div(d_sub(border, (double)origin), (double)dir);
+    tdelta = d_div(ks.res, (double)fabsf(dir));
+  } else {
+    tmax = DBL_MAX;
+    tdelta = DBL_MAX;
+  }
+}
+
+// getLineStatus over computeRayKeys.  `cell(kx,ky,kz)` returns a CellStatus-like int: 0 lets the walk
+// continue, anything else ends it and is returned (the caller folds "unknown counts only when
+// treat_unknown_as_occupied" into the functor).  Start voxel tested, end voxel not; a segment whose
+// ends share a voxel, or with an end outside the 16-bit key range, tests nothing.  `steps`
+// (optional) counts cell() calls.
+template <class Cell>
+SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float ex, float ey, float ez, Cell& cell,
+                        int* steps = nullptr) {
+  int kx, ky, kz, ekx, eky, ekz;
+  if (!coord_to_key(ks, (double)ox, kx) || !coord_to_key(ks, (double)oy, ky) || !coord_to_key(ks, (double)oz, kz) ||
+      !coord_to_key(ks, (double)ex, ekx) || !coord_to_key(ks, (double)ey, eky) || !coord_to_key(ks, (double)ez, ekz))
+    return CELL_FREE;
+  if (kx == ekx && ky == eky && kz == ekz) return CELL_FREE;
+  if (steps) ++*steps;
+  int st = cell(kx, ky, kz);
+  if (st) return st;
+
+  float dx = f_sub(ex, ox), dy = f_sub(ey, oy), dz = f_sub(ez, oz);
+  float length = d2f(norm3f(dx, dy, dz));
+  dx = f_div(dx, length);
+  dy = f_div(dy, length);
+  dz = f_div(dz, length);
+  int sx, sy, sz;
+  double tx, ty, tz, dtx, dty, dtz;
+  dda_axis(ks, dx, ox, kx, true, sx, tx, dtx);
+  dda_axis(ks, dy, oy, ky, true, sy, ty, dty);
+  dda_axis(ks, dz, oz, kz, true, sz, tz, dtz);
+  const double dlen = (double)length;
+  for (int it = 0; it < 262144; ++it) {
+    // argmin with upstream's tie rule
+    if (tx < ty) {
+      if (tx < tz) { kx = (kx + sx) & 0xFFFF; tx = d_add(tx, dtx); }
+      else         { kz = (kz + sz) & 0xFFFF; tz = d_add(tz, dtz); }
+    } else {
+      if (ty < tz) { ky = (ky + sy) & 0xFFFF; ty = d_add(ty, dty); }
+      else         { kz = (kz + sz) & 0xFFFF; tz = d_add(tz, dtz); }
+    }
+    if (kx == ekx && ky == eky && kz == ekz) break;
+    double m = tx < ty ? tx : ty;  // std::min(std::min(t0,t1),t2)
+    m = tz < m ? tz : m;
+    if (m > dlen) break;
+    if (steps) ++*steps;
+    st = cell(kx, ky, kz);
+    if (st) return st;
+  }
+  return CELL_FREE;
+}
+
+// OccupancyOcTreeBase::castRay.  `cell` returns CELL_FREE / CELL_OCCUPIED / CELL_UNKNOWN for a key.
+// Returns true when an occupied voxel was reached (hit_k* = its key).
+template <class Cell>
+SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float dirx, float diry, float dirz,
+                      bool ignore_unknown, double max_range, Cell& cell, int& hx, int& hy, int& hz, int* steps = nullptr) {
+  int kx, ky, kz;
+  hx = hy = hz = -1;
+  if (!coord_to_key(ks, (double)ox, kx) || !coord_to_key(ks, (double)oy, ky) || !coord_to_key(ks, (double)oz, kz))
+    return false;
+  if (steps) ++*steps;
+  int st = cell(kx, ky, kz);
+  if (st == CELL_OCCUPIED) { hx = kx; hy = ky; hz = kz; return true; }
+  if (st == CELL_UNKNOWN && !ignore_unknown) return false;
+  // directionP.normalized(): divide by (float)norm() when the norm is positive
+  double len = norm3f(dirx, diry, dirz);
+  if (len > 0) {
+    float fl = d2f(len);
+    dirx = f_div(dirx, fl); diry = f_div(diry, fl); dirz = f_div(dirz, fl);
+  }
+  int sx, sy, sz;
+  double tx, ty, tz, dtx, dty, dtz;
+  dda_axis(ks, dirx, ox, kx, false, sx, tx, dtx);
+  dda_axis(ks, diry, oy, ky, false, sy, ty, dty);
+  dda_axis(ks, dirz, oz, kz, false, sz, tz, dtz);
+  if (sx == 0 && sy == 0 && sz == 0) return false;
+  const bool max_range_set = (max_range > 0.0);
+  const double maxrange_sq = d_mul(max_range, max_range);
+  for (int it = 0; it < 262144; ++it) {
+    int dim;
+    if (tx < ty) dim = (tx < tz) ? 0 : 2;
+    else dim = (ty < tz) ? 1 : 2;
+    if (dim == 0) {
+      if ((sx < 0 && kx == 0) || (sx > 0 && kx == 65535)) return false;
+      kx += sx; tx = d_add(tx, dtx);
+    } else if (dim == 1) {
+      if ((sy < 0 && ky == 0) || (sy > 0 && ky == 65535)) return false;
+      ky += sy; ty = d_add(ty, dty);
+    } else {
+      if ((sz < 0 && kz == 0) || (sz > 0 && kz == 65535)) return false;
+      kz += sz; tz = d_add(tz, dtz);
+    }
+    if (max_range_set) {
+      // end = keyToCoord(key) narrowed to float; squared distance: float products summed in double
+      float cx = d2f(key_to_coord(ks, kx)), cy = d2f(key_to_coord(ks, ky)), cz = d2f(key_to_coord(ks, kz));
+      float ddx = f_sub(cx, ox), ddy = f_sub(cy, oy), ddz = f_sub(cz, oz);
+      double d2 = 0.0;
+      d2 = d_add(d2, (double)f_mul(ddx, ddx));
+      d2 = d_add(d2, (double)f_mul(ddy, ddy));
+      d2 = d_add(d2, (double)f_mul(ddz, ddz));
+      if (d2 > maxrange_sq) return false;
+    }
+    if (steps) ++*steps;
+    st = cell(kx, ky, kz);
+    if (st == CELL_OCCUPIED) { hx = kx; hy = ky; hz = kz; return true; }
+    if (st == CELL_UNKNOWN && !ignore_unknown) return false;
+  }
+  return false;
+}
+
+// The parallel-ray lattice OctomapWorld::getLineStatusBoundingBox sweeps over the robot box
+// (upstream): per axis disc = size / ceil((size + 0.001) / res), offsets from -size/2 while
+// <= +size/2 by `double +=`.  The accumulated rounding decides how many offsets there are (e.g.
+// four, not five, along a 0.3 m axis at res 0.15), so the table is always generated by this loop.
+// Host only.  Returns the count, or -1 when it exceeds cap.
+inline int ray_lattice_axis(double size, double res, double* out, int cap) {
+  const double epsilon = 0.001;
+  double disc = size / ceil((size + epsilon) / res);
+  if (disc <= 0.0) disc = 1.0;
+  double half = size * 0.5;
+  int n = 0;
+  for (double v = -half; v <= half; v += disc) {
+    if (n >= cap) return -1;
+    out[n++] = v;
+  }
+  return n;
+}
+
+}  // namespace sspp

@@ -1,0 +1,117 @@
+// engine.cuh — device-side data layout shared by the kernels of sspp_gpu.cu.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dda_core.cuh"
+
+namespace sspp {
+
+// Dense occupancy map in HBM.
+//
+// Voxel (x,y,z) of the window (x = key_x - kmin[0] ...) is bit (x & 31) of 32-bit word
+//     word(xw = x >> 5, y, z) = ((xw * NZ) + z) * NY + y                       ["x-packed, y-fastest"]
+// so that the voxels a warp stages around a node — a box of a few words in x and 10-40 rows in y and
+// z — are runs of consecutive words along y (coalesced), and a DDA step along y or z stays in the
+// same or the next 32-byte sector.  Three planes of that shape:
+//   occ      1 = occupied leaf            (octomap: isNodeOccupied)
+//   known    1 = a leaf exists here       (octomap: search() != NULL)
+//   blocked  occ | (treat_unknown ? ~known : 0)   — what a swept-robot ray stops at
+// and one coarse level over 4x4x4 voxel blocks with the same word layout:
+//   cblocked 1 = some voxel of the block is blocked.
+struct DeviceMap {
+  KeySpace ks;
+  int kmin[3];   // key of window voxel (0,0,0)
+  int dims[3];   // padded window size in voxels: x multiple of 128, y and z multiples of 4
+  int nxw;       // dims[0] / 32
+  int cdims[3];  // dims / 4
+  int cnxw;      // cdims[0] / 32
+  int treat_unknown;
+  const uint32_t* occ;
+  const uint32_t* known;
+  const uint32_t* blocked;
+  const uint32_t* cblocked;
+};
+
+__device__ __forceinline__ size_t map_word(const DeviceMap& m, int xw, int y, int z) {
+  return ((size_t)xw * m.dims[2] + z) * m.dims[1] + y;
+}
+
+// CellStatus of one key straight from HBM/L2 (no staging).  Keys outside the window were never observed.
+__device__ __forceinline__ int map_cell_status(const DeviceMap& m, int kx, int ky, int kz) {
+  int x = kx - m.kmin[0], y = ky - m.kmin[1], z = kz - m.kmin[2];
+  if ((unsigned)x >= (unsigned)m.dims[0] || (unsigned)y >= (unsigned)m.dims[1] || (unsigned)z >= (unsigned)m.dims[2])
+    return CELL_UNKNOWN;
+  size_t w = map_word(m, x >> 5, y, z);
+  uint32_t bit = 1u << (x & 31);
+  if (!(__ldg(m.known + w) & bit)) return CELL_UNKNOWN;
+  return (__ldg(m.occ + w) & bit) ? CELL_OCCUPIED : CELL_FREE;
+}
+
+// 1 when a swept-robot ray must stop at this key.
+__device__ __forceinline__ int map_blocked(const DeviceMap& m, int kx, int ky, int kz) {
+  int x = kx - m.kmin[0], y = ky - m.kmin[1], z = kz - m.kmin[2];
+  if ((unsigned)x >= (unsigned)m.dims[0] || (unsigned)y >= (unsigned)m.dims[1] || (unsigned)z >= (unsigned)m.dims[2])
+    return m.treat_unknown;
+  return (__ldg(m.blocked + map_word(m, x >> 5, y, z)) >> (x & 31)) & 1u;
+}
+
+// getLineStatus cell functor on the raw planes: unknown only stops the walk when it counts as occupied.
+struct CellFromPlanes {
+  const DeviceMap* m;
+  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const {
+    int st = map_cell_status(*m, kx, ky, kz);
+    if (st == CELL_UNKNOWN && !m->treat_unknown) return CELL_FREE;
+    return st;
+  }
+};
+
+// castRay cell functor: the plain status.
+struct CellStatusFn {
+  const DeviceMap* m;
+  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const { return map_cell_status(*m, kx, ky, kz); }
+};
+
+// A per-warp copy of the blocked plane around one source node, in shared memory.  It is a cache,
+// not a bound: a key outside it falls through to the global plane, so its size never changes a result.
+struct BlockedTile {
+  const uint32_t* tile;  // [XW][SZ][SY] words, shared memory
+  int xw0, y0, z0;       // window coordinates of tile word (0,0,0)
+  int XW, SY, SZ;
+  const DeviceMap* m;
+  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const {
+    int x = kx - m->kmin[0], y = ky - m->kmin[1], z = kz - m->kmin[2];
+    unsigned tx = (unsigned)((x >> 5) - xw0), ty = (unsigned)(y - y0), tz = (unsigned)(z - z0);
+    if (tx < (unsigned)XW && ty < (unsigned)SY && tz < (unsigned)SZ)
+      return (tile[(tx * SZ + tz) * SY + ty] >> (x & 31)) & 1u;
+    return map_blocked(*m, kx, ky, kz);
+  }
+};
+
+struct BlockedGlobal {
+  const DeviceMap* m;
+  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const { return map_blocked(*m, kx, ky, kz); }
+};
+
+// Uniform grid over the node set for the radius search (cell edge >= radius, so 27 cells suffice).
+struct NodeGrid {
+  double min[3];
+  double inv_cell;
+  int n[3];  // cells per axis; cell id = (cz * n[1] + cy) * n[0] + cx
+};
+
+__device__ __forceinline__ int grid_cell_axis(const NodeGrid& g, double v, int a) {
+  int c = (int)floor((v - g.min[a]) * g.inv_cell);
+  return c < 0 ? 0 : (c >= g.n[a] ? g.n[a] - 1 : c);
+}
+
+#define SSPP_MAX_LATTICE 64  // ray offsets per axis the kernels keep in constant memory
+
+struct RayLattice {
+  double off[3][SSPP_MAX_LATTICE];
+  int n[3];
+  int rays;  // n[0]*n[1]*n[2]
+};
+
+}  // namespace sspp

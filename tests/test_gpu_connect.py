@@ -1,0 +1,238 @@
+"""Parity of the CUDA connection pass with the oracle, through the C ABI (bit-exact CSR)."""
+import os
+
+import numpy as np
+import pytest
+
+from sspp_b200 import scenes
+from sspp_b200.engine import SsppError
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+BOX = (0.5, 0.5, 0.3)
+
+
+def make_map(eng, orc, res, treat, n_vox=64, seed=3, shell=0.0, region=None, n_boxes=8, n_spheres=6):
+    region = region if region is not None else n_vox * res * 0.75
+    km, dm, occ, known = scenes.synthetic_map(n_vox=n_vox, res=res, seed=seed, n_boxes=n_boxes, n_spheres=n_spheres,
+                                              region=region, unknown_shell=shell)
+    eng.map_create(res, km, dm, treat)
+    eng.map_upload_dense(occ, known)
+    w = orc.world(res, treat)
+    w.build_dense(km, dm, occ, known)
+    return w
+
+
+def assert_same_graph(eng, orc, w, nodes, radius, box=BOX, mode=0, **kw):
+    eng.set_nodes(nodes)
+    st = eng.connect(radius=radius, box=box, use_map=w is not None, position_mode=mode, **kw)
+    rp, col = eng.connect_fetch(st)
+    rp_o, col_o, cnt = orc.connect(w, nodes, radius, box, mode)
+    assert np.array_equal(rp, rp_o), "row_ptr differs"
+    assert np.array_equal(col, col_o), "col_idx differs"
+    assert st.edges == len(col_o) and st.tested_pairs == cnt[0] and st.in_radius_pairs == cnt[0] + cnt[1]
+    return st, cnt
+
+
+def test_known_answer_no_map(eng, orc):
+    """src/distance_heuristic_test.cpp scenario (golden from the reference's own sources): 1452 nodes, 80 580 edges"""
+    g = np.load(os.path.join(GOLD, "dht_known_answer.npz"))
+    eng.set_nodes(g["poses"][:, :3])
+    st = eng.connect(radius=1.5, use_map=False)
+    rp, col = eng.connect_fetch(st)
+    assert st.edges == 80580 and st.tested_pairs == 76224
+    assert np.array_equal(rp, g["row_ptr"]) and np.array_equal(col, g["col_idx"])
+
+
+def test_reactive_sphere_golden(eng, orc):
+    """reactive scene through map_set_box (setFree) + leaf upload; golden adjacency from oracle/_ref"""
+    g = np.load(os.path.join(GOLD, "reactive_sphere.npz"))
+    eng.map_create(0.3, [32768 - 64] * 3, [128] * 3, False)
+    eng.map_set_box([0, 0, 0], [15, 15, 10], False)
+    k = g["sphere_keys"].astype(np.float64)
+    eng.map_upload_boxes((k - 32768 + 0.5) * 0.3, np.full(len(k), 0.3), np.ones(len(k), dtype=np.uint8))
+    eng.set_nodes(g["poses"][:, :3])
+    st = eng.connect(radius=1.5, box=BOX, use_map=True)
+    rp, col = eng.connect_fetch(st)
+    assert st.tested_pairs == 840 and st.edges == 777
+    assert np.array_equal(rp, g["row_ptr"]) and np.array_equal(col, g["col_idx"])
+
+
+def test_uav_fixture_golden(eng):
+    g = np.load(os.path.join(GOLD, "uav_fixture_R25.npz"))
+    eng.set_nodes(g["poses"][:, :3])
+    st = eng.connect(radius=2.5, use_map=False)
+    rp, col = eng.connect_fetch(st)
+    assert st.edges == int(g["connections"]) and np.array_equal(rp, g["row_ptr"])
+    assert np.array_equal(col[:4096], g["col_head"])
+
+
+@pytest.mark.parametrize("res,treat,shell", [(0.3, True, 0.0), (0.3, False, 0.2), (0.3, True, 0.2), (0.15, True, 0.0),
+                                             (0.5, False, 0.0), (1.0, True, 0.0), (0.1, True, 0.1)])
+def test_lattice_nodes_with_map(eng, orc, res, treat, shell):
+    n_vox = 64 if res >= 0.3 else 96
+    w = make_map(eng, orc, res, treat, n_vox=n_vox, shell=shell)
+    ext = n_vox * res
+    npa = max(4, min(14, int(ext * 0.8)))
+    spacing = min(1.0, ext * 0.8 / npa)
+    nodes = scenes.lattice_nodes(npa, spacing)
+    st, cnt = assert_same_graph(eng, orc, w, nodes, 1.5 * spacing)
+    assert 0 < st.edges < st.in_radius_pairs  # some edges collide, some do not
+    w.close()
+
+
+@pytest.mark.parametrize("pyramid", [True, False])
+def test_random_nodes_with_map(eng, orc, pyramid):
+    w = make_map(eng, orc, 0.3, True, n_vox=96, seed=9)
+    nodes = scenes.uniform_nodes(3000, extent=22.0, seed=5)
+    st, _ = assert_same_graph(eng, orc, w, nodes, 1.7, use_pyramid=pyramid)
+    assert (st.pyramid_rows > 0) == pyramid
+    w.close()
+
+
+def test_duplicates_and_position_modes(eng, orc):
+    """same-position nodes (other yaw) are connected without a test; mode 1 uses the 1e-12 tolerance"""
+    w = make_map(eng, orc, 0.3, True, n_vox=64, seed=4)
+    base = scenes.lattice_nodes(6, 1.0)
+    jit = base[:50] + 1e-13   # equal under isPositionEqual, different under exact !=
+    nodes = np.concatenate([base, base[::3], jit])
+    for mode in (0, 1):
+        st, cnt = assert_same_graph(eng, orc, w, nodes, 1.5, mode=mode)
+        assert cnt[1] > 0
+    w.close()
+
+
+def test_large_box_many_rays(eng, orc):
+    """r > 32 rays per pair (chunked lattice) and a tile too large to stage (direct lookups)"""
+    w = make_map(eng, orc, 0.1, True, n_vox=128, seed=6, region=9.0)
+    nodes = scenes.uniform_nodes(400, extent=8.0, seed=8)
+    assert_same_graph(eng, orc, w, nodes, 1.2, box=(0.5, 0.5, 0.3))    # 245 rays
+    assert_same_graph(eng, orc, w, nodes[:150], 4.0, box=(0.3, 0.2, 0.0))  # reach too wide for the smem tile
+    w.close()
+
+
+def test_edge_cases(eng, orc):
+    w = make_map(eng, orc, 0.3, True)
+    # empty node set
+    eng.set_nodes(np.zeros((0, 3)))
+    st = eng.connect(radius=1.5)
+    rp, col = eng.connect_fetch(st)
+    assert st.edges == 0 and rp.tolist() == [0] and len(col) == 0
+    # a single node, and two coincident nodes
+    assert_same_graph(eng, orc, w, np.array([[0.1, 0.2, 0.3]]), 1.5)
+    assert_same_graph(eng, orc, w, np.array([[0.1, 0.2, 0.3], [0.1, 0.2, 0.3]]), 1.5)
+    # radius 0 and negative radius
+    nodes = scenes.lattice_nodes(4, 1.0)
+    assert_same_graph(eng, orc, w, nodes, 0.0)
+    assert_same_graph(eng, orc, w, nodes, -1.0)
+    # radius exactly on the lattice spacing: `<=` keeps the axis neighbours
+    st, _ = assert_same_graph(eng, orc, w, nodes, 1.0)
+    # nodes outside the mapped window (unknown there)
+    far = nodes + 500.0
+    assert_same_graph(eng, orc, w, far, 1.5)
+    # zero-size robot box: a single ray
+    assert_same_graph(eng, orc, w, nodes, 1.5, box=(0.0, 0.0, 0.0))
+    w.close()
+
+
+def test_errors(eng):
+    with pytest.raises(SsppError) as e:
+        eng.connect(radius=1.5, use_map=True)          # no map yet
+    assert e.value.code == 3
+    eng.set_nodes(np.array([[0.0, np.nan, 0.0], [1.0, 0.0, 0.0]]))
+    with pytest.raises(SsppError) as e:
+        eng.connect(radius=1.5, use_map=False)
+    assert e.value.code == 1 and "finite" in str(e.value)
+    eng.set_nodes(np.zeros((4, 3)))
+    with pytest.raises(SsppError):
+        eng.connect(radius=1.5, use_map=False, rows=(2, 9))
+    with pytest.raises(SsppError):
+        eng.map_create(0.3, [65000] * 3, [1024] * 3, True)   # window leaves the 16-bit key space
+
+
+def test_row_sharding_concatenates_to_full_csr(eng, orc):
+    """multi-GPU partition: CSR blocks of contiguous row ranges concatenate to the 1-GPU CSR"""
+    w = make_map(eng, orc, 0.3, True, n_vox=96, seed=9)
+    nodes = scenes.uniform_nodes(2500, extent=20.0, seed=12)
+    eng.set_nodes(nodes)
+    st = eng.connect(radius=1.7, box=BOX)
+    rp, col = eng.connect_fetch(st)
+    parts_rp, parts_col = [np.zeros(1, dtype=np.int64)], []
+    bounds = [0, 700, 701, 1800, 2500]
+    for lo, hi in zip(bounds[:-1], bounds[1:]):
+        s = eng.connect(radius=1.7, box=BOX, rows=(lo, hi))
+        r, c = eng.connect_fetch(s)
+        assert s.rows == hi - lo
+        parts_rp.append(r[1:] + parts_rp[-1][-1])
+        parts_col.append(c)
+    assert np.array_equal(np.concatenate(parts_rp), rp) and np.array_equal(np.concatenate(parts_col), col)
+    w.close()
+
+
+def test_connect_nodes_host_and_determinism(eng, orc):
+    w = make_map(eng, orc, 0.3, True, n_vox=96, seed=9)
+    nodes = scenes.uniform_nodes(2000, extent=20.0, seed=2)
+    rp_o, col_o, _ = orc.connect(w, nodes, 1.6, BOX)
+    rp = np.zeros(len(nodes) + 1, dtype=np.int64)
+    col = np.zeros(len(col_o) + 16, dtype=np.int32)
+    for _ in range(3):
+        st = eng.connect_nodes_host(nodes, rp, col, radius=1.6, box=BOX)
+        assert np.array_equal(rp, rp_o) and np.array_equal(col[:st.edges], col_o)
+    small = np.zeros(4, dtype=np.int32)
+    with pytest.raises(SsppError) as e:
+        eng.connect_nodes_host(nodes, rp, small, radius=1.6, box=BOX)
+    assert e.value.code == 4
+    w.close()
+
+
+def test_full_size_properties(eng):
+    """BASELINE config 4 shape (512^3 voxels, 10^6 lattice nodes): size-independent properties.
+    (a) with an empty (all-free) map the graph equals the map-free graph; (b) the pyramid skip does
+    not change the graph; (c) interior degree is 18 without obstacles; (d) rows are ascending."""
+    res = 0.3
+    km, dm, occ, known = scenes.synthetic_map(n_vox=512, res=res, seed=42)
+    nodes = scenes.lattice_nodes(100, 1.0)
+    eng.set_nodes(nodes)
+    s0 = eng.connect(radius=1.5, use_map=False)
+    rp0, col0 = eng.connect_fetch(s0)
+    assert s0.tested_pairs == 17701200  # candidate pairs of the 100^3 lattice at R = 1.5
+    assert np.diff(rp0).max() == 18
+    eng.map_create(res, km, dm, True)
+    eng.map_upload_dense(np.zeros_like(occ), known)
+    s1 = eng.connect(radius=1.5, box=BOX, use_map=True, use_pyramid=False)
+    rp1, col1 = eng.connect_fetch(s1)
+    assert np.array_equal(rp0, rp1) and np.array_equal(col0, col1)
+    eng.map_upload_dense(occ, known)
+    sa = eng.connect(radius=1.5, box=BOX, use_map=True, use_pyramid=True)
+    rpa, cola = eng.connect_fetch(sa)
+    sb = eng.connect(radius=1.5, box=BOX, use_map=True, use_pyramid=False)
+    rpb, colb = eng.connect_fetch(sb)
+    assert np.array_equal(rpa, rpb) and np.array_equal(cola, colb)
+    assert 0 < sa.edges < s0.edges and sa.pyramid_rows > 0
+    # every accepted edge is also an edge of the map-free graph, and columns ascend within a row
+    rows = np.repeat(np.arange(len(nodes)), np.diff(rpa))
+    d = cola[1:] - cola[:-1]
+    assert np.all((d > 0) | (rows[1:] != rows[:-1]))
+    key0 = rows.astype(np.int64) * len(nodes) + cola
+    rows0 = np.repeat(np.arange(len(nodes)), np.diff(rp0))
+    assert np.isin(key0, rows0.astype(np.int64) * len(nodes) + col0, assume_unique=True).all()
+
+
+@pytest.mark.parametrize("res,box", [(0.3, BOX), (0.15, BOX), (1.0, BOX), (0.1, (0.5, 0.5, 0.3))])
+def test_voxel_step_count_matches_reference_semantics(eng, orc, res, box):
+    """the instrumented run counts exactly the lookups getLineStatusBoundingBox performs (rays in
+    lattice order, stopping at the first non-free voxel of the first failing ray) — the Σsteps term
+    of the roofline's byte model"""
+    n_vox = 64 if res >= 0.3 else 96
+    w = make_map(eng, orc, res, True, n_vox=n_vox, seed=21, shell=0.1)
+    ext = n_vox * res
+    nodes = scenes.uniform_nodes(600, extent=ext * 0.7, seed=4)
+    radius = min(1.5, ext / 6)
+    eng.set_nodes(nodes)
+    st = eng.connect(radius=radius, box=box, count_steps=True)
+    rp, col = eng.connect_fetch(st)
+    rp_o, col_o, cnt = orc.connect(w, nodes, radius, box)
+    assert np.array_equal(col, col_o)
+    assert st.voxel_steps == cnt[2] and st.voxel_steps > 0
+    assert st.tested_pairs * st.rays_per_pair >= cnt[3]
+    w.close()

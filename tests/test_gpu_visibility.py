@@ -1,0 +1,73 @@
+"""Coverage visibility (spec v1): frustum culling + occlusion castRay, CUDA vs oracle, through the C ABI."""
+import numpy as np
+import pytest
+
+from sspp_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+
+
+def scene(eng, orc, res=0.25, n_vox=96, seed=4):
+    km, dm, occ, known = scenes.synthetic_map(n_vox=n_vox, res=res, seed=seed, n_boxes=10, n_spheres=8,
+                                              region=n_vox * res * 0.7)
+    eng.map_create(res, km, dm, True)
+    eng.map_upload_dense(occ, known)
+    w = orc.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    pts = scenes.surface_points(occ, known, km, dm, res, 20000, seed=45)
+    return w, pts
+
+
+def test_visibility_matches_oracle(eng, orc):
+    w, pts = scene(eng, orc)
+    poses = scenes.viewpoints_near(pts, 60, standoff=3.0, seed=46)
+    eng.set_model_points(pts)
+    st, vp, idx = eng.visibility(poses, 58.0, 45.0, 0.7, 6.0)
+    vp_o, idx_o, rays_o, _ = w.visibility(poses, 58.0, 45.0, 0.7, 6.0, pts)
+    assert st.rays == rays_o and rays_o > 0
+    assert np.array_equal(vp, vp_o) and np.array_equal(idx, idx_o)
+    assert 0 < st.visible_pairs < st.rays  # some in-frustum points are occluded
+    w.close()
+
+
+def test_visibility_degenerate_inputs(eng, orc):
+    w, pts = scene(eng, orc)
+    eng.set_model_points(pts)
+    # no viewpoints / no points
+    st, vp, idx = eng.visibility(np.zeros((0, 7)), 58.0, 45.0, 0.7, 6.0)
+    assert st.rays == 0 and vp.tolist() == [0]
+    poses = scenes.viewpoints_near(pts, 8, standoff=2.0, seed=1)
+    eng.set_model_points(np.zeros((0, 3), dtype=np.float32))
+    st, vp, idx = eng.visibility(poses, 58.0, 45.0, 0.7, 6.0)
+    assert st.visible_pairs == 0 and len(vp) == 9
+    # viewpoint sitting exactly on a model point; wide and narrow frusta; many points per viewpoint
+    eng.set_model_points(pts)
+    poses[0, :3] = pts[5]
+    for hf, vf, nr, fr in ((58.0, 45.0, 0.7, 6.0), (120.0, 100.0, 0.0, 12.0), (5.0, 5.0, 1.0, 4.0)):
+        st, vp, idx = eng.visibility(poses, hf, vf, nr, fr)
+        vp_o, idx_o, rays_o, _ = w.visibility(poses, hf, vf, nr, fr, pts)
+        assert st.rays == rays_o and np.array_equal(vp, vp_o) and np.array_equal(idx, idx_o)
+    w.close()
+
+
+def test_visibility_large_segments_sorted(eng, orc):
+    """more than 8192 visible points for one viewpoint exercises the global-memory sort path"""
+    res = 0.25
+    km, dm = [32768 - 48] * 3, [96] * 3
+    occ = np.zeros((96, 96, 96), dtype=bool)
+    occ[:, :, 70:72] = True  # a wall at x ~ 5.5 m
+    known = np.ones_like(occ)
+    ob, kb = scenes.pack_bits(occ), scenes.pack_bits(known)
+    eng.map_create(res, km, dm, True)
+    eng.map_upload_dense(ob, kb)
+    w = orc.world(res, True)
+    w.build_dense(km, dm, ob, kb)
+    rng = np.random.RandomState(0)
+    pts = np.stack([np.full(40000, 5.6), rng.uniform(-3, 3, 40000), rng.uniform(-3, 3, 40000)], axis=1).astype(np.float32)
+    pose = np.array([[0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 1.0]])  # looking along +x
+    eng.set_model_points(pts)
+    st, vp, idx = eng.visibility(pose, 90.0, 90.0, 0.5, 9.0)
+    vp_o, idx_o, rays_o, _ = w.visibility(pose, 90.0, 90.0, 0.5, 9.0, pts)
+    assert st.visible_pairs > 8192
+    assert np.array_equal(vp, vp_o) and np.array_equal(idx, idx_o)
+    w.close()
