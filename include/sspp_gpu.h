@@ -137,6 +137,25 @@ int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n,
 int sspp_gpu_check_segments(sspp_gpu_ctx* ctx, const double* starts_xyz, const double* ends_xyz, int64_t n,
                             const double box[3], uint8_t* status);
 
+/* Allocation-free twin of sspp_gpu_check_segments.  No counterpart in the reference: it exists for
+ * callers that must not, or cannot, obtain device memory at query time — a replanning callback that
+ * runs after some other component (an inference engine, a memory pool) has claimed the rest of the
+ * GPU, or a control loop that cannot afford the device-wide stall a cudaMalloc/cudaFree causes.
+ * Same arguments, same results; the difference is where the working memory comes from: the device
+ * copies of `starts`/`ends`/`status` and the ray-offset table live in one fixed array compiled into
+ * the library (about 0.8 MB, resident on every GPU that loads the library until the process exits),
+ * so the call performs no cudaMalloc, cudaFree or other allocating call.
+ *   - n may not exceed SSPP_NOALLOC_MAX_SEGMENTS; a larger batch is refused with SSPP_ERR_RANGE
+ *     (split it, or use sspp_gpu_check_segments).
+ *   - The first call on each device looks up the array's device address; make that first call
+ *     before starting any stream capture on that device.
+ *   - The array is shared by every context on the device and keeps the previous call's contents.
+ *     Each call overwrites everything it later reads, so nothing needs clearing between calls, but
+ *     two calls whose GPU work overlaps (different contexts or threads) would race on it: serialise them. */
+#define SSPP_NOALLOC_MAX_SEGMENTS 16384
+int sspp_gpu_check_segments_noalloc(sspp_gpu_ctx* ctx, const double* starts_xyz, const double* ends_xyz, int64_t n,
+                                    const double box[3], uint8_t* status);
+
 /* Node validity.  Replaces: the hook Heuristic::isFilteringConditionSatisfied
  * (include/sspp/heuristic_interface.h:44; called at src/pathplanner.cpp:160), which the only
  * heuristic in the reference answers `true` (src/distance_heuristic.cpp:134-138).  Defined here as

@@ -1651,6 +1651,79 @@ int sspp_gpu_check_segments(sspp_gpu_ctx* ctx, const double* starts, const doubl
   return SSPP_OK;
 }
 
+// ---- allocation-free segment check ------------------------------------------------------------
+// Working memory for sspp_gpu_check_segments_noalloc: one fixed device array instead of the
+// cudaMalloc-ed staging buffers the regular entry point grows on demand.  Layout (bytes):
+//   [0, 2048)                      ray-offset table (RayLattice, rewritten in full by every call)
+//   [2048, +24*MAX)                segment starts   (first n entries rewritten before they are read)
+//   [.., +24*MAX)                  segment ends     (same)
+//   [.., +MAX)                     status bytes     (first n written by the kernel, then copied out)
+// Nothing in it has to start at zero, so no clearing is needed; every GPU that loads the library
+// holds the array (~0.8 MB) until the process exits.
+namespace {
+constexpr size_t NA_MAX = SSPP_NOALLOC_MAX_SEGMENTS;
+constexpr size_t NA_LATTICE_BYTES = 2048;
+constexpr size_t NA_STARTS_OFF = NA_LATTICE_BYTES;
+constexpr size_t NA_ENDS_OFF = NA_STARTS_OFF + NA_MAX * 24;
+constexpr size_t NA_STATUS_OFF = NA_ENDS_OFF + NA_MAX * 24;
+constexpr size_t NA_BYTES = NA_STATUS_OFF + NA_MAX;
+static_assert(sizeof(RayLattice) <= NA_LATTICE_BYTES, "ray-offset table must fit its slot");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the
+// address a kernel can use is asked for once per device, with that device current.
+constexpr int NA_MAX_DEVICES = 64;
+unsigned char* g_noalloc_addr[NA_MAX_DEVICES] = {nullptr};
+
+int noalloc_scratch_address(sspp_gpu_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= NA_MAX_DEVICES) return fail(ctx, SSPP_ERR_RANGE, "check_segments_noalloc: device index too large");
+  if (!g_noalloc_addr[ctx->device]) {
+    unsigned char* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || !ptr) return cuda_fail(ctx, e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    g_noalloc_addr[ctx->device] = ptr;
+  }
+  *out = g_noalloc_addr[ctx->device];
+  return SSPP_OK;
+}
+}  // namespace
+
+// Batched getLineStatusBoundingBox without any device allocation (see include/sspp_gpu.h).  The
+// first call on a device resolves the scratch array's address — do it before any stream capture.
+// All contexts of a device share the array: calls whose GPU work overlaps race on it.
+int sspp_gpu_check_segments_noalloc(sspp_gpu_ctx* ctx, const double* starts, const double* ends, int64_t n,
+                                    const double box[3], uint8_t* status) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!ctx->has_map) return fail(ctx, SSPP_ERR_STATE, "no map");
+  if (n < 0 || !box || (n > 0 && (!starts || !ends || !status))) return fail(ctx, SSPP_ERR_INVALID, "check_segments_noalloc: null argument");
+  if (n > (int64_t)NA_MAX)
+    return fail(ctx, SSPP_ERR_RANGE, "check_segments_noalloc: more than SSPP_NOALLOC_MAX_SEGMENTS (16384) segments in one call; "
+                                     "split the batch or use sspp_gpu_check_segments");
+  if (n == 0) return SSPP_OK;
+  CK(cudaSetDevice(ctx->device));
+  unsigned char* base = nullptr;
+  int rc = noalloc_scratch_address(ctx, &base);
+  if (rc) return rc;
+  RayLattice lat;
+  rc = build_lattice(ctx, box, lat);
+  if (rc) return rc;
+  RayLattice* d_lat = (RayLattice*)base;
+  double* d_starts = (double*)(base + NA_STARTS_OFF);
+  double* d_ends = (double*)(base + NA_ENDS_OFF);
+  uint8_t* d_status = base + NA_STATUS_OFF;
+  CK(cudaMemcpyAsync(d_lat, &lat, sizeof(RayLattice), cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(d_starts, starts, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(d_ends, ends, (size_t)n * 24, cudaMemcpyHostToDevice, ctx->stream));
+  int G = lat.rays >= 32 ? 32 : lat.rays;
+  int EPI = 32 / G;
+  int64_t warps = (n + EPI - 1) / EPI;
+  k_check_segments<<<ceil_div(warps * 32, 256), 256, 0, ctx->stream>>>(ctx->map, d_lat, d_starts, d_ends, n, d_status);
+  LAUNCHED(ctx);
+  CK(cudaMemcpyAsync(status, d_status, (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return SSPP_OK;
+}
+
 int sspp_gpu_validity(sspp_gpu_ctx* ctx, const double* pts, int64_t n, const double box[3], uint8_t* status) {
   if (!ctx) return SSPP_ERR_INVALID;
   if (!ctx->has_map) return fail(ctx, SSPP_ERR_STATE, "no map");

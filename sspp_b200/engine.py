@@ -74,6 +74,7 @@ def load_library():
                                                        c_i64, ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_timings": (ctypes.c_int, [c_vp, c_vp]),
         "sspp_gpu_check_segments": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp]),
+        "sspp_gpu_check_segments_noalloc": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp]),
         "sspp_gpu_validity": (ctypes.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
         "sspp_gpu_cast_rays": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, ctypes.c_int, c_vp, c_vp, c_vp]),
         "sspp_gpu_set_model_points": (ctypes.c_int, [c_vp, c_vp, c_i64]),
@@ -223,6 +224,16 @@ class Engine:
         b = _f64(box)
         out = np.zeros(len(s), dtype=np.uint8)
         self._ck(self.L.sspp_gpu_check_segments(self.h, _p(s), _p(e), len(s), _p(b), _p(out)))
+        return out
+
+    def check_segments_noalloc(self, starts, ends, box=(0.5, 0.5, 0.3)):
+        """Same query through the entry point that allocates no device memory (at most
+        SSPP_NOALLOC_MAX_SEGMENTS = 16384 segments per call)."""
+        s = _f64(starts, 3)
+        e = _f64(ends, 3)
+        b = _f64(box)
+        out = np.zeros(len(s), dtype=np.uint8)
+        self._ck(self.L.sspp_gpu_check_segments_noalloc(self.h, _p(s), _p(e), len(s), _p(b), _p(out)))
         return out
 
     def validity(self, points, box=(0.5, 0.5, 0.3)):
