@@ -448,7 +448,8 @@ def main():
                 "l2_read_gbps_measured": l2_gbps, "frac_of_l2": (achieved / l2_gbps) if l2_gbps else None,
                 "phase_ms": {"total": float(ph[0]), "binning": float(ph[1]), "count": float(ph[2]), "edges": float(ph[3]),
                              "csr": float(ph[4])},
-                "pyramid_rows": int(st.pyramid_rows)}
+                "pyramid_rows": int(st.pyramid_rows), "tile_rows": int(st.tile_rows), "box_pairs": int(st.box_pairs),
+                "lattice_pairs": int(st.lattice_pairs)}
 
     # ---- visibility half of the metric (rank 0, one GPU): occlusion rays/s
     vis = None

@@ -35,7 +35,8 @@ def build_gpu(force=False, verbose=False):
     srcs.append(os.path.join(REPO, "include", "sspp_gpu.h"))
     if not force and _newer(LIB_GPU, srcs):
         return LIB_GPU
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_GPU, srcs[0]]
+    extra = os.environ.get("SSPP_NVCC_EXTRA", "").split()  # e.g. -DEDGE_MIN_BLOCKS=2 for tuning runs
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_GPU, srcs[0]]
     subprocess.run(cmd, check=True, cwd=CSRC)
     return LIB_GPU
 

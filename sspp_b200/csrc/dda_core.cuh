@@ -36,6 +36,7 @@ SSPP_HD double d_mul(double a, double b) { return __dmul_rn(a, b); }
 SSPP_HD double d_div(double a, double b) { return __ddiv_rn(a, b); }
 SSPP_HD double d_sqrt(double a) { return __dsqrt_rn(a); }
 SSPP_HD float d2f(double a) { return __double2float_rn(a); }
+SSPP_HD float f_sqrt(float a) { return __fsqrt_rn(a); }
 #else
 SSPP_HD float f_add(float a, float b) { return a + b; }
 SSPP_HD float f_sub(float a, float b) { return a - b; }
@@ -47,6 +48,7 @@ SSPP_HD double d_mul(double a, double b) { return a * b; }
 SSPP_HD double d_div(double a, double b) { return a / b; }
 SSPP_HD double d_sqrt(double a) { return sqrt(a); }
 SSPP_HD float d2f(double a) { return (float)a; }
+SSPP_HD float f_sqrt(float a) { return sqrtf(a); }
 #endif
 
 // Constants of one map, computed once on the host in double.
@@ -103,6 +105,13 @@ SSPP_HD void dda_axis(const KeySpace& ks, float dir, float origin, int key, bool
 // treat_unknown_as_occupied" into the functor).  Start voxel tested, end voxel not; a segment whose
 // ends share a voxel, or with an end outside the 16-bit key range, tests nothing.  `steps`
 // (optional) counts cell() calls.
+//
+// Two rewrites that leave every result unchanged:
+//  * length = (float)sqrt((double)s) upstream; a correctly rounded float sqrt gives the same float
+//    (double rounding is innocuous for sqrt when the wide format has >= 2p+2 bits: 53 >= 50).
+//  * upstream finds argmin(tMax) to advance, then min(tMax) to compare with the length, then
+//    argmin again on the unchanged values: one argmin per iteration serves both (the axis the tie
+//    rule picks always holds the minimum value).
 template <class Cell>
 SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float ex, float ey, float ez, Cell& cell,
                         int* steps = nullptr) {
@@ -116,7 +125,7 @@ SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float 
   if (st) return st;
 
   float dx = f_sub(ex, ox), dy = f_sub(ey, oy), dz = f_sub(ez, oz);
-  float length = d2f(norm3f(dx, dy, dz));
+  float length = f_sqrt(f_add(f_add(f_mul(dx, dx), f_mul(dy, dy)), f_mul(dz, dz)));
   dx = f_div(dx, length);
   dy = f_div(dy, length);
   dz = f_div(dz, length);
@@ -126,18 +135,24 @@ SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float 
   dda_axis(ks, dy, oy, ky, true, sy, ty, dty);
   dda_axis(ks, dz, oz, kz, true, sz, tz, dtz);
   const double dlen = (double)length;
+  // upstream's tie rule: x only if strictly below both, y only if strictly below z, else z
+  bool d0 = (tx < ty) && (tx < tz);
+  bool d1 = !(tx < ty) && (ty < tz);
   for (int it = 0; it < 262144; ++it) {
-    // argmin with upstream's tie rule
-    if (tx < ty) {
-      if (tx < tz) { kx = (kx + sx) & 0xFFFF; tx = d_add(tx, dtx); }
-      else         { kz = (kz + sz) & 0xFFFF; tz = d_add(tz, dtz); }
-    } else {
-      if (ty < tz) { ky = (ky + sy) & 0xFFFF; ty = d_add(ty, dty); }
-      else         { kz = (kz + sz) & 0xFFFF; tz = d_add(tz, dtz); }
-    }
+    const bool d2 = !d0 && !d1;
+    const double tsel = d0 ? tx : (d1 ? ty : tz);
+    const double dsel = d0 ? dtx : (d1 ? dty : dtz);
+    const double tn = d_add(tsel, dsel);
+    tx = d0 ? tn : tx;
+    ty = d1 ? tn : ty;
+    tz = d2 ? tn : tz;
+    kx = (kx + (d0 ? sx : 0)) & 0xFFFF;
+    ky = (ky + (d1 ? sy : 0)) & 0xFFFF;
+    kz = (kz + (d2 ? sz : 0)) & 0xFFFF;
     if (kx == ekx && ky == eky && kz == ekz) break;
-    double m = tx < ty ? tx : ty;  // std::min(std::min(t0,t1),t2)
-    m = tz < m ? tz : m;
+    d0 = (tx < ty) && (tx < tz);
+    d1 = !(tx < ty) && (ty < tz);
+    const double m = d0 ? tx : (d1 ? ty : tz);  // == std::min(std::min(t0,t1),t2)
     if (m > dlen) break;
     if (steps) ++*steps;
     st = cell(kx, ky, kz);

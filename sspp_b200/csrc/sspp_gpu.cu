@@ -51,6 +51,7 @@ struct DevBuf {
 struct TileShape {
   int XW, SY, SZ;     // 0 = no staging
   double reach[3];    // radius + box/2 per axis
+  double half[3];     // box/2 per axis (largest ray offset)
 };
 
 }  // namespace
@@ -415,13 +416,17 @@ __global__ void k_row_scatter(const int* __restrict__ flag, const int* __restric
 
 // pair classification shared by count and gather: 0 = not connected, 1 = goes to the collision test,
 // 2 = same position (connected without a test).  S = candidate, T = source row ("temp").
-__device__ __forceinline__ int pair_class(double sx, double sy, double sz, double tx, double ty, double tz, double radius,
+// The reference tests sqrt(d2) <= radius (Dist, include/sspp/utils.h:356-359).  sqrt is monotone and
+// correctly rounded, so that is the same predicate as d2 <= r2max with r2max = the largest double
+// whose square root does not exceed the radius — computed once on the host (radius_threshold()).
+__device__ __forceinline__ int pair_class(double sx, double sy, double sz, double tx, double ty, double tz, double r2max,
                                           int mode) {
-  double d = dist3(sx, sy, sz, tx, ty, tz);
-  if (!(d <= radius)) return 0;
+  double dx = d_sub(sx, tx), dy = d_sub(sy, ty), dz = d_sub(sz, tz);
+  double d2 = d_add(d_add(d_mul(dx, dx), d_mul(dy, dy)), d_mul(dz, dz));
+  if (!(d2 <= r2max)) return 0;
   bool differs;
   if (mode == 0) differs = (sx != tx || sy != ty || sz != tz);
-  else differs = !(fabs(d_sub(sx, tx)) < 1E-12 && fabs(d_sub(sy, ty)) < 1E-12 && fabs(d_sub(sz, tz)) < 1E-12);
+  else differs = !(fabs(dx) < 1E-12 && fabs(dy) < 1E-12 && fabs(dz) < 1E-12);
   return differs ? 1 : 2;
 }
 
@@ -464,51 +469,68 @@ struct ConnectArgs {
   const int* rows;  // sorted positions of the rows to process, or NULL = all
   int nrows;
   int64_t lo;  // first list index of this shard
-  double radius;
+  double r2max;  // largest d2 with sqrt(d2) <= radius
   int mode;
   int use_map;
   int use_pyramid;
   TileShape ts;
 };
 
-// counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows
+// counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows, [3] voxel steps (instrumented),
+//           [4] (unused), [5] pairs accepted by their key box, [6] pairs that ran the ray lattice
+//
+// One thread per source row walks the 27 neighbouring cells (9 contiguous ranges of the cell-sorted
+// arrays).  FILL == false: count the in-radius pairs and test the row's reach against the pyramid.
+// FILL == true (after the scan of the counts): write the pairs — (sorted position, list index with
+// bit 31 = same position) — to cand[], in cell order; the edge kernel orders them by list index.
+template <bool FILL>
 __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* __restrict__ cand_count,
-                                               uint8_t* __restrict__ row_free, unsigned long long* counters) {
+                                               uint8_t* __restrict__ row_free, unsigned long long* counters,
+                                               const long long* __restrict__ cand_off, int2* __restrict__ cand) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned long long inr = 0, tested = 0, pyr = 0;
   if (t < a.nrows) {
     int s = a.rows ? a.rows[t] : t;
     double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
+    int r = (int)(a.sorted_idx[s] - a.lo);
     int cx = grid_cell_axis(a.g, px, 0), cy = grid_cell_axis(a.g, py, 1), cz = grid_cell_axis(a.g, pz, 2);
     int x0 = max(cx - 1, 0), x1 = min(cx + 1, a.g.n[0] - 1);
     int cnt = 0, tst = 0;
+    long long w = FILL ? cand_off[r] : 0;
     for (int zz = max(cz - 1, 0); zz <= min(cz + 1, a.g.n[2] - 1); ++zz)
       for (int yy = max(cy - 1, 0); yy <= min(cy + 1, a.g.n[1] - 1); ++yy) {
         int base = (zz * a.g.n[1] + yy) * a.g.n[0];
         int b = a.cell_start[base + x0], e = a.cell_start[base + x1 + 1];
         for (int j = b; j < e; ++j) {
           if (j == s) continue;
-          int pc = pair_class(a.sx[j], a.sy[j], a.sz[j], px, py, pz, a.radius, a.mode);
-          cnt += (pc != 0);
-          tst += (pc == 1);
+          int pc = pair_class(a.sx[j], a.sy[j], a.sz[j], px, py, pz, a.r2max, a.mode);
+          if (FILL) {
+            if (pc) cand[w++] = make_int2(j, a.sorted_idx[j] | (pc == 2 ? (int)0x80000000 : 0));
+          } else {
+            cnt += (pc != 0);
+            tst += (pc == 1);
+          }
         }
       }
-    int r = (int)(a.sorted_idx[s] - a.lo);
-    cand_count[r] = cnt;
-    uint8_t fr = 0;
-    if (a.use_map && a.use_pyramid && tst > 0) fr = row_reach_is_free(m, px, py, pz, a.ts.reach) ? 1 : 0;
-    row_free[r] = fr;
-    inr = cnt; tested = tst; pyr = fr;
+    if (!FILL) {
+      cand_count[r] = cnt;
+      uint8_t fr = 0;
+      if (a.use_map && a.use_pyramid && tst > 0) fr = row_reach_is_free(m, px, py, pz, a.ts.reach) ? 1 : 0;
+      row_free[r] = fr;
+      inr = cnt; tested = tst; pyr = fr;
+    }
   }
-  for (int o = 16; o; o >>= 1) {
-    inr += __shfl_xor_sync(0xffffffffu, inr, o);
-    tested += __shfl_xor_sync(0xffffffffu, tested, o);
-    pyr += __shfl_xor_sync(0xffffffffu, pyr, o);
-  }
-  if ((threadIdx.x & 31) == 0) {
-    if (inr) atomicAdd(counters + 0, inr);
-    if (tested) atomicAdd(counters + 1, tested);
-    if (pyr) atomicAdd(counters + 2, pyr);
+  if (!FILL) {
+    for (int o = 16; o; o >>= 1) {
+      inr += __shfl_xor_sync(0xffffffffu, inr, o);
+      tested += __shfl_xor_sync(0xffffffffu, tested, o);
+      pyr += __shfl_xor_sync(0xffffffffu, pyr, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+      if (inr) atomicAdd(counters + 0, inr);
+      if (tested) atomicAdd(counters + 1, tested);
+      if (pyr) atomicAdd(counters + 2, pyr);
+    }
   }
 }
 
@@ -517,13 +539,64 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
 // ------------------------------------------------------------------------------------------------
 constexpr int EDGE_WARPS = 8;
 
+// Does the key box [lo, hi] (absolute keys, inclusive) hold a blocked voxel?  "true" may also mean
+// "cannot tell cheaply" (the box leaves the mapped window): callers then take the exact path.
+__device__ __forceinline__ bool box_maybe_blocked(const DeviceMap& m, int lox, int hix, int loy, int hiy, int loz, int hiz) {
+  const int x0 = lox - m.kmin[0], x1 = hix - m.kmin[0];
+  const int y0 = loy - m.kmin[1], y1 = hiy - m.kmin[1];
+  const int z0 = loz - m.kmin[2], z1 = hiz - m.kmin[2];
+  if (x0 < 0 || y0 < 0 || z0 < 0 || x1 >= m.dims[0] || y1 >= m.dims[1] || z1 >= m.dims[2] || x0 > x1 || y0 > y1 || z0 > z1)
+    return true;
+  const int w0 = x0 >> 5, w1 = x1 >> 5;
+  uint32_t any = 0;
+  for (int w = w0; w <= w1; ++w) {
+    const int b0 = (w == w0) ? (x0 & 31) : 0, b1 = (w == w1) ? (x1 & 31) : 31;
+    const uint32_t mask = (b1 == 31 ? 0xffffffffu : ((1u << (b1 + 1)) - 1u)) & ~((1u << b0) - 1u);
+    for (int z = z0; z <= z1; ++z) {
+      const uint32_t* row = m.blocked + map_word(m, w, 0, z);
+      for (int y = y0; y <= y1; ++y) any |= __ldg(row + y) & mask;
+    }
+  }
+  return any != 0;
+}
+
+// getLineStatus with a shortcut that cannot change its answer: every voxel the DDA can test lies in
+// the key box spanned by the ray's two end keys, grown by ONE voxel beyond the end key on each axis
+// the ray actually moves along (the walk never steps against its direction; on an axis that has
+// reached its end key it can be stepped once more when rounding leaves that axis' tMax just below
+// the length, and never twice because tMax then grows by tDelta >= res).  If that box holds no
+// blocked voxel the ray is free; otherwise the exact walk decides.
+// the exact walk on the blocked plane, kept out of line: it is the rare path of line_status_fast and
+// inlining it would cost the whole edge kernel its occupancy
+__device__ __noinline__ int line_status_exact(const DeviceMap& m, float ox, float oy, float oz, float ex, float ey, float ez) {
+  BlockedGlobal cell;
+  cell.m = &m;
+  return line_status(m.ks, ox, oy, oz, ex, ey, ez, cell);
+}
+
+__device__ __forceinline__ int line_status_fast(const DeviceMap& m, float ox, float oy, float oz, float ex, float ey, float ez) {
+  int kx, ky, kz, ekx, eky, ekz;
+  if (!coord_to_key(m.ks, (double)ox, kx) || !coord_to_key(m.ks, (double)oy, ky) || !coord_to_key(m.ks, (double)oz, kz) ||
+      !coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
+    return CELL_FREE;
+  if (kx == ekx && ky == eky && kz == ekz) return CELL_FREE;
+  const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
+  const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
+  const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
+  if (!box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) return CELL_FREE;
+  return line_status_exact(m, ox, oy, oz, ex, ey, ez);
+}
+
 // Swept-box status of one segment over lanes: `G` lanes share a segment, chunks of G rays with a
 // ballot after each chunk.  Returns, uniformly over the group, the status of the first non-free ray
 // in lattice order (x outer, y, z inner) or CELL_FREE.  `active` = this lane's group has a segment.
-template <bool COUNT, class Cell>
-__device__ __forceinline__ int swept_status(const KeySpace& ks, const RayLattice& lat, Cell& cell, bool active, int G,
-                                            int sub, int lig, double tx, double ty, double tz, double sx, double sy,
-                                            double sz, unsigned long long* steps_acc = nullptr) {
+// (o0x,o0y,o0z) = this lane's ray offset in the first chunk, hoisted by the caller.
+// FAST: rays go through line_status_fast on the blocked plane (`cell` unused).
+template <bool COUNT, bool FAST, class Cell>
+__device__ __forceinline__ int swept_status(const DeviceMap& m, const RayLattice& lat, Cell& cell, bool active, int G,
+                                            int sub, int lig, double o0x, double o0y, double o0z, double tx, double ty,
+                                            double tz, double sx, double sy, double sz,
+                                            unsigned long long* steps_acc = nullptr, bool fast = true) {
   const int nyz = lat.n[1] * lat.n[2];
   int result = CELL_FREE;
   bool done = !active;
@@ -533,11 +606,16 @@ __device__ __forceinline__ int swept_status(const KeySpace& ks, const RayLattice
     int st = CELL_FREE;
     int nsteps = 0;
     if (!done && q < lat.rays) {
-      int ix = q / nyz, rem = q - ix * nyz;
-      int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
-      double ox = lat.off[0][ix], oy = lat.off[1][iy], oz = lat.off[2][iz];
-      st = line_status(ks, d2f(d_add(tx, ox)), d2f(d_add(ty, oy)), d2f(d_add(tz, oz)), d2f(d_add(sx, ox)),
-                       d2f(d_add(sy, oy)), d2f(d_add(sz, oz)), cell, COUNT ? &nsteps : nullptr);
+      double ox = o0x, oy = o0y, oz = o0z;
+      if (q0) {
+        int ix = q / nyz, rem = q - ix * nyz;
+        int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
+        ox = lat.off[0][ix]; oy = lat.off[1][iy]; oz = lat.off[2][iz];
+      }
+      const float fox = d2f(d_add(tx, ox)), foy = d2f(d_add(ty, oy)), foz = d2f(d_add(tz, oz));
+      const float fex = d2f(d_add(sx, ox)), fey = d2f(d_add(sy, oy)), fez = d2f(d_add(sz, oz));
+      if (FAST) st = fast ? line_status_fast(m, fox, foy, foz, fex, fey, fez) : line_status_exact(m, fox, foy, foz, fex, fey, fez);
+      else st = line_status(m.ks, fox, foy, foz, fex, fey, fez, cell, COUNT ? &nsteps : nullptr);
     }
     unsigned b = __ballot_sync(0xffffffffu, st != CELL_FREE);
     unsigned mine = b & gmask;
@@ -554,15 +632,50 @@ __device__ __forceinline__ int swept_status(const KeySpace& ks, const RayLattice
   return result;
 }
 
-template <bool USE_TILE, bool COUNT>
-__global__ void __launch_bounds__(EDGE_WARPS * 32)
+// lane's ray offset in the first chunk of the lattice
+__device__ __forceinline__ void lane_offset(const RayLattice& lat, int lig, double& ox, double& oy, double& oz) {
+  ox = oy = oz = 0.0;
+  if (lig < lat.rays) {
+    const int nyz = lat.n[1] * lat.n[2];
+    int ix = lig / nyz, rem = lig - ix * nyz;
+    int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
+    ox = lat.off[0][ix]; oy = lat.off[1][iy]; oz = lat.off[2][iz];
+  }
+}
+
+// One axis of the key box ALL rays of a pair stay in.  The lattice offsets run from off_first to
+// off_last, and adding an offset and narrowing to float are both monotone, so the extreme rays
+// bound the rest: start keys in [key(f(t+first)), key(f(t+last))], end keys likewise for s; plus the
+// one-voxel overshoot beyond the end on the side the pair travels to (none when s == t: then every
+// ray has a zero direction component on this axis).  False when a key leaves the 16-bit space.
+__device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, double s, double off_first, double off_last,
+                                             int& lo, int& hi) {
+  int o_lo, o_hi, e_lo, e_hi;
+  if (!coord_to_key(ks, (double)d2f(d_add(t, off_first)), o_lo) || !coord_to_key(ks, (double)d2f(d_add(t, off_last)), o_hi) ||
+      !coord_to_key(ks, (double)d2f(d_add(s, off_first)), e_lo) || !coord_to_key(ks, (double)d2f(d_add(s, off_last)), e_hi))
+    return false;
+  if (s > t) { lo = o_lo; hi = e_hi + 1; }
+  else if (s < t) { lo = e_lo - 1; hi = o_hi; }
+  else { lo = o_lo; hi = o_hi; }
+  return true;
+}
+
+// Edge test, one warp per source row.  Work is shed in stages, none of which can change a result
+// (DESIGN.md §5): (1) rows whose reach is free in the coarse pyramid were flagged by k_count;
+// (2) per pair, one lane each: the key box all its rays stay in holds no blocked voxel -> accepted;
+// (3) per ray: the ray's own key box is free -> ray free; (4) the exact DDA walk.
+// The instrumented variant (COUNT) runs every ray through the exact walk.
+#ifndef EDGE_MIN_BLOCKS
+#define EDGE_MIN_BLOCKS 4
+#endif
+template <bool COUNT>
+__global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
 k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
-        const uint8_t* __restrict__ row_free, int2* candA, int2* candB, int* __restrict__ acc, int* __restrict__ deg,
-        unsigned long long* counters) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  RayLattice* lat = (RayLattice*)smem;
-  uint32_t* tiles = (uint32_t*)(smem + sizeof(RayLattice));
-  for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)lat)[i] = ((const uint32_t*)lat_g)[i];
+        const uint8_t* __restrict__ row_free, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
+        int* __restrict__ deg, unsigned long long* counters) {
+  __shared__ RayLattice lat;
+  __shared__ int2 sortbuf[EDGE_WARPS][32];
+  for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -570,7 +683,6 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   if (t >= a.nrows) return;
   const int s = a.rows ? a.rows[t] : t;
   const int r = (int)(a.sorted_idx[s] - a.lo);
-  const double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
   const long long off = cand_off[r];
   const int n = (int)(cand_off[r + 1] - off);
   if (n == 0) {
@@ -578,38 +690,16 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
     return;
   }
 
-  // 1. gather the in-radius pairs of this row (sorted position, list index), in cell order
-  {
-    int cx = grid_cell_axis(a.g, px, 0), cy = grid_cell_axis(a.g, py, 1), cz = grid_cell_axis(a.g, pz, 2);
-    int x0 = max(cx - 1, 0), x1 = min(cx + 1, a.g.n[0] - 1);
-    int filled = 0;
-    for (int zz = max(cz - 1, 0); zz <= min(cz + 1, a.g.n[2] - 1); ++zz)
-      for (int yy = max(cy - 1, 0); yy <= min(cy + 1, a.g.n[1] - 1); ++yy) {
-        int base = (zz * a.g.n[1] + yy) * a.g.n[0];
-        int b = a.cell_start[base + x0], e = a.cell_start[base + x1 + 1];
-        for (int j0 = b; j0 < e; j0 += 32) {
-          int j = j0 + lane;
-          int pc = 0;
-          if (j < e && j != s) pc = pair_class(a.sx[j], a.sy[j], a.sz[j], px, py, pz, a.radius, a.mode);
-          unsigned bal = __ballot_sync(0xffffffffu, pc != 0);
-          if (pc) {
-            // .y carries the list index; bit 31 marks "same position" (list indices are < 2^31)
-            int idx = a.sorted_idx[j] | (pc == 2 ? (int)0x80000000 : 0);
-            candA[off + filled + __popc(bal & ((1u << lane) - 1u))] = make_int2(j, idx);
-          }
-          filled += __popc(bal);
-        }
-      }
-  }
-  __syncwarp();
-
-  // 2. order by list index (reference adjacency is in list order): rank sort
+  // order the pairs by list index (reference adjacency is in list order): rank sort
+  int2 c0 = make_int2(0, 0);  // n <= 32: this lane's pair after sorting
   if (n <= 32) {
     int2 mine = (lane < n) ? candA[off + lane] : make_int2(0, 0x7fffffff);
     int key = mine.y & 0x7fffffff;
     int rank = 0;
     for (int k = 0; k < n; ++k) rank += ((__shfl_sync(0xffffffffu, mine.y, k) & 0x7fffffff) < key);
-    if (lane < n) candB[off + rank] = mine;
+    if (lane < n) sortbuf[warp][rank] = mine;
+    __syncwarp();
+    if (lane < n) c0 = sortbuf[warp][lane];
   } else {
     for (int e = lane; e < n; e += 32) {
       int2 mine = candA[off + e];
@@ -618,80 +708,87 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
       for (int k = 0; k < n; ++k) rank += ((candA[off + k].y & 0x7fffffff) < key);
       candB[off + rank] = mine;
     }
+    __syncwarp();
   }
-  __syncwarp();
 
-  // 3. collision test
-  const bool skip = !a.use_map || row_free[r];
-  if (skip) {
-    for (int e = lane; e < n; e += 32) acc[off + e] = candB[off + e].y & 0x7fffffff;
+  if (!a.use_map || row_free[r]) {
+    if (n <= 32) {
+      if (lane < n) acc[off + lane] = c0.y & 0x7fffffff;
+    } else {
+      for (int e = lane; e < n; e += 32) acc[off + e] = candB[off + e].y & 0x7fffffff;
+    }
     if (lane == 0) deg[r] = n;
     return;
   }
 
-  BlockedTile tile_fn;
-  tile_fn.m = &m;
-  tile_fn.XW = 0; tile_fn.SY = 0; tile_fn.SZ = 0; tile_fn.xw0 = 0; tile_fn.y0 = 0; tile_fn.z0 = 0;
-  tile_fn.tile = nullptr;
-  if (USE_TILE) {
-    uint32_t* my = tiles + (size_t)warp * a.ts.XW * a.ts.SY * a.ts.SZ;
-    int k0x, k0y, k0z;
-    if (coord_to_key(m.ks, px - a.ts.reach[0], k0x) && coord_to_key(m.ks, py - a.ts.reach[1], k0y) &&
-        coord_to_key(m.ks, pz - a.ts.reach[2], k0z)) {
-      tile_fn.xw0 = (k0x - 1 - m.kmin[0]) >> 5;
-      tile_fn.y0 = k0y - 1 - m.kmin[1];
-      tile_fn.z0 = k0z - 1 - m.kmin[2];
-      tile_fn.XW = a.ts.XW; tile_fn.SY = a.ts.SY; tile_fn.SZ = a.ts.SZ;
-      const int total = a.ts.XW * a.ts.SY * a.ts.SZ;
-      const uint32_t outside = m.treat_unknown ? 0xffffffffu : 0u;
-      for (int w = lane; w < total; w += 32) {
-        int ty = w % a.ts.SY, tz = (w / a.ts.SY) % a.ts.SZ, tx = w / (a.ts.SY * a.ts.SZ);
-        int xw = tile_fn.xw0 + tx, y = tile_fn.y0 + ty, z = tile_fn.z0 + tz;
-        uint32_t v = outside;
-        if ((unsigned)xw < (unsigned)m.nxw && (unsigned)y < (unsigned)m.dims[1] && (unsigned)z < (unsigned)m.dims[2])
-          v = __ldg(m.blocked + map_word(m, xw, y, z));
-        my[w] = v;
-      }
-      tile_fn.tile = my;
-    }
-    __syncwarp();
-  }
+  const double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
   BlockedGlobal glob_fn;
   glob_fn.m = &m;
-
-  const int R = lat->rays;
-  const int G = R >= 32 ? 32 : R;      // lanes per candidate
-  const int EPI = 32 / G;              // candidates per warp iteration
+  const int R = lat.rays;
+  const int G = R >= 32 ? 32 : R;      // lanes per pair in the lattice stage
+  const int EPI = 32 / G;              // pairs per warp iteration
   const int sub = lane / G, lig = lane - sub * G;
+  double o0x, o0y, o0z;
+  lane_offset(lat, lig, o0x, o0y, o0z);
   int nacc = 0;
+  unsigned n_box = 0, n_lat = 0;
   unsigned long long nsteps = 0;
   for (int base = 0; base < n; base += 32) {
     const int nb = min(32, n - base);
-    int2 c = (lane < nb) ? candB[off + base + lane] : make_int2(0, 0);
-    unsigned accmask = 0;
-    for (int k = 0; k < nb; k += EPI) {
-      int kk = k + sub;
-      bool have = (sub < EPI) && (kk < nb);
-      int j = __shfl_sync(0xffffffffu, c.x, kk & 31);
-      int idx = __shfl_sync(0xffffffffu, c.y, kk & 31);
-      bool same = (idx & 0x80000000) != 0;
-      bool active = have && !same;
-      double qx = 0, qy = 0, qz = 0;
-      if (active) { qx = a.sx[j]; qy = a.sy[j]; qz = a.sz[j]; }
+    int2 c = (n <= 32) ? c0 : ((lane < nb) ? candB[off + base + lane] : make_int2(0, 0));
+    const bool mine_valid = lane < nb;
+    const bool same = mine_valid && (c.y & 0x80000000);
+    // this lane's pair: coordinates of the far end
+    double qx = 0, qy = 0, qz = 0;
+    if (mine_valid) { qx = a.sx[c.x]; qy = a.sy[c.x]; qz = a.sz[c.x]; }
+    bool needs = mine_valid && !same;
+    // stage 2: the pair's key box (one lane per pair)
+    if (!COUNT && a.use_pyramid && needs) {
+      int lox, hix, loy, hiy, loz, hiz;
+      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
+          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
+          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
+          !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz))
+        needs = false;
+    }
+    unsigned need = __ballot_sync(0xffffffffu, needs);
+    unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs);  // same-position or box-free pairs
+    n_box += __popc(accmask & ~__ballot_sync(0xffffffffu, same));
+    n_lat += __popc(need);
+    // stages 3-4: the ray lattice for what is left, EPI pairs per iteration
+    while (need) {
+      const int kk = __fns(need, 0, sub + 1);           // sub-th remaining pair (or -1)
+      const bool have = (sub < EPI) && kk >= 0 && kk < 32;
+      const int src = have ? kk : 0;
+      const double ex = __shfl_sync(0xffffffffu, qx, src), ey = __shfl_sync(0xffffffffu, qy, src),
+                   ez = __shfl_sync(0xffffffffu, qz, src);
       int st;
-      if (USE_TILE && tile_fn.tile)
-        st = swept_status<COUNT>(m.ks, *lat, tile_fn, active, G, sub, lig, px, py, pz, qx, qy, qz, &nsteps);
+      if (COUNT)
+        st = swept_status<true, false>(m, lat, glob_fn, have, G, sub, lig, o0x, o0y, o0z, px, py, pz, ex, ey, ez, &nsteps);
       else
-        st = swept_status<COUNT>(m.ks, *lat, glob_fn, active, G, sub, lig, px, py, pz, qx, qy, qz, &nsteps);
-      // leaders of each group report acceptance
-      unsigned ok = __ballot_sync(0xffffffffu, have && lig == 0 && st == CELL_FREE);
-      for (int g = 0; g < EPI; ++g)
-        if ((ok >> (g * G)) & 1u) accmask |= 1u << (k + g);
+        st = swept_status<false, true>(m, lat, glob_fn, have, G, sub, lig, o0x, o0y, o0z, px, py, pz, ex, ey, ez, nullptr,
+                                       a.use_pyramid != 0);
+      // group leaders report; every group clears the pair it took
+      unsigned took = 0, okm = 0;
+      for (int g = 0; g < EPI; ++g) {
+        int kg = __shfl_sync(0xffffffffu, have ? kk : -1, g * G);
+        int sg = __shfl_sync(0xffffffffu, st, g * G);
+        if (kg >= 0) {
+          took |= 1u << kg;
+          if (sg == CELL_FREE) okm |= 1u << kg;
+        }
+      }
+      accmask |= okm;
+      need &= ~took;
     }
     if ((accmask >> lane) & 1u) acc[off + nacc + __popc(accmask & ((1u << lane) - 1u))] = c.y & 0x7fffffff;
     nacc += __popc(accmask);
   }
-  if (lane == 0) deg[r] = nacc;
+  if (lane == 0) {
+    deg[r] = nacc;
+    if (n_box) atomicAdd(counters + 5, (unsigned long long)n_box);
+    if (n_lat) atomicAdd(counters + 6, (unsigned long long)n_lat);
+  }
   if (COUNT) {
     for (int o = 16; o; o >>= 1) nsteps += __shfl_xor_sync(0xffffffffu, nsteps, o);
     if (lane == 0 && nsteps) atomicAdd(counters + 3, nsteps);
@@ -734,7 +831,9 @@ __global__ void __launch_bounds__(256) k_check_segments(DeviceMap m, const RayLa
   }
   CellFromPlanes cell;
   cell.m = &m;
-  int st = swept_status<false>(m.ks, lat, cell, active, G, sub, lig, tx, ty, tz, sx, sy, sz);
+  double o0x, o0y, o0z;
+  lane_offset(lat, lig, o0x, o0y, o0z);
+  int st = swept_status<false, false>(m, lat, cell, active, G, sub, lig, o0x, o0y, o0z, tx, ty, tz, sx, sy, sz);
   if (active && lig == 0) status[seg] = (uint8_t)st;
 }
 
@@ -1082,6 +1181,20 @@ __global__ void k_l2_read(const uint4* __restrict__ buf, size_t n16, int iters, 
 // ------------------------------------------------------------------------------------------------
 // host helpers
 // ------------------------------------------------------------------------------------------------
+// largest double t with sqrt(t) <= radius (IEEE sqrt on the host = __dsqrt_rn on the device)
+double radius_threshold(double radius) {
+  if (!(radius >= 0.0)) return -1.0;  // sqrt(d2) >= 0 > radius: no pair connects
+  if (std::isinf(radius)) return radius;
+  double t = radius * radius;
+  while (t > 0.0 && sqrt(t) > radius) t = nextafter(t, 0.0);
+  for (;;) {
+    double u = nextafter(t, INFINITY);
+    if (std::isinf(u) || sqrt(u) > radius) break;
+    t = u;
+  }
+  return t;
+}
+
 int ensure_planes(sspp_gpu_ctx* ctx) {
   if (!ctx->has_map) return fail(ctx, SSPP_ERR_STATE, "no map: call sspp_gpu_map_create first");
   if (!ctx->planes_dirty) return SSPP_OK;
@@ -1361,6 +1474,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   TileShape ts;
   ts.XW = ts.SY = ts.SZ = 0;
   ts.reach[0] = ts.reach[1] = ts.reach[2] = 0;
+  ts.half[0] = ts.half[1] = ts.half[2] = 0;
   const int use_map = prm->use_map ? 1 : 0;
   if (use_map) {
     int rc = ensure_planes(ctx);
@@ -1370,16 +1484,9 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
     rc = upload_lattice(ctx, lat);
     if (rc) return rc;
     const double rad = std::max(prm->radius, 0.0);
-    int span[3];
     for (int a = 0; a < 3; ++a) {
       ts.reach[a] = rad + prm->box[a] * 0.5;
-      double s = 2.0 * ts.reach[a] * ctx->map.ks.res_factor;
-      span[a] = (s < 1.0e6) ? (int)floor(s) + 4 : 1 << 30;  // +1 straddle, +1 each side margin, +1 slack
-    }
-    if (span[0] < (1 << 20) && span[1] < 4096 && span[2] < 4096) {
-      int XW = (span[0] + 62) / 32;
-      int64_t words = (int64_t)XW * span[1] * span[2];
-      if (words <= 2560) { ts.XW = XW; ts.SY = span[1]; ts.SZ = span[2]; }
+      ts.half[a] = prm->box[a] * 0.5;
     }
   }
   if (stats) stats->rays_per_pair = use_map ? lat.rays : 0;
@@ -1481,7 +1588,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   a.rows = rows;
   a.nrows = (int)nrows;
   a.lo = lo;
-  a.radius = prm->radius;
+  a.r2max = radius_threshold(prm->radius);
   a.mode = prm->position_mode;
   a.use_map = use_map;
   const bool count_steps = use_map && prm->count_steps;
@@ -1490,10 +1597,10 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->cand_count.reserve((size_t)nrows * 4));
   CK(ctx->row_free.reserve((size_t)nrows));
   CK(ctx->cand_off.reserve((size_t)(nrows + 1) * 8));
-  CK(ctx->counters.reserve(4 * 8));
-  CK(cudaMemsetAsync(ctx->counters.p, 0, 4 * 8, st));
-  k_count<<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
-                                               ctx->counters.as<unsigned long long>());
+  CK(ctx->counters.reserve(8 * 8));
+  CK(cudaMemsetAsync(ctx->counters.p, 0, 8 * 8, st));
+  k_count<false><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
+                                                      ctx->counters.as<unsigned long long>(), nullptr, nullptr);
   LAUNCHED(ctx);
   {
     int rc = scan_exclusive<long long>(ctx, ctx->cand_count.as<int>(), nrows, ctx->cand_off.as<long long>());
@@ -1517,26 +1624,26 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->candB.reserve((size_t)std::max<long long>(C, 1) * 8));
   CK(ctx->acc.reserve((size_t)std::max<long long>(C, 1) * 4));
   CK(ctx->deg.reserve((size_t)nrows * 4));
+  k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
+                                                     ctx->candA.as<int2>());
+  LAUNCHED(ctx);
   {
-    const bool tile = use_map && ts.XW > 0;
-    size_t smem = sizeof(RayLattice) + (tile ? (size_t)EDGE_WARPS * ts.XW * ts.SY * ts.SZ * 4 : 0);
     if (!use_map) {
       // lattice buffer is still read by the kernel prologue
       int rc = upload_lattice(ctx, lat);
       if (rc) return rc;
     }
     int blocks = ceil_div(nrows, EDGE_WARPS);
-    auto launch = [&](auto kern) -> cudaError_t {
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e != cudaSuccess) return e;
-      kern<<<blocks, EDGE_WARPS * 32, smem, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(),
-                                                  ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
-                                                  ctx->acc.as<int>(), ctx->deg.as<int>(),
-                                                  ctx->counters.as<unsigned long long>());
-      return cudaSuccess;
-    };
-    if (tile) CK(count_steps ? launch(k_edges<true, true>) : launch(k_edges<true, false>));
-    else CK(count_steps ? launch(k_edges<false, true>) : launch(k_edges<false, false>));
+    if (count_steps)
+      k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(),
+                                                        ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
+                                                        ctx->acc.as<int>(), ctx->deg.as<int>(),
+                                                        ctx->counters.as<unsigned long long>());
+    else
+      k_edges<false><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(),
+                                                         ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
+                                                         ctx->acc.as<int>(), ctx->deg.as<int>(),
+                                                         ctx->counters.as<unsigned long long>());
     LAUNCHED(ctx);
   }
   CK(cudaEventRecord(ctx->ev[3], st));
@@ -1549,9 +1656,16 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   long long E = 0;
   unsigned long long hsteps = 0;
   CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
-  if (count_steps) CK(cudaMemcpyAsync(&hsteps, ctx->counters.as<unsigned long long>() + 3, 8, cudaMemcpyDeviceToHost, st));
+  unsigned long long hstage[4] = {0, 0, 0, 0};  // [3] steps, [4] tile rows, [5] box pairs, [6] lattice pairs
+  CK(cudaMemcpyAsync(hstage, ctx->counters.as<unsigned long long>() + 3, 32, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
-  if (stats) stats->voxel_steps = (int64_t)hsteps;
+  hsteps = count_steps ? hstage[0] : 0;
+  if (stats) {
+    stats->voxel_steps = (int64_t)hsteps;
+    stats->tile_rows = (int64_t)hstage[1];
+    stats->box_pairs = (int64_t)hstage[2];
+    stats->lattice_pairs = (int64_t)hstage[3];
+  }
   CK(ctx->col_idx.reserve((size_t)std::max<long long>(E, 1) * 4));
   k_compact<<<ceil_div(nrows * 32, 256), 256, 0, st>>>(ctx->cand_off.as<long long>(), ctx->deg.as<int>(),
                                                       ctx->row_ptr.as<long long>(), ctx->acc.as<int>(), ctx->col_idx.as<int>(),

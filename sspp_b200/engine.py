@@ -28,7 +28,8 @@ class ConnectParams(ctypes.Structure):
 
 class ConnectStats(ctypes.Structure):
     _fields_ = [("rows", c_i64), ("edges", c_i64), ("in_radius_pairs", c_i64), ("tested_pairs", c_i64),
-                ("rays_per_pair", c_i64), ("pyramid_rows", c_i64), ("voxel_steps", c_i64)]
+                ("rays_per_pair", c_i64), ("pyramid_rows", c_i64), ("tile_rows", c_i64), ("box_pairs", c_i64),
+                ("lattice_pairs", c_i64), ("voxel_steps", c_i64)]
 
 
 class Frustum(ctypes.Structure):
