@@ -61,11 +61,21 @@ struct KeySpace {
 
 // upstream OcTreeBaseImpl::coordToKeyChecked(double): floor(res_factor * c) + 32768, valid in [0, 65536)
 SSPP_HD bool coord_to_key(const KeySpace& ks, double c, int& key) {
+#if defined(__CUDA_ARCH__)
+  // floor + conversion in one saturating instruction; out-of-range values saturate far outside
+  // [0, 65536) and NaN (which converts to 0) is refused explicitly
+  const int k = __double2int_rd(d_mul(ks.res_factor, c));
+  const unsigned u = (unsigned)k + 32768u;
+  if (u >= 65536u || c != c) return false;
+  key = (int)u;
+  return true;
+#else
   double s = floor(d_mul(ks.res_factor, c));
   // out-of-range values (and NaN) must fail without an undefined double->int conversion
   if (!(s >= -32768.0 && s < 32768.0)) return false;
   key = (int)s + 32768;
   return true;
+#endif
 }
 // upstream OcTreeBaseImpl::keyToCoord(key_type): (double(key - 32768) + 0.5) * resolution
 SSPP_HD double key_to_coord(const KeySpace& ks, int key) { return d_mul(d_add((double)(key - 32768), 0.5), ks.res); }

@@ -660,6 +660,66 @@ __device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, doubl
   return true;
 }
 
+// Cheap verdict on one ray before any DDA arithmetic: RAY_FREE / RAY_BLOCKED are final, RAY_WALK
+// means the exact walk has to decide.  `fast` enables the key-box shortcut of line_status_fast.
+enum { RAY_FREE = 0, RAY_BLOCKED = 1, RAY_WALK = 2 };
+__device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float ox, float oy, float oz, float ex, float ey,
+                                            float ez) {
+  int kx, ky, kz, ekx, eky, ekz;
+  if (!coord_to_key(m.ks, (double)ox, kx) || !coord_to_key(m.ks, (double)oy, ky) || !coord_to_key(m.ks, (double)oz, kz) ||
+      !coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
+    return RAY_FREE;  // out of key range: upstream leaves the ray empty
+  if (kx == ekx && ky == eky && kz == ekz) return RAY_FREE;
+  if (fast) {
+    const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
+    const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
+    const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
+    if (!box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) return RAY_FREE;
+  }
+  if (map_blocked(m, kx, ky, kz)) return RAY_BLOCKED;  // the start voxel is the first one the walk tests
+  return RAY_WALK;
+}
+
+constexpr int RAY_TABLE_MAX = 256;
+struct EdgeSmem {
+  RayLattice lat;
+  double ray_off[RAY_TABLE_MAX][3];  // offset of ray q, when the lattice has <= RAY_TABLE_MAX rays
+  int2 sortbuf[EDGE_WARPS][32];
+  double far_end[EDGE_WARPS][32][3];  // far-end coordinates of the batch's pairs
+  int slots[EDGE_WARPS][32];          // batch slots that still need rays, compacted
+  unsigned queue[EDGE_WARPS][64];     // (slot << 20 | ray) waiting for the exact walk
+};
+
+__device__ __forceinline__ void ray_offset(const EdgeSmem& sm, int q, double& ox, double& oy, double& oz) {
+  if (sm.lat.rays <= RAY_TABLE_MAX) {
+    ox = sm.ray_off[q][0]; oy = sm.ray_off[q][1]; oz = sm.ray_off[q][2];
+  } else {
+    const int nyz = sm.lat.n[1] * sm.lat.n[2];
+    int ix = q / nyz, rem = q - ix * nyz;
+    int iy = rem / sm.lat.n[2], iz = rem - iy * sm.lat.n[2];
+    ox = sm.lat.off[0][ix]; oy = sm.lat.off[1][iy]; oz = sm.lat.off[2][iz];
+  }
+}
+
+// Exact walks for the first `count` (<= 32) queue entries of this warp; returns the slots found blocked.
+__device__ __forceinline__ unsigned run_walks(const DeviceMap& m, const EdgeSmem& sm, int warp, int lane, int count,
+                                              unsigned blockedmask, double px, double py, double pz) {
+  unsigned bit = 0;
+  if (lane < count) {
+    const unsigned e = sm.queue[warp][lane];
+    const int k = (int)(e >> 20), q = (int)(e & 0xfffffu);
+    if (!((blockedmask >> k) & 1u)) {
+      double ox, oy, oz;
+      ray_offset(sm, q, ox, oy, oz);
+      const double* f = sm.far_end[warp][k];
+      int st = line_status_exact(m, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
+                                 d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)));
+      if (st != CELL_FREE) bit = 1u << k;
+    }
+  }
+  return __reduce_or_sync(0xffffffffu, bit);
+}
+
 // Edge test, one warp per source row.  Work is shed in stages, none of which can change a result
 // (DESIGN.md §5): (1) rows whose reach is free in the coarse pyramid were flagged by k_count;
 // (2) per pair, one lane each: the key box all its rays stay in holds no blocked voxel -> accepted;
@@ -673,10 +733,19 @@ __global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
 k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
         const uint8_t* __restrict__ row_free, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
         int* __restrict__ deg, unsigned long long* counters) {
-  __shared__ RayLattice lat;
-  __shared__ int2 sortbuf[EDGE_WARPS][32];
+  __shared__ EdgeSmem sm;
+  RayLattice& lat = sm.lat;
   for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
   __syncthreads();
+  if (lat.rays <= RAY_TABLE_MAX) {
+    const int nyz = lat.n[1] * lat.n[2];
+    for (int q = threadIdx.x; q < lat.rays; q += blockDim.x) {
+      int ix = q / nyz, rem = q - ix * nyz;
+      int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
+      sm.ray_off[q][0] = lat.off[0][ix]; sm.ray_off[q][1] = lat.off[1][iy]; sm.ray_off[q][2] = lat.off[2][iz];
+    }
+    __syncthreads();
+  }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * EDGE_WARPS + warp;
@@ -697,9 +766,9 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
     int key = mine.y & 0x7fffffff;
     int rank = 0;
     for (int k = 0; k < n; ++k) rank += ((__shfl_sync(0xffffffffu, mine.y, k) & 0x7fffffff) < key);
-    if (lane < n) sortbuf[warp][rank] = mine;
+    if (lane < n) sm.sortbuf[warp][rank] = mine;
     __syncwarp();
-    if (lane < n) c0 = sortbuf[warp][lane];
+    if (lane < n) c0 = sm.sortbuf[warp][lane];
   } else {
     for (int e = lane; e < n; e += 32) {
       int2 mine = candA[off + e];
@@ -722,14 +791,8 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   }
 
   const double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
-  BlockedGlobal glob_fn;
-  glob_fn.m = &m;
   const int R = lat.rays;
-  const int G = R >= 32 ? 32 : R;      // lanes per pair in the lattice stage
-  const int EPI = 32 / G;              // pairs per warp iteration
-  const int sub = lane / G, lig = lane - sub * G;
-  double o0x, o0y, o0z;
-  lane_offset(lat, lig, o0x, o0y, o0z);
+  const bool fast = a.use_pyramid != 0;
   int nacc = 0;
   unsigned n_box = 0, n_lat = 0;
   unsigned long long nsteps = 0;
@@ -743,7 +806,7 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
     if (mine_valid) { qx = a.sx[c.x]; qy = a.sy[c.x]; qz = a.sz[c.x]; }
     bool needs = mine_valid && !same;
     // stage 2: the pair's key box (one lane per pair)
-    if (!COUNT && a.use_pyramid && needs) {
+    if (!COUNT && fast && needs) {
       int lox, hix, loy, hiy, loz, hiz;
       if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
           pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
@@ -755,31 +818,77 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
     unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs);  // same-position or box-free pairs
     n_box += __popc(accmask & ~__ballot_sync(0xffffffffu, same));
     n_lat += __popc(need);
-    // stages 3-4: the ray lattice for what is left, EPI pairs per iteration
-    while (need) {
-      const int kk = __fns(need, 0, sub + 1);           // sub-th remaining pair (or -1)
-      const bool have = (sub < EPI) && kk >= 0 && kk < 32;
-      const int src = have ? kk : 0;
-      const double ex = __shfl_sync(0xffffffffu, qx, src), ey = __shfl_sync(0xffffffffu, qy, src),
-                   ez = __shfl_sync(0xffffffffu, qz, src);
-      int st;
-      if (COUNT)
-        st = swept_status<true, false>(m, lat, glob_fn, have, G, sub, lig, o0x, o0y, o0z, px, py, pz, ex, ey, ez, &nsteps);
-      else
-        st = swept_status<false, true>(m, lat, glob_fn, have, G, sub, lig, o0x, o0y, o0z, px, py, pz, ex, ey, ez, nullptr,
-                                       a.use_pyramid != 0);
-      // group leaders report; every group clears the pair it took
-      unsigned took = 0, okm = 0;
-      for (int g = 0; g < EPI; ++g) {
-        int kg = __shfl_sync(0xffffffffu, have ? kk : -1, g * G);
-        int sg = __shfl_sync(0xffffffffu, st, g * G);
-        if (kg >= 0) {
-          took |= 1u << kg;
-          if (sg == CELL_FREE) okm |= 1u << kg;
+    if (COUNT) {
+      // instrumented run: every ray through the exact walk, counted with the reference's
+      // sequential semantics (rays in lattice order, stop after the first non-free ray)
+      BlockedGlobal glob_fn;
+      glob_fn.m = &m;
+      const int G = R >= 32 ? 32 : R, EPI = 32 / G;
+      const int sub = lane / G, lig = lane - sub * G;
+      double o0x, o0y, o0z;
+      lane_offset(lat, lig, o0x, o0y, o0z);
+      while (need) {
+        const int kk = __fns(need, 0, sub + 1);
+        const bool have = (sub < EPI) && kk >= 0 && kk < 32;
+        const int src = have ? kk : 0;
+        const double ex = __shfl_sync(0xffffffffu, qx, src), ey = __shfl_sync(0xffffffffu, qy, src),
+                     ez = __shfl_sync(0xffffffffu, qz, src);
+        int st = swept_status<true, false>(m, lat, glob_fn, have, G, sub, lig, o0x, o0y, o0z, px, py, pz, ex, ey, ez, &nsteps);
+        unsigned took = 0, okm = 0;
+        for (int g = 0; g < EPI; ++g) {
+          int kg = __shfl_sync(0xffffffffu, have ? kk : -1, g * G);
+          int sg = __shfl_sync(0xffffffffu, st, g * G);
+          if (kg >= 0) {
+            took |= 1u << kg;
+            if (sg == CELL_FREE) okm |= 1u << kg;
+          }
+        }
+        accmask |= okm;
+        need &= ~took;
+      }
+    } else if (need) {
+      // stages 3-4: all (pair, ray) items of the batch flattened over the lanes.  A cheap verdict per
+      // ray first; rays that need the exact walk are queued and walked 32 at a time, so the warp
+      // stays full whatever the number of rays per pair, and a pair found blocked drops its other rays.
+      if (needs) sm.slots[warp][__popc(need & ((1u << lane) - 1u))] = lane;
+      if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
+      __syncwarp();
+      const int W = __popc(need) * R;
+      unsigned blockedmask = 0;
+      int qn = 0;
+      for (int w0 = 0; w0 < W; w0 += 32) {
+        const int w = w0 + lane;
+        int verdict = RAY_FREE, k = 0, q = 0;
+        if (w < W) {
+          const int p = w / R;
+          q = w - p * R;
+          k = sm.slots[warp][p];
+          if (!((blockedmask >> k) & 1u)) {
+            double ox, oy, oz;
+            ray_offset(sm, q, ox, oy, oz);
+            const double* f = sm.far_end[warp][k];
+            verdict = ray_precheck(m, fast, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
+                                   d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)));
+          }
+        }
+        blockedmask |= __reduce_or_sync(0xffffffffu, verdict == RAY_BLOCKED ? (1u << k) : 0u);
+        const bool push = verdict == RAY_WALK && !((blockedmask >> k) & 1u);
+        const unsigned pb = __ballot_sync(0xffffffffu, push);
+        if (push) sm.queue[warp][qn + __popc(pb & ((1u << lane) - 1u))] = ((unsigned)k << 20) | (unsigned)q;
+        qn += __popc(pb);
+        __syncwarp();
+        if (qn >= 32) {
+          blockedmask |= run_walks(m, sm, warp, lane, 32, blockedmask, px, py, pz);
+          const unsigned moved = (lane + 32 < qn) ? sm.queue[warp][lane + 32] : 0u;
+          __syncwarp();
+          sm.queue[warp][lane] = moved;
+          qn -= 32;
+          __syncwarp();
         }
       }
-      accmask |= okm;
-      need &= ~took;
+      if (qn > 0) blockedmask |= run_walks(m, sm, warp, lane, qn, blockedmask, px, py, pz);
+      __syncwarp();
+      accmask |= need & ~blockedmask;
     }
     if ((accmask >> lane) & 1u) acc[off + nacc + __popc(accmask & ((1u << lane) - 1u))] = c.y & 0x7fffffff;
     nacc += __popc(accmask);
