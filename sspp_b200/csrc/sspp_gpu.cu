@@ -688,6 +688,7 @@ struct EdgeSmem {
   double far_end[EDGE_WARPS][32][3];  // far-end coordinates of the batch's pairs
   int slots[EDGE_WARPS][32];          // batch slots that still need rays, compacted
   unsigned queue[EDGE_WARPS][64];     // (slot << 20 | ray) waiting for the exact walk
+  int okey[EDGE_WARPS][32][3];        // origin keys of the first 32 rays of the row (they do not depend on the pair)
 };
 
 __device__ __forceinline__ void ray_offset(const EdgeSmem& sm, int q, double& ox, double& oy, double& oz) {
@@ -793,6 +794,25 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   const double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
   const int R = lat.rays;
   const bool fast = a.use_pyramid != 0;
+  // Row-level verdicts: every ray starts at p + offset whatever the pair, and the start voxel is the
+  // first one a walk tests.  A ray whose start voxel is blocked therefore rejects every pair of this
+  // row for which that ray is not empty (its end key differs from its start key).
+  unsigned startmask = 0;
+  if (!COUNT && fast && R <= 32) {
+    bool blk = false;
+    if (lane < R) {
+      double ox, oy, oz;
+      ray_offset(sm, lane, ox, oy, oz);
+      int kx, ky, kz;
+      if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
+          coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz)) {
+        sm.okey[warp][lane][0] = kx; sm.okey[warp][lane][1] = ky; sm.okey[warp][lane][2] = kz;
+        blk = map_blocked(m, kx, ky, kz) != 0;
+      }
+    }
+    startmask = __ballot_sync(0xffffffffu, blk);
+    __syncwarp();
+  }
   int nacc = 0;
   unsigned n_box = 0, n_lat = 0;
   unsigned long long nsteps = 0;
@@ -804,8 +824,25 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
     // this lane's pair: coordinates of the far end
     double qx = 0, qy = 0, qz = 0;
     if (mine_valid) { qx = a.sx[c.x]; qy = a.sy[c.x]; qz = a.sz[c.x]; }
+    bool rejected = false;
     bool needs = mine_valid && !same;
-    // stage 2: the pair's key box (one lane per pair)
+    // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
+    if (needs && startmask) {
+      for (unsigned mb = startmask; mb; mb &= mb - 1) {
+        const int q = __ffs(mb) - 1;
+        double ox, oy, oz;
+        ray_offset(sm, q, ox, oy, oz);
+        int ekx, eky, ekz;
+        if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
+            coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
+            (ekx != sm.okey[warp][q][0] || eky != sm.okey[warp][q][1] || ekz != sm.okey[warp][q][2])) {
+          needs = false;
+          rejected = true;
+          break;
+        }
+      }
+    }
+    // stage 2b: the pair's key box (one lane per pair)
     if (!COUNT && fast && needs) {
       int lox, hix, loy, hiy, loz, hiz;
       if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
@@ -815,7 +852,7 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
         needs = false;
     }
     unsigned need = __ballot_sync(0xffffffffu, needs);
-    unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs);  // same-position or box-free pairs
+    unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs && !rejected);  // same-position or box-free pairs
     n_box += __popc(accmask & ~__ballot_sync(0xffffffffu, same));
     n_lat += __popc(need);
     if (COUNT) {
