@@ -76,7 +76,8 @@ struct sspp_gpu_ctx {
 
   // connect scratch + result
   DevBuf bbox, cell_of, cell_start, cell_cursor, sorted_idx, sx, sy, sz, rows, row_flag, row_free;
-  DevBuf cand_count, cand_off, candA, candB, acc, deg, row_ptr, col_idx, counters, scan_tmp, lattice;
+  DevBuf cand_count, cand_off, candA, candB, acc, deg, row_ptr, col_idx, counters, scan_tmp, lattice, work_rows;
+  int sm_count = 148;
   bool has_result = false;
   int64_t res_rows = 0, res_edges = 0;
   cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -477,7 +478,8 @@ struct ConnectArgs {
 };
 
 // counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows, [3] voxel steps (instrumented),
-//           [4] (unused), [5] pairs accepted by their key box, [6] pairs that ran the ray lattice
+//           [4] next work row (edge kernel's ticket), [5] pairs accepted by their key box,
+//           [6] pairs that ran the ray lattice, [7] number of work rows
 //
 // One thread per source row walks the 27 neighbouring cells (9 contiguous ranges of the cell-sorted
 // arrays).  FILL == false: count the in-radius pairs and test the row's reach against the pyramid.
@@ -486,9 +488,11 @@ struct ConnectArgs {
 template <bool FILL>
 __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* __restrict__ cand_count,
                                                uint8_t* __restrict__ row_free, unsigned long long* counters,
-                                               const long long* __restrict__ cand_off, int2* __restrict__ cand) {
+                                               const long long* __restrict__ cand_off, int2* __restrict__ cand,
+                                               int* __restrict__ work_rows) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned long long inr = 0, tested = 0, pyr = 0;
+  bool is_work = false;
   if (t < a.nrows) {
     int s = a.rows ? a.rows[t] : t;
     double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
@@ -518,9 +522,19 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
       if (a.use_map && a.use_pyramid && tst > 0) fr = row_reach_is_free(m, px, py, pz, a.ts.reach) ? 1 : 0;
       row_free[r] = fr;
       inr = cnt; tested = tst; pyr = fr;
+      is_work = a.use_map && !fr && cnt > 0;
     }
   }
   if (!FILL) {
+    // rows that need the edge kernel, appended warp by warp (their order does not matter)
+    const unsigned wb = __ballot_sync(0xffffffffu, is_work);
+    if (wb) {
+      const int lane = threadIdx.x & 31;
+      unsigned long long base = 0;
+      if (lane == 0) base = atomicAdd(counters + 7, (unsigned long long)__popc(wb));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (is_work) work_rows[base + __popc(wb & ((1u << lane) - 1u))] = t;
+    }
     for (int o = 16; o; o >>= 1) {
       inr += __shfl_xor_sync(0xffffffffu, inr, o);
       tested += __shfl_xor_sync(0xffffffffu, tested, o);
@@ -681,10 +695,13 @@ __device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float
 }
 
 constexpr int RAY_TABLE_MAX = 256;
+struct EdgeSmemSort {
+  int2 buf[EDGE_WARPS][32];
+};
 struct EdgeSmem {
   RayLattice lat;
   double ray_off[RAY_TABLE_MAX][3];  // offset of ray q, when the lattice has <= RAY_TABLE_MAX rays
-  int2 sortbuf[EDGE_WARPS][32];
+  EdgeSmemSort sort;
   double far_end[EDGE_WARPS][32][3];  // far-end coordinates of the batch's pairs
   int slots[EDGE_WARPS][32];          // batch slots that still need rays, compacted
   unsigned queue[EDGE_WARPS][64];     // (slot << 20 | ray) waiting for the exact walk
@@ -729,47 +746,20 @@ __device__ __forceinline__ unsigned run_walks(const DeviceMap& m, const EdgeSmem
 #ifndef EDGE_MIN_BLOCKS
 #define EDGE_MIN_BLOCKS 4
 #endif
-template <bool COUNT>
-__global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
-k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
-        const uint8_t* __restrict__ row_free, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
-        int* __restrict__ deg, unsigned long long* counters) {
-  __shared__ EdgeSmem sm;
-  RayLattice& lat = sm.lat;
-  for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
-  __syncthreads();
-  if (lat.rays <= RAY_TABLE_MAX) {
-    const int nyz = lat.n[1] * lat.n[2];
-    for (int q = threadIdx.x; q < lat.rays; q += blockDim.x) {
-      int ix = q / nyz, rem = q - ix * nyz;
-      int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
-      sm.ray_off[q][0] = lat.off[0][ix]; sm.ray_off[q][1] = lat.off[1][iy]; sm.ray_off[q][2] = lat.off[2][iz];
-    }
-    __syncthreads();
-  }
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int t = blockIdx.x * EDGE_WARPS + warp;
-  if (t >= a.nrows) return;
-  const int s = a.rows ? a.rows[t] : t;
-  const int r = (int)(a.sorted_idx[s] - a.lo);
-  const long long off = cand_off[r];
-  const int n = (int)(cand_off[r + 1] - off);
-  if (n == 0) {
-    if (lane == 0) deg[r] = 0;
-    return;
-  }
-
-  // order the pairs by list index (reference adjacency is in list order): rank sort
-  int2 c0 = make_int2(0, 0);  // n <= 32: this lane's pair after sorting
+// order one row's pairs by list index (reference adjacency is in list order): rank sort.
+// n <= 32: returns this lane's pair after sorting (in registers); else sorts candA -> candB in global memory.
+__device__ __forceinline__ int2 sort_row_pairs(EdgeSmemSort& sb, int warp, int lane, const int2* __restrict__ candA,
+                                               int2* candB, long long off, int n) {
+  int2 c0 = make_int2(0, 0);
   if (n <= 32) {
     int2 mine = (lane < n) ? candA[off + lane] : make_int2(0, 0x7fffffff);
     int key = mine.y & 0x7fffffff;
     int rank = 0;
     for (int k = 0; k < n; ++k) rank += ((__shfl_sync(0xffffffffu, mine.y, k) & 0x7fffffff) < key);
-    if (lane < n) sm.sortbuf[warp][rank] = mine;
+    if (lane < n) sb.buf[warp][rank] = mine;
     __syncwarp();
-    if (lane < n) c0 = sm.sortbuf[warp][lane];
+    if (lane < n) c0 = sb.buf[warp][lane];
+    __syncwarp();
   } else {
     for (int e = lane; e < n; e += 32) {
       int2 mine = candA[off + e];
@@ -780,16 +770,47 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
     }
     __syncwarp();
   }
+  return c0;
+}
 
-  if (!a.use_map || row_free[r]) {
-    if (n <= 32) {
-      if (lane < n) acc[off + lane] = c0.y & 0x7fffffff;
-    } else {
-      for (int e = lane; e < n; e += 32) acc[off + e] = candB[off + e].y & 0x7fffffff;
-    }
-    if (lane == 0) deg[r] = n;
+// Rows the edge kernel does not have to look at — no map, reach free in the pyramid, or no pair at
+// all: every pair is an edge.  One warp per row: sort by list index, write.
+__global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long long* __restrict__ cand_off,
+                                                     const uint8_t* __restrict__ row_free, const int2* __restrict__ candA,
+                                                     int2* candB, int* __restrict__ acc, int* __restrict__ deg) {
+  __shared__ EdgeSmemSort sb;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = blockIdx.x * EDGE_WARPS + warp;
+  if (t >= a.nrows) return;
+  const int s = a.rows ? a.rows[t] : t;
+  const int r = (int)(a.sorted_idx[s] - a.lo);
+  const long long off = cand_off[r];
+  const int n = (int)(cand_off[r + 1] - off);
+  if (a.use_map && !row_free[r] && n > 0) return;  // a work row: k_edges writes it
+  if (n == 0) {
+    if (lane == 0) deg[r] = 0;
     return;
   }
+  int2 c0 = sort_row_pairs(sb, warp, lane, candA, candB, off, n);
+  if (n <= 32) {
+    if (lane < n) acc[off + lane] = c0.y & 0x7fffffff;
+  } else {
+    for (int e = lane; e < n; e += 32) acc[off + e] = candB[off + e].y & 0x7fffffff;
+  }
+  if (lane == 0) deg[r] = n;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& m, EdgeSmem& sm, const int warp, const int lane,
+                                         const int t, const long long* __restrict__ cand_off,
+                                         const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
+                                         int* __restrict__ deg, unsigned long long* counters) {
+  const RayLattice& lat = sm.lat;
+  const int s = a.rows ? a.rows[t] : t;
+  const int r = (int)(a.sorted_idx[s] - a.lo);
+  const long long off = cand_off[r];
+  const int n = (int)(cand_off[r + 1] - off);
+  const int2 c0 = sort_row_pairs(sm.sort, warp, lane, candA, candB, off, n);
 
   const double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
   const int R = lat.rays;
@@ -938,6 +959,38 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   if (COUNT) {
     for (int o = 16; o; o >>= 1) nsteps += __shfl_xor_sync(0xffffffffu, nsteps, o);
     if (lane == 0 && nsteps) atomicAdd(counters + 3, nsteps);
+  }
+  __syncwarp();
+}
+
+// Persistent edge kernel: a fixed grid (EDGE_MIN_BLOCKS CTAs per SM); every warp draws the next work
+// row with a ticket, so a row that needs many walks does not hold seven finished warps hostage.
+template <bool COUNT>
+__global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
+k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
+        const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
+        int* __restrict__ deg, unsigned long long* counters) {
+  __shared__ EdgeSmem sm;
+  RayLattice& lat = sm.lat;
+  for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
+  __syncthreads();
+  if (lat.rays <= RAY_TABLE_MAX) {
+    const int nyz = lat.n[1] * lat.n[2];
+    for (int q = threadIdx.x; q < lat.rays; q += blockDim.x) {
+      int ix = q / nyz, rem = q - ix * nyz;
+      int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
+      sm.ray_off[q][0] = lat.off[0][ix]; sm.ray_off[q][1] = lat.off[1][iy]; sm.ray_off[q][2] = lat.off[2][iz];
+    }
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned long long n_work = counters[7];
+  for (;;) {
+    unsigned long long i = 0;
+    if (lane == 0) i = atomicAdd(counters + 4, 1ull);
+    i = __shfl_sync(0xffffffffu, i, 0);
+    if (i >= n_work) break;
+    edge_row<COUNT>(a, m, sm, warp, lane, work_rows[i], cand_off, candA, candB, acc, deg, counters);
   }
 }
 
@@ -1393,6 +1446,8 @@ int sspp_gpu_create(sspp_gpu_ctx** out, int device) {
   for (int i = 0; i < 6; ++i)
     if (cudaEventCreate(&ctx->ev[i]) != cudaSuccess) { delete ctx; return SSPP_ERR_CUDA; }
   memset(&ctx->map, 0, sizeof(ctx->map));
+  if (cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || ctx->sm_count < 1)
+    ctx->sm_count = 148;
   *out = ctx;
   return SSPP_OK;
 }
@@ -1404,7 +1459,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
   DevBuf* bufs[] = {&ctx->occ, &ctx->known, &ctx->blocked, &ctx->cblocked, &ctx->map_stage, &ctx->xyz, &ctx->bbox,
                     &ctx->cell_of, &ctx->cell_start, &ctx->cell_cursor, &ctx->sorted_idx, &ctx->sx, &ctx->sy, &ctx->sz,
                     &ctx->rows, &ctx->row_flag, &ctx->row_free, &ctx->cand_count, &ctx->cand_off, &ctx->candA, &ctx->candB,
-                    &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice,
+                    &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice, &ctx->work_rows,
                     &ctx->q0, &ctx->q1, &ctx->q2, &ctx->q3, &ctx->q4, &ctx->pts, &ctx->vis_cnt, &ctx->vis_ptr,
                     &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters};
   for (DevBuf* b : bufs) b->release();
@@ -1745,8 +1800,10 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->cand_off.reserve((size_t)(nrows + 1) * 8));
   CK(ctx->counters.reserve(8 * 8));
   CK(cudaMemsetAsync(ctx->counters.p, 0, 8 * 8, st));
+  CK(ctx->work_rows.reserve((size_t)nrows * 4));
   k_count<false><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
-                                                      ctx->counters.as<unsigned long long>(), nullptr, nullptr);
+                                                      ctx->counters.as<unsigned long long>(), nullptr, nullptr,
+                                                      ctx->work_rows.as<int>());
   LAUNCHED(ctx);
   {
     int rc = scan_exclusive<long long>(ctx, ctx->cand_count.as<int>(), nrows, ctx->cand_off.as<long long>());
@@ -1771,23 +1828,23 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->acc.reserve((size_t)std::max<long long>(C, 1) * 4));
   CK(ctx->deg.reserve((size_t)nrows * 4));
   k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
-                                                     ctx->candA.as<int2>());
+                                                     ctx->candA.as<int2>(), nullptr);
   LAUNCHED(ctx);
-  {
-    if (!use_map) {
-      // lattice buffer is still read by the kernel prologue
-      int rc = upload_lattice(ctx, lat);
-      if (rc) return rc;
-    }
-    int blocks = ceil_div(nrows, EDGE_WARPS);
+  k_rows_accept<<<ceil_div(nrows, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
+                                                                        ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(),
+                                                                        ctx->candB.as<int2>(), ctx->acc.as<int>(),
+                                                                        ctx->deg.as<int>());
+  LAUNCHED(ctx);
+  if (use_map) {
+    const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
     if (count_steps)
       k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(),
-                                                        ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
+                                                        ctx->work_rows.as<int>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
                                                         ctx->acc.as<int>(), ctx->deg.as<int>(),
                                                         ctx->counters.as<unsigned long long>());
     else
       k_edges<false><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(),
-                                                         ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
+                                                         ctx->work_rows.as<int>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
                                                          ctx->acc.as<int>(), ctx->deg.as<int>(),
                                                          ctx->counters.as<unsigned long long>());
     LAUNCHED(ctx);
