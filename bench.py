@@ -300,29 +300,21 @@ def main():
     steps_total = st_cnt.voxel_steps
 
     # ---- device-resident timing: `value`
-    gather_bufs = {}
+    state = {"buffers": None, "send": None}
 
     def assemble_csr(st):
         """N>1: all-gather the per-rank CSR blocks over NCCL (row counts, then padded column blocks)."""
         if not distributed:
             return
-        cnt = torch.tensor([st.rows, st.edges], dtype=torch.int64, device="cuda")
-        allc = [torch.empty_like(cnt) for _ in range(world)]
-        dist.all_gather(allc, cnt)
-        allc = torch.stack(allc).cpu().numpy()
-        max_e, max_r = int(allc[:, 1].max()), int(allc[:, 0].max())
-        key = (max_e, max_r)
-        if key not in gather_bufs:
-            gather_bufs.clear()
-            gather_bufs[key] = (torch.empty(max_r + 1, dtype=torch.int64, device="cuda"),
-                                torch.empty(max(max_e, 1), dtype=torch.int32, device="cuda"),
-                                torch.empty(world * (max_r + 1), dtype=torch.int64, device="cuda"),
-                                torch.empty(world * max(max_e, 1), dtype=torch.int32, device="cuda"))
-        rp_s, col_s, rp_all, col_all = gather_bufs[key]
-        eng.connect_fetch_device(rp_s.data_ptr(), col_s.data_ptr())
-        dist.all_gather_into_tensor(rp_all, rp_s)
-        dist.all_gather_into_tensor(col_all, col_s)
-        return rp_all, col_all, allc
+        from sspp_b200 import sharded
+        send = state["send"]
+        if send is None or send[0].numel() != st.rows + 1 or send[1].numel() < max(st.edges, 1):
+            send = (torch.empty(st.rows + 1, dtype=torch.int64, device="cuda"),
+                    torch.empty(max(int(st.edges * 1.1), 1), dtype=torch.int32, device="cuda"))
+            state["send"] = send
+        eng.connect_fetch_device(send[0].data_ptr(), send[1].data_ptr())
+        rp_g, col_g, state["buffers"] = sharded.assemble_csr(send[0], send[1][: st.edges], buffers=state["buffers"])
+        return rp_g, col_g
 
     def step_resident():
         st = eng.connect(radius=RADIUS, box=BOX, rows=rows)

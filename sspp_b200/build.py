@@ -51,7 +51,8 @@ def build_host(force=False):
     if not force and _newer(LIB_HOST, deps):
         return LIB_HOST
     cmd = [GXX, "-std=c++17", "-O2", "-frounding-math", "-ffp-contract=off", "-fPIC", "-shared", "-o", LIB_HOST,
-           "-I", os.path.join(HOST, "include"), "-I", os.path.join(REPO, "include")] + srcs + ["-ldl"]
+           "-I", os.path.join(HOST, "include"), "-I", os.path.join(REPO, "include")] + srcs + [
+               "-L", CSRC, "-lsspp_gpu", "-Wl,-rpath," + CSRC, "-Wl,-rpath,$ORIGIN/../csrc"]
     subprocess.run(cmd, check=True)
     return LIB_HOST
 

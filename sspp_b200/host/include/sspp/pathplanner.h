@@ -1,0 +1,49 @@
+// PathPlanner — the graph-build facade (reference include/sspp/pathplanner.h:57-114,
+// src/pathplanner.cpp): regular-grid sampling, node connection, search.  Same entry points and member
+// names; connectNodes() / connectClustersInternalNodes() are batched through the heuristic's
+// connectAll() (one C-ABI call) instead of looping over all ordered pairs on the host.
+#pragma once
+#include <string>
+#include <vector>
+#include "astar.h"
+#include "sensors.h"
+
+namespace SSPP {
+class PathPlanner : public Astar {
+ public:
+  double regGridConRadius;
+  PathPlanner(Robot* rob, double regGridConRadius, int progressDisplayFrequency);
+  PathPlanner(Robot* rob, double regGridConRadius, int progressDisplayFrequency, std::vector<Sensors>& rSensors);
+  ~PathPlanner();
+  void setConRad(double r) { regGridConRadius = r; }
+  void setMultiAgentSupport(bool on) { multiAgentSupport = on; }
+  void freeResources();
+  void freePath();
+  void generateRegularGrid(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize);
+  void generateRegularGrid(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize, float gridRes);
+  void generateRegularGrid(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize, float gridRes,
+                           bool sampleOrientations, float orientationRes = 360, bool samplesFiltering = false,
+                           bool insertSearchSpace = true);
+  void connectNodes();
+  void connectClustersInternalNodes(SearchSpaceNode* space, double connRadius);
+  void disconnectNodes();
+  void blockPath(Node* path);
+  Node* startSearch(Pose startPose);
+  std::vector<geometry_msgs::Point> getConnections();
+  std::vector<geometry_msgs::Point> getSearchSpace();
+  void getRobotSensorPoses(geometry_msgs::PoseArray& robotPoses, std::vector<geometry_msgs::PoseArray>& sensorsPoses);
+  void loadRegularGrid(const char* robotFile, const char* sensor1File, const char* sensor2File);
+  void saveSearchSpace(const char* filename);
+  bool loadSearchSpace(const char* filename);
+
+  std::vector<Sensors> robotSensors;
+  bool sampleOrientations = false, samplesFiltering = false, multiAgentSupport = false, insertSearchSpace = true;
+  float gridResolution = 1.0f;          // float, as in the reference: the double loop variable is stepped by it
+  float orientationResolution = 360.0f;
+  pcl::PointCloud<pcl::PointXYZ> globalCloud;
+  std::vector<pcl::PointCloud<pcl::PointXYZ> > accuracyClusters;
+  geometry_msgs::PoseArray robotFilteredPoses;
+  std::vector<geometry_msgs::PoseArray> sensorsFilteredPoses;
+  std::vector<Node*> paths;
+};
+}  // namespace SSPP
