@@ -346,7 +346,7 @@ def main():
         eng.synchronize()
         wall.append(time.perf_counter() - t0)
         t = eng.connect_timings()
-        kern_ms.append(float(t[3]))
+        kern_ms.append(float(t[5]))
         phase_ms.append([float(x) for x in t])
     barrier()
     launches = eng.launch_count() - launches0
@@ -438,8 +438,8 @@ def main():
                 "bytes_model": "24*C + 4*steps + 4*E + 32*N with C=%d in-radius pairs, steps=%d voxel lookups (counted on the "
                                "device by the instrumented run, reference semantics), E=%d, N=%d" % (C_l, steps_total, E_l, N_l),
                 "l2_read_gbps_measured": l2_gbps, "frac_of_l2": (achieved / l2_gbps) if l2_gbps else None,
-                "phase_ms": {"total": float(ph[0]), "binning": float(ph[1]), "count": float(ph[2]), "edges": float(ph[3]),
-                             "csr": float(ph[4])},
+                "phase_ms": {"total": float(ph[0]), "binning": float(ph[1]), "count": float(ph[2]), "edge_phase": float(ph[3]),
+                             "csr": float(ph[4]), "k_edges": float(ph[5])},
                 "pyramid_rows": int(st.pyramid_rows), "tile_rows": int(st.tile_rows), "box_pairs": int(st.box_pairs),
                 "lattice_pairs": int(st.lattice_pairs)}
 

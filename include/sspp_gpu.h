@@ -200,8 +200,9 @@ int sspp_gpu_visibility_fetch(sspp_gpu_ctx* ctx, int64_t* view_ptr, int32_t* poi
  * denominator north_star asks for ("achievable L2 bandwidth"), not in MEASURED_PEAKS.json. */
 int sspp_gpu_measure_l2_bandwidth(sspp_gpu_ctx* ctx, int64_t bytes, int iters, double* gbps);
 /* Milliseconds the kernels of the last sspp_gpu_connect spent on the stream (CUDA events):
- * [0] total, [1] binning+scan, [2] count, [3] edge test (DDA), [4] CSR compaction. */
-int sspp_gpu_connect_timings(sspp_gpu_ctx* ctx, float ms[5]);
+ * [0] total, [1] binning+scan, [2] count+scan, [3] edge phase (pair fill, accept rows, edge kernel),
+ * [4] CSR scan+compaction, [5] the edge kernel (k_edges) alone, [6..7] reserved. */
+int sspp_gpu_connect_timings(sspp_gpu_ctx* ctx, float ms[8]);
 /* Number of kernels this library has launched on the context since creation. */
 int64_t sspp_gpu_launch_count(const sspp_gpu_ctx* ctx);
 

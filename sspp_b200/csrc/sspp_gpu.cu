@@ -80,8 +80,8 @@ struct sspp_gpu_ctx {
   int sm_count = 148;
   bool has_result = false;
   int64_t res_rows = 0, res_edges = 0;
-  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  float timings[5] = {0, 0, 0, 0, 0};
+  cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  float timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
   // generic query scratch
   DevBuf q0, q1, q2, q3, q4;
@@ -574,12 +574,6 @@ __device__ __forceinline__ bool box_maybe_blocked(const DeviceMap& m, int lox, i
   return any != 0;
 }
 
-// getLineStatus with a shortcut that cannot change its answer: every voxel the DDA can test lies in
-// the key box spanned by the ray's two end keys, grown by ONE voxel beyond the end key on each axis
-// the ray actually moves along (the walk never steps against its direction; on an axis that has
-// reached its end key it can be stepped once more when rounding leaves that axis' tMax just below
-// the length, and never twice because tMax then grows by tDelta >= res).  If that box holds no
-// blocked voxel the ray is free; otherwise the exact walk decides.
 // the exact walk on the blocked plane, kept out of line: it is the rare path of line_status_fast and
 // inlining it would cost the whole edge kernel its occupancy
 __device__ __noinline__ int line_status_exact(const DeviceMap& m, float ox, float oy, float oz, float ex, float ey, float ez) {
@@ -1443,7 +1437,7 @@ int sspp_gpu_create(sspp_gpu_ctx** out, int device) {
   sspp_gpu_ctx* ctx = new sspp_gpu_ctx();
   ctx->device = device;
   if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return SSPP_ERR_CUDA; }
-  for (int i = 0; i < 6; ++i)
+  for (int i = 0; i < 8; ++i)
     if (cudaEventCreate(&ctx->ev[i]) != cudaSuccess) { delete ctx; return SSPP_ERR_CUDA; }
   memset(&ctx->map, 0, sizeof(ctx->map));
   if (cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || ctx->sm_count < 1)
@@ -1463,7 +1457,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
                     &ctx->q0, &ctx->q1, &ctx->q2, &ctx->q3, &ctx->q4, &ctx->pts, &ctx->vis_cnt, &ctx->vis_ptr,
                     &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters};
   for (DevBuf* b : bufs) b->release();
-  for (int i = 0; i < 6; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -1703,7 +1697,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
     ctx->res_rows = nrows;
     ctx->res_edges = 0;
     if (stats) stats->rows = nrows;
-    for (int i = 0; i < 5; ++i) ctx->timings[i] = 0;
+    for (int i = 0; i < 8; ++i) ctx->timings[i] = 0;
     return SSPP_OK;
   }
 
@@ -1835,6 +1829,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
                                                                         ctx->candB.as<int2>(), ctx->acc.as<int>(),
                                                                         ctx->deg.as<int>());
   LAUNCHED(ctx);
+  CK(cudaEventRecord(ctx->ev[5], st));
   if (use_map) {
     const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
     if (count_steps)
@@ -1881,6 +1876,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   cudaEventElapsedTime(&ctx->timings[2], ctx->ev[1], ctx->ev[2]);
   cudaEventElapsedTime(&ctx->timings[3], ctx->ev[2], ctx->ev[3]);
   cudaEventElapsedTime(&ctx->timings[4], ctx->ev[3], ctx->ev[4]);
+  cudaEventElapsedTime(&ctx->timings[5], ctx->ev[5], ctx->ev[3]);
   ctx->has_result = true;
   ctx->res_rows = nrows;
   ctx->res_edges = E;
@@ -1932,9 +1928,9 @@ int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n,
   return sspp_gpu_connect_fetch(ctx, row_ptr, col_idx);
 }
 
-int sspp_gpu_connect_timings(sspp_gpu_ctx* ctx, float ms[5]) {
+int sspp_gpu_connect_timings(sspp_gpu_ctx* ctx, float ms[8]) {
   if (!ctx || !ms) return SSPP_ERR_INVALID;
-  for (int i = 0; i < 5; ++i) ms[i] = ctx->timings[i];
+  for (int i = 0; i < 8; ++i) ms[i] = ctx->timings[i];
   return SSPP_OK;
 }
 

@@ -214,7 +214,7 @@ class Engine:
         return s
 
     def connect_timings(self):
-        t = np.zeros(5, dtype=np.float32)
+        t = np.zeros(8, dtype=np.float32)
         self._ck(self.L.sspp_gpu_connect_timings(self.h, _p(t)))
         return t
 
