@@ -12,9 +12,9 @@ namespace sspp {
 //
 // Voxel (x,y,z) of the window (x = key_x - kmin[0] ...) is bit (x & 31) of 32-bit word
 //     word(xw = x >> 5, y, z) = ((xw * NZ) + z) * NY + y                       ["x-packed, y-fastest"]
-// so that the voxels a warp stages around a node — a box of a few words in x and 10-40 rows in y and
-// z — are runs of consecutive words along y (coalesced), and a DDA step along y or z stays in the
-// same or the next 32-byte sector.  Three planes of that shape:
+// so that the key boxes the edge kernel scans — one or two words in x, a few rows in y and z — are
+// short runs of consecutive words along y, and a DDA step along y or z stays in the same or the
+// next 32-byte sector.  Three planes of that shape:
 //   occ      1 = occupied leaf            (octomap: isNodeOccupied)
 //   known    1 = a leaf exists here       (octomap: search() != NULL)
 //   blocked  occ | (treat_unknown ? ~known : 0)   — what a swept-robot ray stops at
@@ -73,22 +73,6 @@ struct CellStatusFn {
   __device__ __forceinline__ int operator()(int kx, int ky, int kz) const { return map_cell_status(*m, kx, ky, kz); }
 };
 
-// A per-warp copy of the blocked plane around one source node, in shared memory.  It is a cache,
-// not a bound: a key outside it falls through to the global plane, so its size never changes a result.
-struct BlockedTile {
-  const uint32_t* tile;  // [XW][SZ][SY] words, shared memory
-  int xw0, y0, z0;       // window coordinates of tile word (0,0,0)
-  int XW, SY, SZ;
-  const DeviceMap* m;
-  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const {
-    int x = kx - m->kmin[0], y = ky - m->kmin[1], z = kz - m->kmin[2];
-    unsigned tx = (unsigned)((x >> 5) - xw0), ty = (unsigned)(y - y0), tz = (unsigned)(z - z0);
-    if (tx < (unsigned)XW && ty < (unsigned)SY && tz < (unsigned)SZ)
-      return (tile[(tx * SZ + tz) * SY + ty] >> (x & 31)) & 1u;
-    return map_blocked(*m, kx, ky, kz);
-  }
-};
-
 struct BlockedGlobal {
   const DeviceMap* m;
   __device__ __forceinline__ int operator()(int kx, int ky, int kz) const { return map_blocked(*m, kx, ky, kz); }
@@ -97,6 +81,7 @@ struct BlockedGlobal {
 // Uniform grid over the node set for the radius search (cell edge >= radius, so 27 cells suffice).
 struct NodeGrid {
   double min[3];
+  double max[3];  // nodes outside [min, max] are not binned (a shard's window; the whole set otherwise)
   double inv_cell;
   int n[3];  // cells per axis; cell id = (cz * n[1] + cy) * n[0] + cx
 };

@@ -366,10 +366,17 @@ __global__ void k_bbox(const double* __restrict__ xyz, int64_t n, unsigned long 
   }
 }
 
+// Nodes outside [g.min, g.max] (a shard only bins the nodes its rows can reach) get cell -1 and are
+// left out of the sorted arrays.
 __global__ void k_cell_hist(const double* __restrict__ xyz, int64_t n, NodeGrid g, int* __restrict__ cell_of, int* cell_count) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  int cx = grid_cell_axis(g, xyz[3 * i], 0), cy = grid_cell_axis(g, xyz[3 * i + 1], 1), cz = grid_cell_axis(g, xyz[3 * i + 2], 2);
+  const double x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  if (x < g.min[0] || x > g.max[0] || y < g.min[1] || y > g.max[1] || z < g.min[2] || z > g.max[2]) {
+    cell_of[i] = -1;
+    return;
+  }
+  int cx = grid_cell_axis(g, x, 0), cy = grid_cell_axis(g, y, 1), cz = grid_cell_axis(g, z, 2);
   int c = (cz * g.n[1] + cy) * g.n[0] + cx;
   cell_of[i] = c;
   atomicAdd(cell_count + c, 1);
@@ -379,7 +386,7 @@ __global__ void k_cell_scatter(const double* __restrict__ xyz, int64_t n, const 
                                int* __restrict__ sorted_idx, double* __restrict__ sx, double* __restrict__ sy,
                                double* __restrict__ sz) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  if (i >= n || cell_of[i] < 0) return;
   int pos = atomicAdd(cursor + cell_of[i], 1);
   sorted_idx[pos] = (int)i;
   sx[pos] = xyz[3 * i];
@@ -406,9 +413,11 @@ __global__ void k_cell_sort(const int* __restrict__ cell_start, int ncells, int*
 }
 
 // rows of a shard: flag sorted positions whose list index is in [lo, hi)
-__global__ void k_row_flags(const int* __restrict__ sorted_idx, int64_t n, int64_t lo, int64_t hi, int* __restrict__ flag) {
+// n_sorted_ptr: how many nodes were binned (device side); positions beyond it hold nothing
+__global__ void k_row_flags(const int* __restrict__ sorted_idx, int64_t n, const int* __restrict__ n_sorted_ptr, int64_t lo,
+                            int64_t hi, int* __restrict__ flag) {
   int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < n) flag[s] = (sorted_idx[s] >= lo && sorted_idx[s] < hi) ? 1 : 0;
+  if (s < n) flag[s] = (s < *n_sorted_ptr && sorted_idx[s] >= lo && sorted_idx[s] < hi) ? 1 : 0;
 }
 __global__ void k_row_scatter(const int* __restrict__ flag, const int* __restrict__ pos, int64_t n, int* __restrict__ rows) {
   int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -489,7 +498,8 @@ template <bool FILL>
 __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* __restrict__ cand_count,
                                                uint8_t* __restrict__ row_free, unsigned long long* counters,
                                                const long long* __restrict__ cand_off, int2* __restrict__ cand,
-                                               int* __restrict__ work_rows) {
+                                               int* __restrict__ work_rows, long long pair_cap) {
+  if (FILL && cand_off[a.nrows] > pair_cap) return;  // the pair buffers are too small: the host grows them and reruns
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned long long inr = 0, tested = 0, pyr = 0;
   bool is_work = false;
@@ -771,8 +781,9 @@ __device__ __forceinline__ int2 sort_row_pairs(EdgeSmemSort& sb, int warp, int l
 // all: every pair is an edge.  One warp per row: sort by list index, write.
 __global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long long* __restrict__ cand_off,
                                                      const uint8_t* __restrict__ row_free, const int2* __restrict__ candA,
-                                                     int2* candB, int* __restrict__ acc, int* __restrict__ deg) {
+                                                     int2* candB, int* __restrict__ acc, int* __restrict__ deg, long long pair_cap) {
   __shared__ EdgeSmemSort sb;
+  if (cand_off[a.nrows] > pair_cap) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * EDGE_WARPS + warp;
   if (t >= a.nrows) return;
@@ -963,8 +974,9 @@ template <bool COUNT>
 __global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
 k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
         const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
-        int* __restrict__ deg, unsigned long long* counters) {
+        int* __restrict__ deg, unsigned long long* counters, long long pair_cap) {
   __shared__ EdgeSmem sm;
+  if (cand_off[a.nrows] > pair_cap) return;
   RayLattice& lat = sm.lat;
   for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
   __syncthreads();
@@ -991,7 +1003,8 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
 // CSR compaction: one warp per row, coalesced copy of the accepted prefix
 __global__ void k_compact(const long long* __restrict__ cand_off, const int* __restrict__ deg,
                           const long long* __restrict__ row_ptr, const int* __restrict__ acc, int* __restrict__ col,
-                          int nrows) {
+                          int nrows, long long pair_cap) {
+  if (cand_off[nrows] > pair_cap) return;
   int r = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   int lane = threadIdx.x & 31;
   if (r >= nrows) return;
@@ -1215,7 +1228,7 @@ __global__ void k_pts_hist(const float* __restrict__ xyz, int64_t n, PointGrid g
 __global__ void k_pts_scatter(const float* __restrict__ xyz, int64_t n, const int* __restrict__ cell_of, int* cursor,
                               int* __restrict__ sorted_idx, float4* __restrict__ sp) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  if (i >= n || cell_of[i] < 0) return;
   int pos = atomicAdd(cursor + cell_of[i], 1);
   sorted_idx[pos] = (int)i;
   sp[pos] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], __int_as_float((int)i));
@@ -1414,9 +1427,9 @@ int build_lattice(sspp_gpu_ctx* ctx, const double box[3], RayLattice& lat) {
 
 int upload_lattice(sspp_gpu_ctx* ctx, const RayLattice& lat) {
   CK(ctx->lattice.reserve(sizeof(RayLattice)));
+  // `lat` is pageable host memory: the call returns once it has been copied to the driver's staging
+  // buffer, so the caller's stack object may go away afterwards
   CK(cudaMemcpyAsync(ctx->lattice.p, &lat, sizeof(RayLattice), cudaMemcpyHostToDevice, ctx->stream));
-  // the source is a stack object: make sure the copy has been staged before it goes away
-  CK(cudaStreamSynchronize(ctx->stream));
   return SSPP_OK;
 }
 
@@ -1701,26 +1714,46 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
     return SSPP_OK;
   }
 
-  // --- 1. bounding box of the nodes
-  CK(ctx->bbox.reserve(7 * 8));
-  unsigned long long init[7] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
+  // --- 1. bounding box: of all nodes (also the finiteness check) and, for a shard, of its own rows
+  const bool sharded = nrows != n;
+  CK(ctx->bbox.reserve(14 * 8));
+  unsigned long long init[14] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0, ~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
   CK(cudaMemcpyAsync(ctx->bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
   k_bbox<<<std::min(ceil_div(n, 256), 148 * 8), 256, 0, st>>>(ctx->xyz.as<double>(), n, ctx->bbox.as<unsigned long long>());
   LAUNCHED(ctx);
-  unsigned long long hb[7];
+  if (sharded) {
+    k_bbox<<<std::min(ceil_div(nrows, 256), 148 * 8), 256, 0, st>>>(ctx->xyz.as<double>() + 3 * lo, nrows,
+                                                                   ctx->bbox.as<unsigned long long>() + 7);
+    LAUNCHED(ctx);
+  }
+  unsigned long long hb[14];
   CK(cudaMemcpyAsync(hb, ctx->bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   if (hb[6]) return fail(ctx, SSPP_ERR_INVALID, "connect: node coordinates must be finite");
 
-  NodeGrid g;
-  double ext[3];
-  for (int a = 0; a < 3; ++a) { g.min[a] = dec_f64(hb[a]); ext[a] = dec_f64(hb[3 + a]) - g.min[a]; }
   // cell edge slightly above the radius: two nodes within `radius` of each other are then never
   // more than one cell apart, whatever the rounding of the cell index
+  NodeGrid g;
+  double ext[3];
   double cell = std::max(prm->radius, 0.0) * (1.0 + 1e-6);
-  double maxext = std::max(ext[0], std::max(ext[1], ext[2]));
-  if (!(cell > 0.0)) cell = std::max(maxext, 1.0);
-  cell = std::max(cell, maxext * 1e-9);
+  {
+    double full_ext = 0;
+    for (int a = 0; a < 3; ++a) full_ext = std::max(full_ext, dec_f64(hb[3 + a]) - dec_f64(hb[a]));
+    if (!(cell > 0.0)) cell = std::max(full_ext, 1.0);
+    cell = std::max(cell, full_ext * 1e-9);
+  }
+  for (int a = 0; a < 3; ++a) {
+    if (sharded) {
+      // a shard bins only what its rows can reach: its own bounding box grown by one cell (>= radius)
+      const double grow = cell * 1.001;
+      g.min[a] = std::max(dec_f64(hb[a]), dec_f64(hb[7 + a]) - grow);
+      g.max[a] = std::min(dec_f64(hb[3 + a]), dec_f64(hb[10 + a]) + grow);
+    } else {
+      g.min[a] = dec_f64(hb[a]);
+      g.max[a] = dec_f64(hb[3 + a]);
+    }
+    ext[a] = g.max[a] - g.min[a];
+  }
   for (;;) {
     double total = 1;
     for (int a = 0; a < 3; ++a) total *= floor(ext[a] / cell) + 2.0;
@@ -1757,12 +1790,13 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
 
   // rows of this shard, in cell order
   const int* rows = nullptr;
-  if (nrows != n) {
+  if (sharded) {
     CK(ctx->row_flag.reserve((size_t)n * 4));
     CK(ctx->rows.reserve((size_t)(n + 1) * 4 + (size_t)nrows * 4));
     int* pos = ctx->rows.as<int>();
     int* rows_w = pos + (n + 1);
-    k_row_flags<<<ceil_div(n, 256), 256, 0, st>>>(ctx->sorted_idx.as<int>(), n, lo, hi, ctx->row_flag.as<int>());
+    k_row_flags<<<ceil_div(n, 256), 256, 0, st>>>(ctx->sorted_idx.as<int>(), n, ctx->cell_start.as<int>() + ncells, lo, hi,
+                                                 ctx->row_flag.as<int>());
     LAUNCHED(ctx);
     int rc = scan_exclusive<int>(ctx, ctx->row_flag.as<int>(), n, pos);
     if (rc) return rc;
@@ -1795,82 +1829,94 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->counters.reserve(8 * 8));
   CK(cudaMemsetAsync(ctx->counters.p, 0, 8 * 8, st));
   CK(ctx->work_rows.reserve((size_t)nrows * 4));
+  CK(ctx->deg.reserve((size_t)nrows * 4));
   k_count<false><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
                                                       ctx->counters.as<unsigned long long>(), nullptr, nullptr,
-                                                      ctx->work_rows.as<int>());
+                                                      ctx->work_rows.as<int>(), 0);
   LAUNCHED(ctx);
   {
     int rc = scan_exclusive<long long>(ctx, ctx->cand_count.as<int>(), nrows, ctx->cand_off.as<long long>());
     if (rc) return rc;
   }
-  unsigned long long hc[4];
-  long long C = 0;
-  CK(cudaMemcpyAsync(hc, ctx->counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
-  CK(cudaMemcpyAsync(&C, ctx->cand_off.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
   CK(cudaEventRecord(ctx->ev[2], st));
-  CK(cudaStreamSynchronize(st));
+
+  // --- 4/5. edge test and CSR.  The pair buffers keep their size from call to call; the kernels
+  // refuse to run when the pair count exceeds it, which the host sees at the single synchronisation
+  // at the end (it then grows the buffers and repeats this phase).  Only the first call, with no
+  // buffers yet, has to wait for the count here.
+  auto pair_capacity = [&]() -> long long {
+    return (long long)std::min(std::min(ctx->candA.cap / 8, ctx->candB.cap / 8), std::min(ctx->acc.cap / 4, ctx->col_idx.cap / 4));
+  };
+  auto reserve_pairs = [&](long long c) -> cudaError_t {
+    const size_t want = (size_t)std::max<long long>(c + c / 16 + 1024, 1);
+    cudaError_t e;
+    if ((e = ctx->candA.reserve(want * 8)) != cudaSuccess) return e;
+    if ((e = ctx->candB.reserve(want * 8)) != cudaSuccess) return e;
+    if ((e = ctx->acc.reserve(want * 4)) != cudaSuccess) return e;
+    return ctx->col_idx.reserve(want * 4);
+  };
+  long long C = -1;
+  if (pair_capacity() == 0) {
+    CK(cudaMemcpyAsync(&C, ctx->cand_off.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(reserve_pairs(C));
+  }
+  unsigned long long hc[8];
+  long long E = 0;
+  for (int attempt = 0;; ++attempt) {
+    const long long cap = pair_capacity();
+    k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
+                                                       ctx->candA.as<int2>(), nullptr, cap);
+    LAUNCHED(ctx);
+    k_rows_accept<<<ceil_div(nrows, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
+                                                                          ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(),
+                                                                          ctx->candB.as<int2>(), ctx->acc.as<int>(),
+                                                                          ctx->deg.as<int>(), cap);
+    LAUNCHED(ctx);
+    CK(cudaEventRecord(ctx->ev[5], st));
+    if (use_map) {
+      const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
+      if (count_steps)
+        k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
+                                                          ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
+                                                          ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
+                                                          ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap);
+      else
+        k_edges<false><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
+                                                           ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
+                                                           ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
+                                                           ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap);
+      LAUNCHED(ctx);
+    }
+    CK(cudaEventRecord(ctx->ev[3], st));
+    {
+      int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
+      if (rc) return rc;
+    }
+    k_compact<<<ceil_div(nrows * 32, 256), 256, 0, st>>>(ctx->cand_off.as<long long>(), ctx->deg.as<int>(),
+                                                        ctx->row_ptr.as<long long>(), ctx->acc.as<int>(), ctx->col_idx.as<int>(),
+                                                        (int)nrows, cap);
+    LAUNCHED(ctx);
+    CK(cudaEventRecord(ctx->ev[4], st));
+    CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&C, ctx->cand_off.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hc, ctx->counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (C <= cap) break;
+    if (attempt > 0) return fail(ctx, SSPP_ERR_CUDA, "connect: pair buffers still too small after growing them");
+    CK(reserve_pairs(C));
+  }
   if (stats) {
     stats->rows = nrows;
     stats->in_radius_pairs = (int64_t)hc[0];
     stats->tested_pairs = (int64_t)hc[1];
     stats->pyramid_rows = (int64_t)hc[2];
+    stats->voxel_steps = count_steps ? (int64_t)hc[3] : 0;
+    stats->tile_rows = 0;
+    stats->box_pairs = (int64_t)hc[5];
+    stats->lattice_pairs = (int64_t)hc[6];
+    stats->edges = E;
   }
-
-  // --- 4. edge test
-  CK(ctx->candA.reserve((size_t)std::max<long long>(C, 1) * 8));
-  CK(ctx->candB.reserve((size_t)std::max<long long>(C, 1) * 8));
-  CK(ctx->acc.reserve((size_t)std::max<long long>(C, 1) * 4));
-  CK(ctx->deg.reserve((size_t)nrows * 4));
-  k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
-                                                     ctx->candA.as<int2>(), nullptr);
-  LAUNCHED(ctx);
-  k_rows_accept<<<ceil_div(nrows, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
-                                                                        ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(),
-                                                                        ctx->candB.as<int2>(), ctx->acc.as<int>(),
-                                                                        ctx->deg.as<int>());
-  LAUNCHED(ctx);
-  CK(cudaEventRecord(ctx->ev[5], st));
-  if (use_map) {
-    const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
-    if (count_steps)
-      k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(),
-                                                        ctx->work_rows.as<int>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
-                                                        ctx->acc.as<int>(), ctx->deg.as<int>(),
-                                                        ctx->counters.as<unsigned long long>());
-    else
-      k_edges<false><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(),
-                                                         ctx->work_rows.as<int>(), ctx->candA.as<int2>(), ctx->candB.as<int2>(),
-                                                         ctx->acc.as<int>(), ctx->deg.as<int>(),
-                                                         ctx->counters.as<unsigned long long>());
-    LAUNCHED(ctx);
-  }
-  CK(cudaEventRecord(ctx->ev[3], st));
-
-  // --- 5. CSR
-  {
-    int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
-    if (rc) return rc;
-  }
-  long long E = 0;
-  unsigned long long hsteps = 0;
-  CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
-  unsigned long long hstage[4] = {0, 0, 0, 0};  // [3] steps, [4] tile rows, [5] box pairs, [6] lattice pairs
-  CK(cudaMemcpyAsync(hstage, ctx->counters.as<unsigned long long>() + 3, 32, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  hsteps = count_steps ? hstage[0] : 0;
-  if (stats) {
-    stats->voxel_steps = (int64_t)hsteps;
-    stats->tile_rows = (int64_t)hstage[1];
-    stats->box_pairs = (int64_t)hstage[2];
-    stats->lattice_pairs = (int64_t)hstage[3];
-  }
-  CK(ctx->col_idx.reserve((size_t)std::max<long long>(E, 1) * 4));
-  k_compact<<<ceil_div(nrows * 32, 256), 256, 0, st>>>(ctx->cand_off.as<long long>(), ctx->deg.as<int>(),
-                                                      ctx->row_ptr.as<long long>(), ctx->acc.as<int>(), ctx->col_idx.as<int>(),
-                                                      (int)nrows);
-  LAUNCHED(ctx);
-  CK(cudaEventRecord(ctx->ev[4], st));
-  CK(cudaStreamSynchronize(st));
   cudaEventElapsedTime(&ctx->timings[0], ctx->ev[0], ctx->ev[4]);
   cudaEventElapsedTime(&ctx->timings[1], ctx->ev[0], ctx->ev[1]);
   cudaEventElapsedTime(&ctx->timings[2], ctx->ev[1], ctx->ev[2]);
@@ -1880,7 +1926,6 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   ctx->has_result = true;
   ctx->res_rows = nrows;
   ctx->res_edges = E;
-  if (stats) stats->edges = E;
   return SSPP_OK;
 }
 
