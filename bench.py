@@ -266,6 +266,8 @@ def main():
     distributed = world > 1
     if distributed:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL's version banner / warnings go to stdout by default, which must hold exactly one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_gpus = world if distributed else 1
     W = max(args.warmup, 3)
@@ -300,21 +302,15 @@ def main():
     steps_total = st_cnt.voxel_steps
 
     # ---- device-resident timing: `value`
-    state = {"buffers": None, "send": None}
+    assembler = None
+    if distributed:
+        from sspp_b200 import sharded
+        assembler = sharded.GpuCsrAssembler(eng, n, torch.device("cuda", local_rank))
 
     def assemble_csr(st):
-        """N>1: all-gather the per-rank CSR blocks over NCCL (row counts, then padded column blocks)."""
-        if not distributed:
-            return
-        from sspp_b200 import sharded
-        send = state["send"]
-        if send is None or send[0].numel() != st.rows + 1 or send[1].numel() < max(st.edges, 1):
-            send = (torch.empty(st.rows + 1, dtype=torch.int64, device="cuda"),
-                    torch.empty(max(int(st.edges * 1.1), 1), dtype=torch.int32, device="cuda"))
-            state["send"] = send
-        eng.connect_fetch_device(send[0].data_ptr(), send[1].data_ptr())
-        rp_g, col_g, state["buffers"] = sharded.assemble_csr(send[0], send[1][: st.edges], buffers=state["buffers"])
-        return rp_g, col_g
+        """N>1: all-gather the per-rank CSR blocks over NCCL and pack them on the device."""
+        if assembler is not None:
+            return assembler.assemble(st)
 
     def step_resident():
         st = eng.connect(radius=RADIUS, box=BOX, rows=rows)

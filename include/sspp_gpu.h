@@ -124,6 +124,15 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* params, sspp_
 int sspp_gpu_connect_fetch(sspp_gpu_ctx* ctx, int64_t* row_ptr, int32_t* col_idx);
 /* Same, into DEVICE buffers of the caller (e.g. the send buffers of an NCCL all-gather). */
 int sspp_gpu_connect_fetch_device(sspp_gpu_ctx* ctx, int64_t* row_ptr_device, int32_t* col_idx_device);
+/* Multi-GPU assembly (SURVEY.md §8 e): after an all-gather of every rank's padded blocks —
+ * row_ptr blocks of `row_stride` int64 (entry [rows_g] holds the block's edge count) and column blocks
+ * of `col_stride` int32 — rebases and packs them into the whole-graph CSR on the context's stream, no
+ * host round trip.  row_base_device: world+1 first-row indices.  *overflow_device receives the largest
+ * edge count that did not fit `col_stride` (0 = all fitted); the caller then regathers with larger slots.
+ * The concatenation equals what PathPlanner::connectNodes (src/pathplanner.cpp:527-567) builds in one piece. */
+int sspp_gpu_assemble_csr_blocks(sspp_gpu_ctx* ctx, const int64_t* row_ptr_blocks_device, const int32_t* col_blocks_device,
+                                 int world, int64_t row_stride, int64_t col_stride, const int64_t* row_base_device,
+                                 int64_t* row_ptr_out_device, int32_t* col_out_device, int64_t* overflow_device);
 /* Device addresses of the last CSR (valid until the next connect on this context). */
 int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_device, const int32_t** col_idx_device);
 

@@ -73,6 +73,11 @@ struct sspp_gpu_ctx {
   // nodes
   int64_t n_nodes = 0;
   DevBuf xyz;
+  bool bbox_pending = false;          // k_bbox of the current node set has been queued, result not read yet
+  bool bbox_valid = false;
+  unsigned long long bbox_host[7] = {0, 0, 0, 0, 0, 0, 0};
+  int64_t shard_lo = -1, shard_hi = -1;  // row range whose bounding box is cached in shard_bbox_host
+  unsigned long long shard_bbox_host[7] = {0, 0, 0, 0, 0, 0, 0};
 
   // connect scratch + result
   DevBuf bbox, cell_of, cell_start, cell_cursor, sorted_idx, sx, sy, sz, rows, row_flag, row_free;
@@ -1013,6 +1018,30 @@ __global__ void k_compact(const long long* __restrict__ cand_off, const int* __r
   for (int e = lane; e < d; e += 32) col[dst + e] = acc[src + e];
 }
 
+// Multi-GPU CSR assembly: every rank holds the all-gathered, padded blocks of all ranks
+// (row_ptr blocks of stride_r entries whose entry [rows_g] is the block's edge count; column blocks
+// of stride_e entries).  One CTA per block rebases and copies: the whole-graph CSR without a host
+// round trip.  bases[g] = first row of block g; out_row_ptr[total_rows] is written by the last block.
+__global__ void k_assemble_blocks(const long long* __restrict__ rp_all, const int* __restrict__ col_all, int world,
+                                  long long stride_r, long long stride_e, const long long* __restrict__ row_base,
+                                  long long* __restrict__ out_rp, int* __restrict__ out_col, long long* __restrict__ overflow) {
+  const int g = blockIdx.y;
+  const long long rows = row_base[g + 1] - row_base[g];
+  long long ebase = 0;
+  for (int k = 0; k < g; ++k) ebase += rp_all[k * stride_r + (row_base[k + 1] - row_base[k])];
+  const long long* rp = rp_all + g * stride_r;
+  const long long edges = rp[rows];
+  if (edges > stride_e) {  // a block did not fit its slot: tell the host, which regathers with larger slots
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicMax((unsigned long long*)overflow, (unsigned long long)edges);
+    return;
+  }
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  for (long long i = tid; i < rows; i += nth) out_rp[row_base[g] + i] = rp[i] + ebase;
+  if (g == world - 1 && tid == 0) out_rp[row_base[g] + rows] = ebase + edges;
+  const int* col = col_all + g * stride_e;
+  for (long long i = tid; i < edges; i += nth) out_col[ebase + i] = col[i];
+}
+
 // ------------------------------------------------------------------------------------------------
 // batched queries
 // ------------------------------------------------------------------------------------------------
@@ -1650,6 +1679,19 @@ static int set_nodes_impl(sspp_gpu_ctx* ctx, const double* xyz, int64_t n, cudaM
   if (n) CK(cudaMemcpyAsync(ctx->xyz.p, xyz, (size_t)n * 24, kind, ctx->stream));
   ctx->n_nodes = n;
   ctx->has_result = false;
+  // the bounding box (and the finiteness check) of the node set belongs to the node store: queued
+  // here, read by the first connect that needs it
+  ctx->bbox_valid = false;
+  ctx->bbox_pending = false;
+  ctx->shard_lo = ctx->shard_hi = -1;
+  if (n) {
+    CK(ctx->bbox.reserve(14 * 8));
+    static const unsigned long long init[7] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
+    CK(cudaMemcpyAsync(ctx->bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+    k_bbox<<<std::min(ceil_div(n, 256), 148 * 8), 256, 0, ctx->stream>>>(ctx->xyz.as<double>(), n, ctx->bbox.as<unsigned long long>());
+    LAUNCHED(ctx);
+    ctx->bbox_pending = true;
+  }
   return SSPP_OK;
 }
 int sspp_gpu_set_nodes(sspp_gpu_ctx* ctx, const double* xyz, int64_t n) {
@@ -1714,21 +1756,37 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
     return SSPP_OK;
   }
 
-  // --- 1. bounding box: of all nodes (also the finiteness check) and, for a shard, of its own rows
+  // --- 1. bounding box: of all nodes (queued by set_nodes, with the finiteness check) and, for a
+  // shard, of its own rows; both are cached until the node set changes, so a repeated pass over the
+  // same resident nodes does not wait for the host here
   const bool sharded = nrows != n;
-  CK(ctx->bbox.reserve(14 * 8));
-  unsigned long long init[14] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0, ~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
-  CK(cudaMemcpyAsync(ctx->bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
-  k_bbox<<<std::min(ceil_div(n, 256), 148 * 8), 256, 0, st>>>(ctx->xyz.as<double>(), n, ctx->bbox.as<unsigned long long>());
-  LAUNCHED(ctx);
-  if (sharded) {
-    k_bbox<<<std::min(ceil_div(nrows, 256), 148 * 8), 256, 0, st>>>(ctx->xyz.as<double>() + 3 * lo, nrows,
-                                                                   ctx->bbox.as<unsigned long long>() + 7);
-    LAUNCHED(ctx);
+  const bool need_shard_bbox = sharded && !(ctx->shard_lo == lo && ctx->shard_hi == hi);
+  if (!ctx->bbox_valid || need_shard_bbox) {
+    if (!ctx->bbox_valid && !ctx->bbox_pending) return fail(ctx, SSPP_ERR_STATE, "connect: no nodes set");
+    if (need_shard_bbox) {
+      static const unsigned long long init[7] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
+      CK(cudaMemcpyAsync(ctx->bbox.as<unsigned long long>() + 7, init, sizeof(init), cudaMemcpyHostToDevice, st));
+      k_bbox<<<std::min(ceil_div(nrows, 256), 148 * 8), 256, 0, st>>>(ctx->xyz.as<double>() + 3 * lo, nrows,
+                                                                     ctx->bbox.as<unsigned long long>() + 7);
+      LAUNCHED(ctx);
+    }
+    unsigned long long tmp[14];
+    CK(cudaMemcpyAsync(tmp, ctx->bbox.p, sizeof(tmp), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (!ctx->bbox_valid) {
+      memcpy(ctx->bbox_host, tmp, sizeof(ctx->bbox_host));
+      ctx->bbox_valid = true;
+      ctx->bbox_pending = false;
+    }
+    if (need_shard_bbox) {
+      memcpy(ctx->shard_bbox_host, tmp + 7, sizeof(ctx->shard_bbox_host));
+      ctx->shard_lo = lo;
+      ctx->shard_hi = hi;
+    }
   }
   unsigned long long hb[14];
-  CK(cudaMemcpyAsync(hb, ctx->bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
+  memcpy(hb, ctx->bbox_host, sizeof(ctx->bbox_host));
+  memcpy(hb + 7, ctx->shard_bbox_host, sizeof(ctx->shard_bbox_host));
   if (hb[6]) return fail(ctx, SSPP_ERR_INVALID, "connect: node coordinates must be finite");
 
   // cell edge slightly above the radius: two nodes within `radius` of each other are then never
@@ -1950,6 +2008,22 @@ int sspp_gpu_connect_fetch_device(sspp_gpu_ctx* ctx, int64_t* row_ptr_device, in
   if (ctx->res_edges)
     CK(cudaMemcpyAsync(col_idx_device, ctx->col_idx.p, (size_t)ctx->res_edges * 4, cudaMemcpyDeviceToDevice, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
+  return SSPP_OK;
+}
+
+int sspp_gpu_assemble_csr_blocks(sspp_gpu_ctx* ctx, const int64_t* row_ptr_blocks_device, const int32_t* col_blocks_device,
+                                 int world, int64_t row_stride, int64_t col_stride, const int64_t* row_base_device,
+                                 int64_t* row_ptr_out_device, int32_t* col_out_device, int64_t* overflow_device) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (world < 1 || !row_ptr_blocks_device || !col_blocks_device || !row_base_device || !row_ptr_out_device || !col_out_device ||
+      !overflow_device)
+    return fail(ctx, SSPP_ERR_INVALID, "assemble_csr_blocks: null argument");
+  CK(cudaSetDevice(ctx->device));
+  dim3 grid((unsigned)(ctx->sm_count * 2 / world + 1), (unsigned)world);
+  k_assemble_blocks<<<grid, 256, 0, ctx->stream>>>((const long long*)row_ptr_blocks_device, col_blocks_device, world, row_stride,
+                                                   col_stride, (const long long*)row_base_device, (long long*)row_ptr_out_device,
+                                                   col_out_device, (long long*)overflow_device);
+  LAUNCHED(ctx);
   return SSPP_OK;
 }
 

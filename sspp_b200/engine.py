@@ -70,6 +70,7 @@ def load_library():
         "sspp_gpu_connect": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_fetch": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_connect_fetch_device": (ctypes.c_int, [c_vp, c_vp, c_vp]),
+        "sspp_gpu_assemble_csr_blocks": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
         "sspp_gpu_connect_result_device": (ctypes.c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
         "sspp_gpu_connect_nodes_host": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(ConnectParams), c_vp, c_vp,
                                                        c_i64, ctypes.POINTER(ConnectStats)]),
@@ -199,6 +200,11 @@ class Engine:
     def connect_fetch_device(self, row_ptr_dev, col_idx_dev):
         """D2D copy of the last CSR into caller-owned device buffers (raw addresses)."""
         self._ck(self.L.sspp_gpu_connect_fetch_device(self.h, c_vp(row_ptr_dev), c_vp(col_idx_dev)))
+
+    def assemble_csr_blocks(self, rp_blocks, col_blocks, world, row_stride, col_stride, row_base, rp_out, col_out, overflow):
+        """all arguments are raw device addresses (int) except the three integers"""
+        self._ck(self.L.sspp_gpu_assemble_csr_blocks(self.h, c_vp(rp_blocks), c_vp(col_blocks), world, row_stride, col_stride,
+                                                     c_vp(row_base), c_vp(rp_out), c_vp(col_out), c_vp(overflow)))
 
     def connect_result_device(self):
         a, b = c_vp(), c_vp()

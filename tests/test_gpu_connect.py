@@ -236,3 +236,45 @@ def test_voxel_step_count_matches_reference_semantics(eng, orc, res, box):
     assert st.voxel_steps == cnt[2] and st.voxel_steps > 0
     assert st.tested_pairs * st.rays_per_pair >= cnt[3]
     w.close()
+
+
+def test_device_block_assembly(eng, orc):
+    """sspp_gpu_assemble_csr_blocks: padded per-rank blocks (as an all-gather leaves them) are packed into the
+    whole-graph CSR on the device; a slot too small for its block is reported, not truncated"""
+    import torch
+    w = make_map(eng, orc, 0.3, True, n_vox=96, seed=9)
+    nodes = scenes.uniform_nodes(2500, extent=20.0, seed=12)
+    eng.set_nodes(nodes)
+    st = eng.connect(radius=1.7, box=BOX)
+    rp, col = eng.connect_fetch(st)
+    world = 3
+    bounds = [0, 833, 1666, 2500]
+    stride_r = 835
+    blocks = []
+    for lo, hi in zip(bounds[:-1], bounds[1:]):
+        s = eng.connect(radius=1.7, box=BOX, rows=(lo, hi))
+        blocks.append(eng.connect_fetch(s))
+    stride_e = max(len(c) for _, c in blocks) + 7
+    dev = torch.device("cuda", 0)
+    rp_all = torch.zeros(world * stride_r, dtype=torch.int64, device=dev)
+    col_all = torch.full((world * stride_e,), -1, dtype=torch.int32, device=dev)
+    for g, (r, c) in enumerate(blocks):
+        rp_all[g * stride_r: g * stride_r + len(r)] = torch.from_numpy(r).to(dev)
+        col_all[g * stride_e: g * stride_e + len(c)] = torch.from_numpy(c).to(dev)
+    base = torch.tensor(bounds, dtype=torch.int64, device=dev)
+    out_rp = torch.zeros(len(nodes) + 1, dtype=torch.int64, device=dev)
+    out_col = torch.zeros(world * stride_e, dtype=torch.int32, device=dev)
+    over = torch.zeros(1, dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+    eng.assemble_csr_blocks(rp_all.data_ptr(), col_all.data_ptr(), world, stride_r, stride_e, base.data_ptr(), out_rp.data_ptr(),
+                            out_col.data_ptr(), over.data_ptr())
+    eng.synchronize()
+    assert int(over.item()) == 0
+    assert np.array_equal(out_rp.cpu().numpy(), rp) and np.array_equal(out_col.cpu().numpy()[:len(col)], col)
+    # slots one entry too small for the largest block
+    small = max(len(c) for _, c in blocks) - 1
+    eng.assemble_csr_blocks(rp_all.data_ptr(), col_all.data_ptr(), world, stride_r, small, base.data_ptr(), out_rp.data_ptr(),
+                            out_col.data_ptr(), over.data_ptr())
+    eng.synchronize()
+    assert int(over.item()) == small + 1
+    w.close()
