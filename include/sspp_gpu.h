@@ -73,6 +73,26 @@ int sspp_gpu_map_upload_boxes(sspp_gpu_ctx* ctx, const double* centres_xyz, cons
  * setOccupied: every voxel met by a resolution-spaced lattice over the box grown by 0.001. */
 int sspp_gpu_map_set_box(sspp_gpu_ctx* ctx, const double position[3], const double box[3], int occupied);
 
+/* Sensor model of the incremental map update: OctomapParameters of volumetric_mapping (upstream);
+ * the defaults are that library's (0.65, 0.4, 0.12, 0.97, 0.7). */
+typedef struct sspp_sensor_model {
+  double probability_hit, probability_miss, threshold_min, threshold_max, threshold_occupancy;
+} sspp_sensor_model;
+int sspp_gpu_map_set_sensor_model(sspp_gpu_ctx* ctx, const sspp_sensor_model* model);
+
+/* Replaces: OctomapManager::insertPointcloudWithTf (src/reactive_planner_server.cpp:238) after its TF
+ * step, i.e. OctomapWorld::insertPointcloudIntoMapImpl + castRay + updateOccupancy (upstream) for points
+ * already in the world frame: one ray per point from the sensor origin (free cells along it, the end
+ * cell occupied; beyond sensor_max_range only the free part up to the range), a point whose voxel an
+ * earlier point of the same cloud already marked occupied casts no ray, every voxel updated at most
+ * once per cloud (occupied wins), log-odds += hit / miss with clamping.  sensor_max_range < 0 = unlimited.
+ * Keeps a float log-odds grid next to the bit planes (allocated on first use).  Cells outside the
+ * map window are dropped. */
+int sspp_gpu_map_insert_pointcloud(sspp_gpu_ctx* ctx, const float* points_world_xyz, int64_t n,
+                                   const double sensor_origin[3], double sensor_max_range);
+/* Log-odds of every voxel of the window (un-rounded dims, x fastest, then y, then z); NaN = never observed. */
+int sspp_gpu_map_download_logodds(sspp_gpu_ctx* ctx, float* logodds);
+
 /* Dense bit planes over the window given to map_create (its un-rounded dims), x fastest, rows of
  * ceil(dims[0]/32) 32-bit words, then y, then z.  Bit = (word >> (x & 31)) & 1. */
 int sspp_gpu_map_upload_dense(sspp_gpu_ctx* ctx, const uint32_t* occupied_bits, const uint32_t* known_bits);

@@ -29,6 +29,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <set>
 #include <utility>
 #include <vector>
 
@@ -89,6 +90,8 @@ class OcTree {
     occ_prob_thres_log = logodds(0.5);
     clamping_thres_min = logodds(0.1192);
     clamping_thres_max = logodds(0.971);
+    prob_hit_log = logodds(0.7);
+    prob_miss_log = logodds(0.4);
   }
   ~OcTree() { clear(); }
 
@@ -170,6 +173,19 @@ class OcTree {
     OcTreeKey key;
     if (!coordToKeyChecked(p, key)) return NULL;
     return setNodeValue(key, log_odds_value, lazy_eval);
+  }
+
+  // OccupancyOcTreeBase::updateNode(key, occupied, lazy_eval = false): add the hit / miss log-odds
+  // to the leaf (created at 0 when missing; a pruned ancestor is expanded first) and clamp.  The
+  // early-out of upstream (leaf already saturated in the direction of the update) changes nothing.
+  OcTreeNode* updateNode(const OcTreeKey& key, bool occupied) {
+    const float update = occupied ? prob_hit_log : prob_miss_log;
+    const OcTreeNode* leaf = search(key);
+    if (leaf && ((update >= 0 && leaf->value >= clamping_thres_max) || (update <= 0 && leaf->value <= clamping_thres_min)))
+      return const_cast<OcTreeNode*>(leaf);
+    bool createdRoot = false;
+    if (root == NULL) { root = newNode(); createdRoot = true; }
+    return updateNodeRecurs(root, createdRoot, key, 0, update);
   }
 
   // OccupancyOcTreeBase::updateInnerOccupancy(): inner value = max over children.
@@ -350,7 +366,7 @@ class OcTree {
   double resolution_factor;
   unsigned tree_depth;
   unsigned tree_max_val;
-  float occ_prob_thres_log, clamping_thres_min, clamping_thres_max;
+  float occ_prob_thres_log, clamping_thres_min, clamping_thres_max, prob_hit_log, prob_miss_log;
 
  private:
   OcTreeNode* root;
@@ -418,6 +434,29 @@ class OcTree {
       return ret;
     }
     node->value = v;
+    return node;
+  }
+  OcTreeNode* updateNodeRecurs(OcTreeNode* node, bool node_just_created, const OcTreeKey& key, unsigned depth, float update) {
+    bool created_node = false;
+    if (depth < tree_depth) {
+      unsigned pos = computeChildIdx(key, (int)tree_depth - 1 - (int)depth);
+      if (!(node->children && node->children[pos])) {
+        if (!hasChildren(node) && !node_just_created) {
+          expandNode(node);
+        } else {
+          if (!node->children) allocChildren(node);
+          node->children[pos] = newNode();
+          created_node = true;
+        }
+      }
+      OcTreeNode* ret = updateNodeRecurs(node->children[pos], created_node, key, depth + 1, update);
+      if (pruneNode(node)) ret = node; else updateOccupancyChildren(node);
+      return ret;
+    }
+    // updateNodeLogOdds: float add, then clamp
+    node->value = node->value + update;
+    if (node->value < clamping_thres_min) node->value = clamping_thres_min;
+    else if (node->value > clamping_thres_max) node->value = clamping_thres_max;
     return node;
   }
   void updateInnerRecurs(OcTreeNode* n, unsigned depth) {
@@ -492,6 +531,8 @@ class OctomapWorld {
     tree.occ_prob_thres_log = logodds(0.7);    // threshold_occupancy
     tree.clamping_thres_min = logodds(0.12);   // threshold_min
     tree.clamping_thres_max = logodds(0.97);   // threshold_max
+    tree.prob_hit_log = logodds(0.65);         // probability_hit
+    tree.prob_miss_log = logodds(0.4);         // probability_miss
   }
 
   // per-thread counters of voxel lookups / rays issued by getLineStatus (for the byte model)
@@ -606,6 +647,42 @@ class OctomapWorld {
   }
   void setFree(const double pos[3], const double box[3]) { setLogOddsBoundingBox(pos, box, tree.clamping_thres_min); }
   void setOccupied(const double pos[3], const double box[3]) { setLogOddsBoundingBox(pos, box, tree.clamping_thres_max); }
+
+  // OctomapWorld::insertPointcloudIntoMapImpl + castRay + updateOccupancy (max_free_space == 0, the
+  // default), for points ALREADY in the world frame (the TF / pcl::transformPointCloud step of
+  // insertPointcloudWithTf, src/reactive_planner_server.cpp:238, is the caller's).  Batch semantics:
+  // a point whose voxel an EARLIER point of the same cloud already marked occupied casts no ray;
+  // every voxel is updated at most once per cloud, occupied winning over free.
+  void insertPointcloud(const float* pts, long n, const double origin_d[3], double sensor_max_range) {
+    const point3d origin((float)origin_d[0], (float)origin_d[1], (float)origin_d[2]);
+    std::set<uint64_t> free_cells, occupied_cells;
+    std::vector<OcTreeKey> ray;
+    for (long i = 0; i < n; ++i) {
+      const point3d p(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]);
+      OcTreeKey key(tree.coordToKey((double)p(0)), tree.coordToKey((double)p(1)), tree.coordToKey((double)p(2)));
+      if (occupied_cells.find(pack(key)) != occupied_cells.end()) continue;
+      if (sensor_max_range < 0.0 || (p - origin).norm() <= sensor_max_range) {
+        if (tree.computeRayKeys(origin, p, ray))
+          for (size_t k = 0; k < ray.size(); ++k) free_cells.insert(pack(ray[k]));
+        OcTreeKey ek;
+        if (tree.coordToKeyChecked(p, ek)) occupied_cells.insert(pack(ek));
+      } else {
+        point3d dir = (p - origin).normalized();
+        const float r = (float)sensor_max_range;  // Vector3::operator*(float)
+        point3d new_end(origin(0) + dir(0) * r, origin(1) + dir(1) * r, origin(2) + dir(2) * r);
+        if (tree.computeRayKeys(origin, new_end, ray))
+          for (size_t k = 0; k < ray.size(); ++k) free_cells.insert(pack(ray[k]));
+      }
+    }
+    for (std::set<uint64_t>::const_iterator it = occupied_cells.begin(); it != occupied_cells.end(); ++it) {
+      tree.updateNode(unpack(*it), true);
+      free_cells.erase(*it);
+    }
+    for (std::set<uint64_t>::const_iterator it = free_cells.begin(); it != free_cells.end(); ++it) tree.updateNode(unpack(*it), false);
+    tree.updateInnerOccupancy();
+  }
+  static uint64_t pack(const OcTreeKey& k) { return ((uint64_t)k[0] << 32) | ((uint64_t)k[1] << 16) | (uint64_t)k[2]; }
+  static OcTreeKey unpack(uint64_t v) { return OcTreeKey((key_type)(v >> 32), (key_type)((v >> 16) & 0xffff), (key_type)(v & 0xffff)); }
 
   // OctomapWorld::getAllOccupiedBoxes / getAllFreeBoxes: (centre, edge length) per leaf.
   void getAllBoxes(bool occupied_boxes, std::vector<double>& centres, std::vector<double>& sizes) const {

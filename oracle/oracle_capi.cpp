@@ -137,6 +137,23 @@ void orc_world_set_keys(void* w, const int32_t* keys, long n, int occupied) {
   W->tree.updateInnerOccupancy();
 }
 
+// insertPointcloud for world-frame float points (see OctomapWorld::insertPointcloud)
+void orc_world_insert_pointcloud(void* w, const float* pts, long n, const double origin[3], double max_range) {
+  ((OctomapWorld*)w)->insertPointcloud(pts, n, origin, max_range);
+}
+
+// log-odds of every voxel of a key window (NaN where nothing was observed), x fastest
+void orc_world_export_logodds(void* w, const int32_t kmin[3], const int32_t dims[3], float* out) {
+  OctomapWorld* W = (OctomapWorld*)w;
+  size_t i = 0;
+  for (int z = 0; z < dims[2]; ++z)
+    for (int y = 0; y < dims[1]; ++y)
+      for (int x = 0; x < dims[0]; ++x, ++i) {
+        const orc::OcTreeNode* n = W->tree.search(OcTreeKey((orc::key_type)(kmin[0] + x), (orc::key_type)(kmin[1] + y), (orc::key_type)(kmin[2] + z)));
+        out[i] = n ? n->value : std::nanf("");
+      }
+}
+
 void orc_world_prune(void* w) { ((OctomapWorld*)w)->tree.prune(); }
 long orc_world_num_tree_nodes(void* w) { return (long)((OctomapWorld*)w)->tree.size(); }
 

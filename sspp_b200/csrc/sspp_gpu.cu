@@ -69,6 +69,10 @@ struct sspp_gpu_ctx {
   int user_dims[3] = {0, 0, 0};
   size_t map_words = 0, cmap_words = 0;
   DevBuf occ, known, blocked, cblocked, map_stage;
+  // incremental update (point-cloud insertion): float log-odds per voxel, per-cloud flag planes, first-point table
+  DevBuf logodds, scan_free, scan_occ, pc_pts, pc_keys, pc_vals;
+  bool has_logodds = false;
+  float prob_hit_log = 0, prob_miss_log = 0, clamp_min_log = 0, clamp_max_log = 0, occ_thres_log = 0;
 
   // nodes
   int64_t n_nodes = 0;
@@ -255,8 +259,11 @@ __global__ void k_dense_out(const uint32_t* __restrict__ src, int nxw, int ny, i
 }
 
 // one warp per leaf box: rows (y,z) over lanes, x range as word masks
+// L (may be null): the log-odds grid, kept in line with the planes — leaves written here sit at the
+// clamping values, as setFree / setOccupied leave them
 __global__ void k_upload_boxes(DeviceMap m, uint32_t* occ, uint32_t* known, const double* __restrict__ centres,
-                               const double* __restrict__ sizes, const uint8_t* __restrict__ occupied, int64_t n) {
+                               const double* __restrict__ sizes, const uint8_t* __restrict__ occupied, int64_t n, float* L,
+                               float lo_v, float hi_v) {
   int64_t b = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   int lane = threadIdx.x & 31;
   if (b >= n) return;
@@ -284,13 +291,16 @@ __global__ void k_upload_boxes(DeviceMap m, uint32_t* occ, uint32_t* known, cons
       size_t w = map_word(m, xw, y, z);
       atomicOr(known + w, mask);
       if (is_occ) atomicOr(occ + w, mask); else atomicAnd(occ + w, ~mask);
+      if (L)
+        for (uint32_t rest = mask; rest; rest &= rest - 1) L[w * 32 + (__ffs(rest) - 1)] = is_occ ? hi_v : lo_v;
     }
   }
 }
 
 // setFree / setOccupied: explicit per-axis key lists (window coordinates) from the host lattice loop
 __global__ void k_set_box(DeviceMap m, uint32_t* occ, uint32_t* known, const int* __restrict__ kx, int nx,
-                          const int* __restrict__ ky, int ny, const int* __restrict__ kz, int nz, int is_occ) {
+                          const int* __restrict__ ky, int ny, const int* __restrict__ kz, int nz, int is_occ, float* L,
+                          float lo_v, float hi_v) {
   int64_t total = (int64_t)nx * ny * nz;
   for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
     int x = kx[t % nx], y = ky[(t / nx) % ny], z = kz[t / ((int64_t)nx * ny)];
@@ -299,6 +309,7 @@ __global__ void k_set_box(DeviceMap m, uint32_t* occ, uint32_t* known, const int
     uint32_t bit = 1u << (x & 31);
     atomicOr(known + w, bit);
     if (is_occ) atomicOr(occ + w, bit); else atomicAnd(occ + w, ~bit);
+    if (L) L[w * 32 + (x & 31)] = is_occ ? hi_v : lo_v;
   }
 }
 
@@ -328,6 +339,132 @@ __global__ void k_pyramid(DeviceMap m, const uint32_t* __restrict__ blocked, uin
       out |= c << (8 * q);
     }
     cblocked[w] = out;
+  }
+}
+
+// ---- incremental update: point-cloud insertion (OctomapWorld::insertPointcloudIntoMapImpl, upstream) ----
+// log-odds grid: voxel (word w, bit b) -> logodds[w * 32 + b]
+
+__global__ void k_logodds_init(const uint32_t* __restrict__ occ, const uint32_t* __restrict__ known, float* __restrict__ L,
+                               size_t words, float lo, float hi) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < words * 32; i += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t bit = 1u << (i & 31);
+    const size_t w = i >> 5;
+    L[i] = (known[w] & bit) ? ((occ[w] & bit) ? hi : lo) : 0.0f;
+  }
+}
+
+__device__ __forceinline__ unsigned long long pc_hash(unsigned long long k) {
+  k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+  return k;
+}
+// OcTreeBaseImpl::coordToKey (unchecked): the 16-bit truncation of floor(c / res) + 32768
+__device__ __forceinline__ unsigned key_unchecked(const KeySpace& ks, float c) {
+  return ((unsigned)__double2int_rd(d_mul(ks.res_factor, (double)c)) + 32768u) & 0xffffu;
+}
+__device__ __forceinline__ bool pc_in_range(float px, float py, float pz, float ox, float oy, float oz, double max_range) {
+  return max_range < 0.0 || norm3f(f_sub(px, ox), f_sub(py, oy), f_sub(pz, oz)) <= max_range;
+}
+
+// pass 1: first in-range point (cloud order) of every end voxel
+__global__ void k_pc_first(KeySpace ks, const float* __restrict__ pts, int64_t n, float ox, float oy, float oz, double max_range,
+                           unsigned long long* keys, int* vals, unsigned long long mask) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float px = pts[3 * i], py = pts[3 * i + 1], pz = pts[3 * i + 2];
+  if (!pc_in_range(px, py, pz, ox, oy, oz, max_range)) return;
+  int kx, ky, kz;
+  if (!coord_to_key(ks, (double)px, kx) || !coord_to_key(ks, (double)py, ky) || !coord_to_key(ks, (double)pz, kz)) return;
+  const unsigned long long key = ((unsigned long long)kx << 32) | ((unsigned long long)ky << 16) | (unsigned long long)kz;
+  unsigned long long slot = pc_hash(key) & mask;
+  for (;;) {
+    unsigned long long prev = atomicCAS(keys + slot, ~0ull, key);
+    if (prev == ~0ull || prev == key) { atomicMin(vals + slot, (int)i); return; }
+    slot = (slot + 1) & mask;
+  }
+}
+
+struct MarkFree {
+  const DeviceMap* m;
+  uint32_t* plane;
+  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const {
+    int x = kx - m->kmin[0], y = ky - m->kmin[1], z = kz - m->kmin[2];
+    if ((unsigned)x < (unsigned)m->dims[0] && (unsigned)y < (unsigned)m->dims[1] && (unsigned)z < (unsigned)m->dims[2])
+      atomicOr(plane + map_word(*m, x >> 5, y, z), 1u << (x & 31));
+    return 0;
+  }
+};
+
+// pass 2: one ray per point that is not shadowed by an earlier point of its voxel
+__global__ void __launch_bounds__(128) k_pc_cast(DeviceMap m, const float* __restrict__ pts, int64_t n, float ox, float oy, float oz,
+                                                 double max_range, const unsigned long long* __restrict__ keys,
+                                                 const int* __restrict__ vals, unsigned long long mask, uint32_t* scan_free,
+                                                 uint32_t* scan_occ) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float px = pts[3 * i], py = pts[3 * i + 1], pz = pts[3 * i + 2];
+  {
+    // "already in occupied_cells": some earlier in-range point ended in this voxel
+    const unsigned long long key = ((unsigned long long)key_unchecked(m.ks, px) << 32) |
+                                   ((unsigned long long)key_unchecked(m.ks, py) << 16) | (unsigned long long)key_unchecked(m.ks, pz);
+    unsigned long long slot = pc_hash(key) & mask;
+    for (;;) {
+      const unsigned long long k = keys[slot];
+      if (k == ~0ull) break;
+      if (k == key) { if (vals[slot] < (int)i) return; break; }
+      slot = (slot + 1) & mask;
+    }
+  }
+  MarkFree mark;
+  mark.m = &m;
+  mark.plane = scan_free;
+  if (pc_in_range(px, py, pz, ox, oy, oz, max_range)) {
+    line_status(m.ks, ox, oy, oz, px, py, pz, mark);
+    int kx, ky, kz;
+    if (coord_to_key(m.ks, (double)px, kx) && coord_to_key(m.ks, (double)py, ky) && coord_to_key(m.ks, (double)pz, kz)) {
+      mark.plane = scan_occ;
+      mark(kx, ky, kz);
+    }
+  } else {
+    // free space only, up to the range: origin + normalized(p - origin) * (float)range
+    float dx = f_sub(px, ox), dy = f_sub(py, oy), dz = f_sub(pz, oz);
+    const double len = norm3f(dx, dy, dz);
+    if (len > 0) { const float fl = d2f(len); dx = f_div(dx, fl); dy = f_div(dy, fl); dz = f_div(dz, fl); }
+    const float r = d2f(max_range);
+    line_status(m.ks, ox, oy, oz, f_add(ox, f_mul(dx, r)), f_add(oy, f_mul(dy, r)), f_add(oz, f_mul(dz, r)), mark);
+  }
+}
+
+// pass 3: every flagged voxel once — occupied wins over free; add, clamp, re-threshold; clear the flags
+__global__ void k_pc_apply(uint32_t* occ, uint32_t* known, uint32_t* scan_free, uint32_t* scan_occ, float* __restrict__ L,
+                           size_t words, float hit, float miss, float lo, float hi, float thres) {
+  for (size_t w = (size_t)blockIdx.x * blockDim.x + threadIdx.x; w < words; w += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t f = scan_free[w], o = scan_occ[w];
+    uint32_t any = f | o;
+    if (!any) continue;
+    uint32_t ow = occ[w];
+    for (uint32_t rest = any; rest; rest &= rest - 1) {
+      const int b = __ffs(rest) - 1;
+      float v = f_add(L[w * 32 + b], ((o >> b) & 1u) ? hit : miss);
+      if (v < lo) v = lo; else if (v > hi) v = hi;
+      L[w * 32 + b] = v;
+      if (v >= thres) ow |= 1u << b; else ow &= ~(1u << b);
+    }
+    occ[w] = ow;
+    known[w] |= any;
+    scan_free[w] = 0;
+    scan_occ[w] = 0;
+  }
+}
+
+// device (xw,z,y) log-odds -> host x-fastest float grid, NaN where unknown
+__global__ void k_logodds_out(const float* __restrict__ L, const uint32_t* __restrict__ known, int nxw, int ny, int nz,
+                              float* __restrict__ dst, int ux, int uy, int uz) {
+  size_t total = (size_t)ux * uy * uz;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    int x = (int)(i % ux), y = (int)((i / ux) % uy), z = (int)(i / ((size_t)ux * uy));
+    size_t w = ((size_t)(x >> 5) * nz + z) * ny + y;
+    dst[i] = ((known[w] >> (x & 31)) & 1u) ? L[w * 32 + (x & 31)] : __int_as_float(0x7fc00000);
   }
 }
 
@@ -1492,7 +1629,8 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->occ, &ctx->known, &ctx->blocked, &ctx->cblocked, &ctx->map_stage, &ctx->xyz, &ctx->bbox,
+  DevBuf* bufs[] = {&ctx->occ, &ctx->known, &ctx->blocked, &ctx->cblocked, &ctx->map_stage, &ctx->logodds, &ctx->scan_free,
+                    &ctx->scan_occ, &ctx->pc_pts, &ctx->pc_keys, &ctx->pc_vals, &ctx->xyz, &ctx->bbox,
                     &ctx->cell_of, &ctx->cell_start, &ctx->cell_cursor, &ctx->sorted_idx, &ctx->sx, &ctx->sy, &ctx->sz,
                     &ctx->rows, &ctx->row_flag, &ctx->row_free, &ctx->cand_count, &ctx->cand_off, &ctx->candA, &ctx->candB,
                     &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice, &ctx->work_rows,
@@ -1553,6 +1691,7 @@ int sspp_gpu_map_create(sspp_gpu_ctx* ctx, double resolution, const int32_t key_
   m.cblocked = ctx->cblocked.as<uint32_t>();
   ctx->has_map = true;
   ctx->planes_dirty = true;
+  ctx->has_logodds = false;  // a new map starts without a log-odds grid (allocated by the first point cloud)
   return SSPP_OK;
 }
 
@@ -1579,7 +1718,9 @@ int sspp_gpu_map_upload_boxes(sspp_gpu_ctx* ctx, const double* centres, const do
   CK(cudaMemcpyAsync(ctx->q2.p, occupied, (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
   k_upload_boxes<<<ceil_div(n * 32, 256), 256, 0, ctx->stream>>>(ctx->map, ctx->occ.as<uint32_t>(), ctx->known.as<uint32_t>(),
                                                                ctx->q0.as<double>(), ctx->q1.as<double>(),
-                                                               ctx->q2.as<uint8_t>(), n);
+                                                               ctx->q2.as<uint8_t>(), n,
+                                                               ctx->has_logodds ? ctx->logodds.as<float>() : nullptr,
+                                                               ctx->clamp_min_log, ctx->clamp_max_log);
   LAUNCHED(ctx);
   CK(cudaStreamSynchronize(ctx->stream));
   ctx->planes_dirty = true;
@@ -1617,7 +1758,9 @@ int sspp_gpu_map_set_box(sspp_gpu_ctx* ctx, const double position[3], const doub
   int64_t total = (int64_t)nx * ny * nz;
   int blocks = (int)std::min<int64_t>(ceil_div(total, 256), 148 * 16);
   k_set_box<<<blocks, 256, 0, ctx->stream>>>(ctx->map, ctx->occ.as<uint32_t>(), ctx->known.as<uint32_t>(), d, (int)nx, d + nx,
-                                             (int)ny, d + nx + ny, (int)nz, occupied ? 1 : 0);
+                                             (int)ny, d + nx + ny, (int)nz, occupied ? 1 : 0,
+                                             ctx->has_logodds ? ctx->logodds.as<float>() : nullptr, ctx->clamp_min_log,
+                                             ctx->clamp_max_log);
   LAUNCHED(ctx);
   CK(cudaStreamSynchronize(ctx->stream));
   ctx->planes_dirty = true;
@@ -1640,6 +1783,11 @@ int sspp_gpu_map_upload_dense(sspp_gpu_ctx* ctx, const uint32_t* occ_bits, const
     CK(cudaMemcpyAsync(ctx->map_stage.p, src[p], words * 4, cudaMemcpyHostToDevice, ctx->stream));
     k_dense_in<<<148 * 8, 256, 0, ctx->stream>>>(ctx->map_stage.as<uint32_t>(), wpr, ud[1], ud[2], dst[p], m.nxw, m.dims[1],
                                                  m.dims[2], ud[0]);
+    LAUNCHED(ctx);
+  }
+  if (ctx->has_logodds) {  // a full upload replaces the map: the log-odds grid restarts from the new planes
+    k_logodds_init<<<148 * 8, 256, 0, ctx->stream>>>(ctx->occ.as<uint32_t>(), ctx->known.as<uint32_t>(), ctx->logodds.as<float>(),
+                                                     ctx->map_words, ctx->clamp_min_log, ctx->clamp_max_log);
     LAUNCHED(ctx);
   }
   CK(cudaStreamSynchronize(ctx->stream));
@@ -1666,6 +1814,104 @@ int sspp_gpu_map_download_dense(sspp_gpu_ctx* ctx, uint32_t* occ_bits, uint32_t*
     CK(cudaMemcpyAsync(dst[p], ctx->map_stage.p, words * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
   }
+  return SSPP_OK;
+}
+
+// ---- incremental update ----------------------------------------------------------------------
+static float logodds_f(double p) { return (float)log(p / (1 - p)); }  // octomap::logodds
+
+static void default_sensor_model(sspp_gpu_ctx* ctx) {
+  ctx->prob_hit_log = logodds_f(0.65);
+  ctx->prob_miss_log = logodds_f(0.4);
+  ctx->clamp_min_log = logodds_f(0.12);
+  ctx->clamp_max_log = logodds_f(0.97);
+  ctx->occ_thres_log = logodds_f(0.7);
+}
+
+int sspp_gpu_map_set_sensor_model(sspp_gpu_ctx* ctx, const sspp_sensor_model* model) {
+  if (!ctx || !model) return fail(ctx, SSPP_ERR_INVALID, "set_sensor_model: null argument");
+  const double v[5] = {model->probability_hit, model->probability_miss, model->threshold_min, model->threshold_max,
+                       model->threshold_occupancy};
+  for (int i = 0; i < 5; ++i)
+    if (!(v[i] > 0.0 && v[i] < 1.0)) return fail(ctx, SSPP_ERR_INVALID, "set_sensor_model: probabilities must lie in (0,1)");
+  if (ctx->has_logodds) return fail(ctx, SSPP_ERR_STATE, "set_sensor_model: call before the first point cloud is inserted");
+  ctx->prob_hit_log = logodds_f(v[0]);
+  ctx->prob_miss_log = logodds_f(v[1]);
+  ctx->clamp_min_log = logodds_f(v[2]);
+  ctx->clamp_max_log = logodds_f(v[3]);
+  ctx->occ_thres_log = logodds_f(v[4]);
+  return SSPP_OK;
+}
+
+// the log-odds grid appears with the first cloud, seeded from the planes (known-free / occupied voxels
+// sit at the clamping values, as setFree / setOccupied leave them)
+static int ensure_logodds(sspp_gpu_ctx* ctx) {
+  if (ctx->has_logodds) return SSPP_OK;
+  if (ctx->prob_hit_log == 0 && ctx->prob_miss_log == 0) default_sensor_model(ctx);
+  CK(ctx->logodds.reserve(ctx->map_words * 32 * sizeof(float)));
+  CK(ctx->scan_free.reserve(ctx->map_words * 4));
+  CK(ctx->scan_occ.reserve(ctx->map_words * 4));
+  CK(cudaMemsetAsync(ctx->scan_free.p, 0, ctx->map_words * 4, ctx->stream));
+  CK(cudaMemsetAsync(ctx->scan_occ.p, 0, ctx->map_words * 4, ctx->stream));
+  k_logodds_init<<<148 * 8, 256, 0, ctx->stream>>>(ctx->occ.as<uint32_t>(), ctx->known.as<uint32_t>(), ctx->logodds.as<float>(),
+                                                   ctx->map_words, ctx->clamp_min_log, ctx->clamp_max_log);
+  LAUNCHED(ctx);
+  ctx->has_logodds = true;
+  return SSPP_OK;
+}
+
+int sspp_gpu_map_insert_pointcloud(sspp_gpu_ctx* ctx, const float* pts, int64_t n, const double origin[3], double max_range) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!ctx->has_map) return fail(ctx, SSPP_ERR_STATE, "no map");
+  if (n < 0 || !origin || (n > 0 && !pts)) return fail(ctx, SSPP_ERR_INVALID, "insert_pointcloud: null argument");
+  if (n >= (int64_t)0x7fffffff) return fail(ctx, SSPP_ERR_RANGE, "insert_pointcloud: too many points");
+  if (!std::isfinite(origin[0]) || !std::isfinite(origin[1]) || !std::isfinite(origin[2]) || std::isnan(max_range))
+    return fail(ctx, SSPP_ERR_INVALID, "insert_pointcloud: non-finite sensor origin or range");
+  CK(cudaSetDevice(ctx->device));
+  int rc = ensure_logodds(ctx);
+  if (rc) return rc;
+  if (n == 0) return SSPP_OK;
+  cudaStream_t st = ctx->stream;
+  unsigned long long slots = 1024;
+  while (slots < (unsigned long long)n * 2 + 1) slots <<= 1;
+  CK(ctx->pc_pts.reserve((size_t)n * 12));
+  CK(ctx->pc_keys.reserve((size_t)slots * 8));
+  CK(ctx->pc_vals.reserve((size_t)slots * 4));
+  CK(cudaMemcpyAsync(ctx->pc_pts.p, pts, (size_t)n * 12, cudaMemcpyHostToDevice, st));
+  CK(cudaMemsetAsync(ctx->pc_keys.p, 0xff, (size_t)slots * 8, st));
+  CK(cudaMemsetAsync(ctx->pc_vals.p, 0x7f, (size_t)slots * 4, st));
+  const float ox = (float)origin[0], oy = (float)origin[1], oz = (float)origin[2];
+  k_pc_first<<<ceil_div(n, 256), 256, 0, st>>>(ctx->map.ks, ctx->pc_pts.as<float>(), n, ox, oy, oz, max_range,
+                                              ctx->pc_keys.as<unsigned long long>(), ctx->pc_vals.as<int>(), slots - 1);
+  LAUNCHED(ctx);
+  k_pc_cast<<<ceil_div(n, 128), 128, 0, st>>>(ctx->map, ctx->pc_pts.as<float>(), n, ox, oy, oz, max_range,
+                                             ctx->pc_keys.as<unsigned long long>(), ctx->pc_vals.as<int>(), slots - 1,
+                                             ctx->scan_free.as<uint32_t>(), ctx->scan_occ.as<uint32_t>());
+  LAUNCHED(ctx);
+  k_pc_apply<<<148 * 8, 256, 0, st>>>(ctx->occ.as<uint32_t>(), ctx->known.as<uint32_t>(), ctx->scan_free.as<uint32_t>(),
+                                      ctx->scan_occ.as<uint32_t>(), ctx->logodds.as<float>(), ctx->map_words, ctx->prob_hit_log,
+                                      ctx->prob_miss_log, ctx->clamp_min_log, ctx->clamp_max_log, ctx->occ_thres_log);
+  LAUNCHED(ctx);
+  CK(cudaStreamSynchronize(st));  // the host cloud may be reused on return
+  ctx->planes_dirty = true;
+  return SSPP_OK;
+}
+
+int sspp_gpu_map_download_logodds(sspp_gpu_ctx* ctx, float* out) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!ctx->has_map) return fail(ctx, SSPP_ERR_STATE, "no map");
+  if (!out) return fail(ctx, SSPP_ERR_INVALID, "download_logodds: null argument");
+  CK(cudaSetDevice(ctx->device));
+  int rc = ensure_logodds(ctx);
+  if (rc) return rc;
+  const int* ud = ctx->user_dims;
+  size_t total = (size_t)ud[0] * ud[1] * ud[2];
+  CK(ctx->map_stage.reserve(total * 4));
+  k_logodds_out<<<148 * 8, 256, 0, ctx->stream>>>(ctx->logodds.as<float>(), ctx->known.as<uint32_t>(), ctx->map.nxw, ctx->map.dims[1],
+                                                  ctx->map.dims[2], ctx->map_stage.as<float>(), ud[0], ud[1], ud[2]);
+  LAUNCHED(ctx);
+  CK(cudaMemcpyAsync(out, ctx->map_stage.p, total * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
   return SSPP_OK;
 }
 

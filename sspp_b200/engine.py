@@ -37,6 +37,11 @@ class Frustum(ctypes.Structure):
                 ("far_dist", ctypes.c_double)]
 
 
+class SensorModel(ctypes.Structure):
+    _fields_ = [("probability_hit", ctypes.c_double), ("probability_miss", ctypes.c_double), ("threshold_min", ctypes.c_double),
+                ("threshold_max", ctypes.c_double), ("threshold_occupancy", ctypes.c_double)]
+
+
 class VisibilityStats(ctypes.Structure):
     _fields_ = [("visible_pairs", c_i64), ("rays", c_i64)]
 
@@ -65,6 +70,9 @@ def load_library():
         "sspp_gpu_map_set_box": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int]),
         "sspp_gpu_map_upload_dense": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_map_download_dense": (ctypes.c_int, [c_vp, c_vp, c_vp]),
+        "sspp_gpu_map_set_sensor_model": (ctypes.c_int, [c_vp, ctypes.POINTER(SensorModel)]),
+        "sspp_gpu_map_insert_pointcloud": (ctypes.c_int, [c_vp, c_vp, c_i64, c_vp, ctypes.c_double]),
+        "sspp_gpu_map_download_logodds": (ctypes.c_int, [c_vp, c_vp]),
         "sspp_gpu_set_nodes": (ctypes.c_int, [c_vp, c_vp, c_i64]),
         "sspp_gpu_set_nodes_device": (ctypes.c_int, [c_vp, c_vp, c_i64]),
         "sspp_gpu_connect": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), ctypes.POINTER(ConnectStats)]),
@@ -164,6 +172,20 @@ class Engine:
         k = np.zeros((uz, uy, wpr), dtype=np.uint32)
         self._ck(self.L.sspp_gpu_map_download_dense(self.h, _p(o), _p(k)))
         return o, k
+
+    def map_set_sensor_model(self, hit=0.65, miss=0.4, tmin=0.12, tmax=0.97, tocc=0.7):
+        m = SensorModel(hit, miss, tmin, tmax, tocc)
+        self._ck(self.L.sspp_gpu_map_set_sensor_model(self.h, ctypes.byref(m)))
+
+    def map_insert_pointcloud(self, points, origin, max_range=-1.0):
+        a = np.ascontiguousarray(points, dtype=np.float32).reshape(-1, 3)
+        self._ck(self.L.sspp_gpu_map_insert_pointcloud(self.h, _p(a), len(a), _p(_f64(origin)), float(max_range)))
+
+    def map_download_logodds(self):
+        ux, uy, uz = self.user_dims
+        out = np.zeros((uz, uy, ux), dtype=np.float32)
+        self._ck(self.L.sspp_gpu_map_download_logodds(self.h, _p(out)))
+        return out
 
     # ---- nodes / connect
     def set_nodes(self, xyz):

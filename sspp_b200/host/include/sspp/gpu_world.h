@@ -29,6 +29,8 @@ class GpuWorld {
   void insertBoxes(const std::vector<std::pair<std::vector<double>, double> >& boxes, bool occupied);
   void insertBoxes(const double* centres, const double* sizes, const uint8_t* occupied, int64_t n);
   void uploadDense(const uint32_t* occ_bits, const uint32_t* known_bits);
+  // OctomapManager::insertPointcloudWithTf after its TF step: world-frame points, sensor origin, range
+  void insertPointcloud(const float* points_world_xyz, int64_t n, const double sensor_origin[3], double sensor_max_range);
   double getResolution() const { return resolution_; }
   bool hasMap() const { return has_map_; }
 

@@ -43,6 +43,10 @@ void GpuWorld::uploadDense(const uint32_t* occ_bits, const uint32_t* known_bits)
   check(sspp_gpu_map_upload_dense(ctx_, occ_bits, known_bits), "map_upload_dense");
 }
 
+void GpuWorld::insertPointcloud(const float* pts, int64_t n, const double origin[3], double max_range) {
+  check(sspp_gpu_map_insert_pointcloud(ctx_, pts, n, origin, max_range), "map_insert_pointcloud");
+}
+
 GpuWorld::CellStatus GpuWorld::getLineStatusBoundingBox(const double start[3], const double end[3], const double box[3]) {
   uint8_t st = 0;
   check(sspp_gpu_check_segments(ctx_, start, end, 1, box, &st), "check_segments");

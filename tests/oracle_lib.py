@@ -49,6 +49,17 @@ class World:
         k = np.ascontiguousarray(keys, dtype=np.int32).reshape(-1, 3)
         self.L.orc_world_set_keys(self.h, _p(k), len(k), int(bool(occupied)))
 
+    def insert_pointcloud(self, pts, origin, max_range):
+        a = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+        self.L.orc_world_insert_pointcloud(self.h, _p(a), len(a), _p(_f64(origin)), float(max_range))
+
+    def export_logodds(self, key_min, dims):
+        km = np.asarray(key_min, dtype=np.int32)
+        dm = np.asarray(dims, dtype=np.int32)
+        out = np.zeros((int(dm[2]), int(dm[1]), int(dm[0])), dtype=np.float32)
+        self.L.orc_world_export_logodds(self.h, _p(km), _p(dm), _p(out))
+        return out
+
     def prune(self):
         self.L.orc_world_prune(self.h)
 
@@ -209,6 +220,8 @@ class Oracle:
         L.orc_world_set_box.argtypes = [vp, vp, vp, ctypes.c_int]
         L.orc_world_set_keys.argtypes = [vp, vp, lng, ctypes.c_int]
         L.orc_world_prune.argtypes = [vp]
+        L.orc_world_insert_pointcloud.argtypes = [vp, vp, lng, vp, dbl]
+        L.orc_world_export_logodds.argtypes = [vp, vp, vp, vp]
         L.orc_world_num_tree_nodes.restype = lng
         L.orc_world_num_tree_nodes.argtypes = [vp]
         L.orc_world_build_dense.argtypes = [vp, vp, vp, vp, vp, ctypes.c_int]
