@@ -42,7 +42,7 @@ class DistanceHeuristic : public Heuristic {
 
   int64_t lastTestedPairs = 0;
 
- private:
+ protected:
   bool debug;
   bool filterByValidity = false;
   bool useMap = true;

@@ -41,6 +41,11 @@ class Heuristic {
   // xyz: n x 3 positions in list order; row_ptr: n+1; col: filled with list indices.
   virtual bool connectAll(const double* /*xyz*/, int64_t /*n*/, double /*radius*/, int /*position_mode*/,
                           std::vector<int64_t>& /*row_ptr*/, std::vector<int32_t>& /*col*/) { return false; }
+  // calculateHeuristic for all children of one expansion, in the order the search will consume them.
+  // Default: one call per node, exactly what the reference's loop does (src/astar.cpp:318).
+  virtual void calculateHeuristicAll(std::vector<Node*>& nodes) {
+    for (Node* n : nodes) calculateHeuristic(n);
+  }
   // Validity of many poses in one call (isFilteringConditionSatisfied batched); false = not offered.
   virtual bool filterAll(const double* /*xyz*/, int64_t /*n*/, std::vector<uint8_t>& /*valid*/) { return false; }
 };

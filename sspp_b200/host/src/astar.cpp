@@ -108,11 +108,15 @@ Node* Astar::astarSearch(Pose startPose) {
       return path;
     }
     Node* childList = makeChildrenNodes(current);
+    // score all children of this expansion first (one batched call for heuristics that offer it; the
+    // default loops over calculateHeuristic in the same order), then file them as the reference does
+    std::vector<Node*> batch;
+    for (Node* c = childList; c; c = c->next) batch.push_back(c);
+    heuristic->calculateHeuristicAll(batch);
     while (childList) {
       Node* child = childList;
       childList = childList->next;
       child->next = child->prev = nullptr;
-      heuristic->calculateHeuristic(child);
       ++globalcount;
       // note: the child's f is compared with the CURRENT node's f, not with the stored duplicate's (:330-351)
       const bool condition = cost ? (current->f_value <= child->f_value) : (current->f_value >= child->f_value);

@@ -5,6 +5,7 @@
 #include <cstring>
 #include <string>
 
+#include "sspp/coverage_heuristic.h"
 #include "sspp/distance_heuristic.h"
 #include "sspp/pathplanner.h"
 
@@ -15,6 +16,8 @@ struct Handle {
   GpuWorld* world = nullptr;
   bool own_world = false;
   DistanceHeuristic* heuristic = nullptr;
+  CoverageHeuristic* coverage = nullptr;  // == heuristic when the handle was made by sspph_create_coverage
+  std::vector<Sensors> sensors;
   PathPlanner* planner = nullptr;
   std::string err;
 };
@@ -63,6 +66,67 @@ void* sspph_create(double radius, int device) {
   }
   return h;
 }
+// planner with a CoverageHeuristic and one camera (mount pose relative to the robot, frustum)
+void* sspph_create_coverage(double radius, int device, const double mount_xyz[3], const double mount_rpy[3], double hfov,
+                            double vfov, double near_d, double far_d) {
+  Handle* h = new Handle;
+  try {
+    h->world = new GpuWorld(device);
+    h->own_world = true;
+    h->coverage = new CoverageHeuristic(h->world);
+    h->heuristic = h->coverage;
+    float sp[3] = {(float)mount_xyz[0], (float)mount_xyz[1], (float)mount_xyz[2]};
+    float rp[3] = {(float)mount_rpy[0], (float)mount_rpy[1], (float)mount_rpy[2]};
+    h->sensors.push_back(Sensors(hfov, vfov, 0.0, near_d, far_d, 640, 480, sp, rp));
+    h->coverage->setFrustum(h->sensors[0]);
+    h->planner = new PathPlanner(nullptr, radius, -1, h->sensors);
+    h->planner->setHeuristicFucntion(h->heuristic);
+  } catch (const std::exception& e) {
+    h->err = e.what();
+  }
+  return h;
+}
+int sspph_set_model_points(void* p, const float* xyz, int64_t n) {
+  Handle* h = (Handle*)p;
+  if (!h->coverage) { h->err = "not a coverage planner"; return 1; }
+  GUARD(h, h->coverage->setModelPoints(xyz, n));
+}
+void sspph_set_coverage_goal(void* p, double target_pct, double tolerance_pct) {
+  Handle* h = (Handle*)p;
+  if (!h->coverage) return;
+  h->coverage->setCoverageTarget(target_pct);
+  h->coverage->setCoverageTolerance(tolerance_pct);
+}
+// visible model points of way-point `index` (list order); returns the count (idx filled up to cap), -1 on error
+int64_t sspph_visible_from(void* p, int64_t index, int32_t* idx, int64_t cap) {
+  Handle* h = (Handle*)p;
+  try {
+    const std::vector<SearchSpaceNode*>& l = h->planner->flatten();
+    if (!h->coverage || index < 0 || index >= (int64_t)l.size()) return -1;
+    const std::vector<int32_t>& v = h->coverage->visibleFrom(l[(size_t)index]);
+    for (size_t i = 0; i < v.size() && (int64_t)i < cap; ++i) idx[i] = v[i];
+    return (int64_t)v.size();
+  } catch (const std::exception& e) {
+    h->err = e.what();
+    return -1;
+  }
+}
+void sspph_get_sensor_poses(void* p, double* poses) {  // first sensor pose of every way-point, list order
+  Handle* h = (Handle*)p;
+  const std::vector<SearchSpaceNode*>& l = h->planner->flatten();
+  for (size_t i = 0; i < l.size(); ++i) {
+    geometry_msgs::Pose q = l[i]->sensorLocation.poses.empty() ? geometry_msgs::Pose() : l[i]->sensorLocation.poses[0];
+    double* o = poses + 7 * i;
+    o[0] = q.position.x; o[1] = q.position.y; o[2] = q.position.z;
+    o[3] = q.orientation.x; o[4] = q.orientation.y; o[5] = q.orientation.z; o[6] = q.orientation.w;
+  }
+}
+void sspph_coverage_counters(void* p, int64_t out[2]) {
+  Handle* h = (Handle*)p;
+  out[0] = h->coverage ? h->coverage->raysCast : 0;
+  out[1] = h->coverage ? h->coverage->visibilityCalls : 0;
+}
+
 void sspph_destroy(void* p) {
   Handle* h = (Handle*)p;
   delete h->planner;

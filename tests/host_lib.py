@@ -56,6 +56,14 @@ def lib():
         L.sspph_astar.restype = i64
         L.sspph_astar.argtypes = [vp, vp, vp, i64, vp, vp, i64]
         L.sspph_robot2sensor.argtypes = [vp, vp, vp, i64, vp]
+        L.sspph_create_coverage.restype = vp
+        L.sspph_create_coverage.argtypes = [ctypes.c_double, ctypes.c_int, vp, vp] + [ctypes.c_double] * 4
+        L.sspph_set_model_points.argtypes = [vp, vp, i64]
+        L.sspph_set_coverage_goal.argtypes = [vp, ctypes.c_double, ctypes.c_double]
+        L.sspph_visible_from.restype = i64
+        L.sspph_visible_from.argtypes = [vp, i64, vp, i64]
+        L.sspph_get_sensor_poses.argtypes = [vp, vp]
+        L.sspph_coverage_counters.argtypes = [vp, vp]
         _L = L
     return _L
 
@@ -63,9 +71,14 @@ def lib():
 class HostPlanner:
     """PathPlanner + DistanceHeuristic (+ GpuWorld when device >= 0) of the host mirror."""
 
-    def __init__(self, radius, device=-1):
+    def __init__(self, radius, device=-1, coverage=None):
+        """coverage: None, or dict(mount_xyz, mount_rpy, hfov, vfov, near, far) for a CoverageHeuristic planner"""
         self.L = lib()
-        self.h = self.L.sspph_create(radius, device)
+        if coverage is None:
+            self.h = self.L.sspph_create(radius, device)
+        else:
+            self.h = self.L.sspph_create_coverage(radius, device, _p(_f64(coverage["mount_xyz"])), _p(_f64(coverage["mount_rpy"])),
+                                                  coverage["hfov"], coverage["vfov"], coverage["near"], coverage["far"])
         if not self.L.sspph_ok(self.h):
             msg = self.L.sspph_error(self.h).decode()
             self.L.sspph_destroy(self.h)
@@ -99,6 +112,31 @@ class HostPlanner:
 
     def set_goal(self, end_pose, tol):
         self.L.sspph_set_goal(self.h, _p(_f64(end_pose)), tol)
+
+    def set_model_points(self, pts):
+        a = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+        self._ck(self.L.sspph_set_model_points(self.h, _p(a), len(a)))
+
+    def set_coverage_goal(self, target_pct, tol_pct):
+        self.L.sspph_set_coverage_goal(self.h, target_pct, tol_pct)
+
+    def visible_from(self, index, cap=1 << 22):
+        idx = np.zeros(cap, dtype=np.int32)
+        k = self.L.sspph_visible_from(self.h, index, _p(idx), cap)
+        if k < 0:
+            raise HostError(self.L.sspph_error(self.h).decode())
+        return idx[:k].copy()
+
+    def sensor_poses(self):
+        n = self.L.sspph_num_nodes(self.h)
+        P = np.zeros((n, 7))
+        self.L.sspph_get_sensor_poses(self.h, _p(P))
+        return P
+
+    def coverage_counters(self):
+        c = np.zeros(2, dtype=np.int64)
+        self.L.sspph_coverage_counters(self.h, _p(c))
+        return int(c[0]), int(c[1])
 
     def set_filter_by_validity(self, on):
         self.L.sspph_set_filter_by_validity(self.h, int(bool(on)))

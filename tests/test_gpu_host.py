@@ -75,3 +75,45 @@ def test_validity_filtering_in_grid_generation(eng, orc):
     p.close()
     q.close()
     w.close()
+
+
+def test_coverage_heuristic_plans_a_view_path(eng, orc):
+    """CoverageHeuristic (authored; the reference snapshot has no source for it) over the engine's visibility
+    pass: the visible set of every way-point on the path equals the oracle's for its sensor pose; the
+    coverage along the path is the size of the running union; the search stops within tolerance of the target"""
+    from sspp_b200 import scenes
+    res = 0.25
+    km, dm, occ, known = scenes.synthetic_map(n_vox=96, res=res, seed=4, n_boxes=10, n_spheres=8, region=16.0)
+    pts = scenes.surface_points(occ, known, km, dm, res, 30000, seed=45)
+    cam = dict(mount_xyz=[0.1, 0.0, -0.05], mount_rpy=[0.0, 0.3, 0.0], hfov=58.0, vfov=45.0, near=0.7, far=6.0)
+    p = host_lib.HostPlanner(1.6, device=0, coverage=cam)
+    p.map_create(res, km, dm, True)
+    p.map_upload_dense(occ, known)
+    p.set_model_points(pts)
+    p.set_filter_by_validity(True)
+    p.generate_grid([0, 0, 0], [14, 14, 4], 1.5, True, 90.0, filtering=True)
+    poses, _ = p.nodes()
+    assert len(poses) > 100
+    edges, tested = p.connect()
+    assert 0 < edges
+    p.set_coverage_goal(12.0, 0.5)
+    path, created, expanded, order = p.astar([-6, -6, 0, 0, 0, 0, 1])
+    assert len(path) >= 2
+    cov = path[:, 8]
+    assert np.all(np.diff(cov) >= 0) and cov[-1] >= 12.0 - 0.5
+    rays, calls = p.coverage_counters()
+    assert rays > 0 and calls <= expanded + 1   # one batched visibility call per expansion at most
+    # visible sets along the path against the oracle, and coverage = |union| / |model|
+    w = orc.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    sens = p.sensor_poses()
+    union = set()
+    for k in range(len(path)):
+        i = int(np.nonzero(np.all(np.abs(poses - path[k, :7]) < 1e-12, axis=1))[0][0])
+        got = p.visible_from(i)
+        _, want, _, _ = w.visibility(sens[i:i + 1], 58.0, 45.0, 0.7, 6.0, pts)
+        assert np.array_equal(got, want)
+        union |= set(got.tolist())
+        assert abs(cov[k] - 100.0 * len(union) / len(pts)) < 1e-9
+    p.close()
+    w.close()
