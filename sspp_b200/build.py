@@ -31,7 +31,9 @@ def _nvcc():
 
 
 def build_gpu(force=False, verbose=False):
-    srcs = [os.path.join(CSRC, f) for f in ("sspp_gpu.cu", "engine.cuh", "dda_core.cuh")]
+    srcs = [os.path.join(CSRC, f) for f in ("sspp_gpu.cu", "engine.cuh", "dda_core.cuh", "context.cuh", "scan.cuh",
+                                            "map_kernels.cuh", "connect_kernels.cuh", "query_kernels.cuh",
+                                            "visibility_kernels.cuh")]
     srcs.append(os.path.join(REPO, "include", "sspp_gpu.h"))
     if not force and _newer(LIB_GPU, srcs):
         return LIB_GPU

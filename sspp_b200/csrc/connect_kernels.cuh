@@ -1,0 +1,719 @@
+// connect_kernels.cuh — the connectNodes pass: node binning, in-radius pair count / fill, the edge kernel, CSR compaction, multi-GPU block assembly.
+// Part of the single translation unit sspp_gpu.cu (included there, in order); not a stand-alone header.
+#pragma once
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// neighbour search kernels
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long enc_f64(double v) {
+  unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  return (b & 0x8000000000000000ull) ? ~b : (b | 0x8000000000000000ull);
+}
+inline double dec_f64(unsigned long long k) {
+  unsigned long long b = (k & 0x8000000000000000ull) ? (k & 0x7fffffffffffffffull) : ~k;
+  double d;
+  memcpy(&d, &b, 8);
+  return d;
+}
+
+// bbox[0..2] = min (encoded), bbox[3..5] = max (encoded), bbox[6] = count of non-finite coordinates
+__global__ void k_bbox(const double* __restrict__ xyz, int64_t n, unsigned long long* bbox) {
+  unsigned long long mn[3] = {~0ull, ~0ull, ~0ull}, mx[3] = {0, 0, 0};
+  unsigned long long bad = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    for (int a = 0; a < 3; ++a) {
+      double v = xyz[3 * i + a];
+      if (!isfinite(v)) { ++bad; continue; }
+      unsigned long long e = enc_f64(v);
+      mn[a] = min(mn[a], e);
+      mx[a] = max(mx[a], e);
+    }
+  }
+  for (int a = 0; a < 3; ++a) {
+    for (int o = 16; o; o >>= 1) {
+      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  }
+  for (int o = 16; o; o >>= 1) bad += __shfl_xor_sync(0xffffffffu, bad, o);
+  if ((threadIdx.x & 31) == 0) {
+    for (int a = 0; a < 3; ++a) { atomicMin(bbox + a, mn[a]); atomicMax(bbox + 3 + a, mx[a]); }
+    if (bad) atomicAdd(bbox + 6, bad);
+  }
+}
+
+// Nodes outside [g.min, g.max] (a shard only bins the nodes its rows can reach) get cell -1 and are
+// left out of the sorted arrays.
+__global__ void k_cell_hist(const double* __restrict__ xyz, int64_t n, NodeGrid g, int* __restrict__ cell_of, int* cell_count) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  if (x < g.min[0] || x > g.max[0] || y < g.min[1] || y > g.max[1] || z < g.min[2] || z > g.max[2]) {
+    cell_of[i] = -1;
+    return;
+  }
+  int cx = grid_cell_axis(g, x, 0), cy = grid_cell_axis(g, y, 1), cz = grid_cell_axis(g, z, 2);
+  int c = (cz * g.n[1] + cy) * g.n[0] + cx;
+  cell_of[i] = c;
+  atomicAdd(cell_count + c, 1);
+}
+
+__global__ void k_cell_scatter(const double* __restrict__ xyz, int64_t n, const int* __restrict__ cell_of, int* cursor,
+                               int* __restrict__ sorted_idx, double* __restrict__ sx, double* __restrict__ sy,
+                               double* __restrict__ sz) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || cell_of[i] < 0) return;
+  int pos = atomicAdd(cursor + cell_of[i], 1);
+  sorted_idx[pos] = (int)i;
+  sx[pos] = xyz[3 * i];
+  sy[pos] = xyz[3 * i + 1];
+  sz[pos] = xyz[3 * i + 2];
+}
+
+// Order the members of every cell by list index, so the whole pipeline is run-to-run deterministic
+// (the scatter above lands them in atomic order).  Cells hold a handful of nodes: insertion sort.
+__global__ void k_cell_sort(const int* __restrict__ cell_start, int ncells, int* sorted_idx, double* sx, double* sy, double* sz) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncells) return;
+  int b = cell_start[c], e = cell_start[c + 1];
+  for (int i = b + 1; i < e; ++i) {
+    int k = sorted_idx[i];
+    double x = sx[i], y = sy[i], z = sz[i];
+    int j = i - 1;
+    while (j >= b && sorted_idx[j] > k) {
+      sorted_idx[j + 1] = sorted_idx[j]; sx[j + 1] = sx[j]; sy[j + 1] = sy[j]; sz[j + 1] = sz[j];
+      --j;
+    }
+    sorted_idx[j + 1] = k; sx[j + 1] = x; sy[j + 1] = y; sz[j + 1] = z;
+  }
+}
+
+// rows of a shard: flag sorted positions whose list index is in [lo, hi)
+// n_sorted_ptr: how many nodes were binned (device side); positions beyond it hold nothing
+__global__ void k_row_flags(const int* __restrict__ sorted_idx, int64_t n, const int* __restrict__ n_sorted_ptr, int64_t lo,
+                            int64_t hi, int* __restrict__ flag) {
+  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n) flag[s] = (s < *n_sorted_ptr && sorted_idx[s] >= lo && sorted_idx[s] < hi) ? 1 : 0;
+}
+__global__ void k_row_scatter(const int* __restrict__ flag, const int* __restrict__ pos, int64_t n, int* __restrict__ rows) {
+  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s < n && flag[s]) rows[pos[s]] = (int)s;
+}
+
+// pair classification shared by count and gather: 0 = not connected, 1 = goes to the collision test,
+// 2 = same position (connected without a test).  S = candidate, T = source row ("temp").
+// The reference tests sqrt(d2) <= radius (Dist, include/sspp/utils.h:356-359).  sqrt is monotone and
+// correctly rounded, so that is the same predicate as d2 <= r2max with r2max = the largest double
+// whose square root does not exceed the radius — computed once on the host (radius_threshold()).
+__device__ __forceinline__ int pair_class(double sx, double sy, double sz, double tx, double ty, double tz, double r2max,
+                                          int mode) {
+  double dx = d_sub(sx, tx), dy = d_sub(sy, ty), dz = d_sub(sz, tz);
+  double d2 = d_add(d_add(d_mul(dx, dx), d_mul(dy, dy)), d_mul(dz, dz));
+  if (!(d2 <= r2max)) return 0;
+  bool differs;
+  if (mode == 0) differs = (sx != tx || sy != ty || sz != tz);
+  else differs = !(fabs(dx) < 1E-12 && fabs(dy) < 1E-12 && fabs(dz) < 1E-12);
+  return differs ? 1 : 2;
+}
+
+// Is the whole reach of a row free at the coarse level?  Region = keys of (p -+ reach) grown by two
+// voxels; every voxel a ray of this row can visit lies inside it (DESIGN.md "pyramid skip").
+__device__ bool row_reach_is_free(const DeviceMap& m, double px, double py, double pz, const double reach[3]) {
+  double p[3] = {px, py, pz};
+  int lo[3], hi[3];
+  for (int a = 0; a < 3; ++a) {
+    int k0, k1;
+    if (!coord_to_key(m.ks, p[a] - reach[a], k0) || !coord_to_key(m.ks, p[a] + reach[a], k1)) return false;
+    lo[a] = k0 - 2 - m.kmin[a];
+    hi[a] = k1 + 2 - m.kmin[a];
+    if (lo[a] < 0 || hi[a] >= m.dims[a]) {
+      if (m.treat_unknown) return false;  // outside the window = never observed = blocked
+      lo[a] = max(lo[a], 0);
+      hi[a] = min(hi[a], m.dims[a] - 1);
+      if (lo[a] > hi[a]) return true;  // nothing of the reach is inside the window, and unknown is free
+    }
+    lo[a] >>= 2;
+    hi[a] >>= 2;
+  }
+  for (int cz = lo[2]; cz <= hi[2]; ++cz)
+    for (int cy = lo[1]; cy <= hi[1]; ++cy)
+      for (int cxw = lo[0] >> 5; cxw <= (hi[0] >> 5); ++cxw) {
+        int b0 = max(lo[0], cxw * 32) & 31, b1 = min(hi[0], cxw * 32 + 31) & 31;
+        uint32_t mask = (b1 == 31 ? 0xffffffffu : ((1u << (b1 + 1)) - 1u)) & ~((1u << b0) - 1u);
+        if (__ldg(m.cblocked + ((size_t)cxw * m.cdims[2] + cz) * m.cdims[1] + cy) & mask) return false;
+      }
+  return true;
+}
+
+struct ConnectArgs {
+  NodeGrid g;
+  const int* cell_start;
+  const int* sorted_idx;
+  const double* sx;
+  const double* sy;
+  const double* sz;
+  const int* rows;  // sorted positions of the rows to process, or NULL = all
+  int nrows;
+  int64_t lo;  // first list index of this shard
+  double r2max;  // largest d2 with sqrt(d2) <= radius
+  int mode;
+  int use_map;
+  int use_pyramid;
+  TileShape ts;
+};
+
+// counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows, [3] voxel steps (instrumented),
+//           [4] next work row (edge kernel's ticket), [5] pairs accepted by their key box,
+//           [6] pairs that ran the ray lattice, [7] number of work rows
+//
+// One thread per source row walks the 27 neighbouring cells (9 contiguous ranges of the cell-sorted
+// arrays).  FILL == false: count the in-radius pairs and test the row's reach against the pyramid.
+// FILL == true (after the scan of the counts): write the pairs — (sorted position, list index with
+// bit 31 = same position) — to cand[], in cell order; the edge kernel orders them by list index.
+template <bool FILL>
+__global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* __restrict__ cand_count,
+                                               uint8_t* __restrict__ row_free, unsigned long long* counters,
+                                               const long long* __restrict__ cand_off, int2* __restrict__ cand,
+                                               int* __restrict__ work_rows, long long pair_cap) {
+  if (FILL && cand_off[a.nrows] > pair_cap) return;  // the pair buffers are too small: the host grows them and reruns
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long inr = 0, tested = 0, pyr = 0;
+  bool is_work = false;
+  if (t < a.nrows) {
+    int s = a.rows ? a.rows[t] : t;
+    double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
+    int r = (int)(a.sorted_idx[s] - a.lo);
+    int cx = grid_cell_axis(a.g, px, 0), cy = grid_cell_axis(a.g, py, 1), cz = grid_cell_axis(a.g, pz, 2);
+    int x0 = max(cx - 1, 0), x1 = min(cx + 1, a.g.n[0] - 1);
+    int cnt = 0, tst = 0;
+    long long w = FILL ? cand_off[r] : 0;
+    for (int zz = max(cz - 1, 0); zz <= min(cz + 1, a.g.n[2] - 1); ++zz)
+      for (int yy = max(cy - 1, 0); yy <= min(cy + 1, a.g.n[1] - 1); ++yy) {
+        int base = (zz * a.g.n[1] + yy) * a.g.n[0];
+        int b = a.cell_start[base + x0], e = a.cell_start[base + x1 + 1];
+        for (int j = b; j < e; ++j) {
+          if (j == s) continue;
+          int pc = pair_class(a.sx[j], a.sy[j], a.sz[j], px, py, pz, a.r2max, a.mode);
+          if (FILL) {
+            if (pc) cand[w++] = make_int2(j, a.sorted_idx[j] | (pc == 2 ? (int)0x80000000 : 0));
+          } else {
+            cnt += (pc != 0);
+            tst += (pc == 1);
+          }
+        }
+      }
+    if (!FILL) {
+      cand_count[r] = cnt;
+      uint8_t fr = 0;
+      if (a.use_map && a.use_pyramid && tst > 0) fr = row_reach_is_free(m, px, py, pz, a.ts.reach) ? 1 : 0;
+      row_free[r] = fr;
+      inr = cnt; tested = tst; pyr = fr;
+      is_work = a.use_map && !fr && cnt > 0;
+    }
+  }
+  if (!FILL) {
+    // rows that need the edge kernel, appended warp by warp (their order does not matter)
+    const unsigned wb = __ballot_sync(0xffffffffu, is_work);
+    if (wb) {
+      const int lane = threadIdx.x & 31;
+      unsigned long long base = 0;
+      if (lane == 0) base = atomicAdd(counters + 7, (unsigned long long)__popc(wb));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (is_work) work_rows[base + __popc(wb & ((1u << lane) - 1u))] = t;
+    }
+    for (int o = 16; o; o >>= 1) {
+      inr += __shfl_xor_sync(0xffffffffu, inr, o);
+      tested += __shfl_xor_sync(0xffffffffu, tested, o);
+      pyr += __shfl_xor_sync(0xffffffffu, pyr, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+      if (inr) atomicAdd(counters + 0, inr);
+      if (tested) atomicAdd(counters + 1, tested);
+      if (pyr) atomicAdd(counters + 2, pyr);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// edge test: one warp per source row
+// ------------------------------------------------------------------------------------------------
+constexpr int EDGE_WARPS = 8;
+
+// Does the key box [lo, hi] (absolute keys, inclusive) hold a blocked voxel?  "true" may also mean
+// "cannot tell cheaply" (the box leaves the mapped window): callers then take the exact path.
+__device__ __forceinline__ bool box_maybe_blocked(const DeviceMap& m, int lox, int hix, int loy, int hiy, int loz, int hiz) {
+  const int x0 = lox - m.kmin[0], x1 = hix - m.kmin[0];
+  const int y0 = loy - m.kmin[1], y1 = hiy - m.kmin[1];
+  const int z0 = loz - m.kmin[2], z1 = hiz - m.kmin[2];
+  if (x0 < 0 || y0 < 0 || z0 < 0 || x1 >= m.dims[0] || y1 >= m.dims[1] || z1 >= m.dims[2] || x0 > x1 || y0 > y1 || z0 > z1)
+    return true;
+  const int w0 = x0 >> 5, w1 = x1 >> 5;
+  uint32_t any = 0;
+  for (int w = w0; w <= w1; ++w) {
+    const int b0 = (w == w0) ? (x0 & 31) : 0, b1 = (w == w1) ? (x1 & 31) : 31;
+    const uint32_t mask = (b1 == 31 ? 0xffffffffu : ((1u << (b1 + 1)) - 1u)) & ~((1u << b0) - 1u);
+    for (int z = z0; z <= z1; ++z) {
+      const uint32_t* row = m.blocked + map_word(m, w, 0, z);
+      for (int y = y0; y <= y1; ++y) any |= __ldg(row + y) & mask;
+    }
+  }
+  return any != 0;
+}
+
+// the exact walk on the blocked plane, kept out of line: it is the rare path of line_status_fast and
+// inlining it would cost the whole edge kernel its occupancy
+__device__ __noinline__ int line_status_exact(const DeviceMap& m, float ox, float oy, float oz, float ex, float ey, float ez) {
+  BlockedGlobal cell;
+  cell.m = &m;
+  return line_status(m.ks, ox, oy, oz, ex, ey, ez, cell);
+}
+
+__device__ __forceinline__ int line_status_fast(const DeviceMap& m, float ox, float oy, float oz, float ex, float ey, float ez) {
+  int kx, ky, kz, ekx, eky, ekz;
+  if (!coord_to_key(m.ks, (double)ox, kx) || !coord_to_key(m.ks, (double)oy, ky) || !coord_to_key(m.ks, (double)oz, kz) ||
+      !coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
+    return CELL_FREE;
+  if (kx == ekx && ky == eky && kz == ekz) return CELL_FREE;
+  const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
+  const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
+  const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
+  if (!box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) return CELL_FREE;
+  return line_status_exact(m, ox, oy, oz, ex, ey, ez);
+}
+
+// Swept-box status of one segment over lanes: `G` lanes share a segment, chunks of G rays with a
+// ballot after each chunk.  Returns, uniformly over the group, the status of the first non-free ray
+// in lattice order (x outer, y, z inner) or CELL_FREE.  `active` = this lane's group has a segment.
+// (o0x,o0y,o0z) = this lane's ray offset in the first chunk, hoisted by the caller.
+// FAST: rays go through line_status_fast on the blocked plane (`cell` unused).
+template <bool COUNT, bool FAST, class Cell>
+__device__ __forceinline__ int swept_status(const DeviceMap& m, const RayLattice& lat, Cell& cell, bool active, int G,
+                                            int sub, int lig, double o0x, double o0y, double o0z, double tx, double ty,
+                                            double tz, double sx, double sy, double sz,
+                                            unsigned long long* steps_acc = nullptr, bool fast = true) {
+  const int nyz = lat.n[1] * lat.n[2];
+  int result = CELL_FREE;
+  bool done = !active;
+  unsigned gmask = (G == 32) ? 0xffffffffu : (((1u << G) - 1u) << (sub * G));
+  for (int q0 = 0; q0 < lat.rays; q0 += G) {
+    int q = q0 + lig;
+    int st = CELL_FREE;
+    int nsteps = 0;
+    if (!done && q < lat.rays) {
+      double ox = o0x, oy = o0y, oz = o0z;
+      if (q0) {
+        int ix = q / nyz, rem = q - ix * nyz;
+        int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
+        ox = lat.off[0][ix]; oy = lat.off[1][iy]; oz = lat.off[2][iz];
+      }
+      const float fox = d2f(d_add(tx, ox)), foy = d2f(d_add(ty, oy)), foz = d2f(d_add(tz, oz));
+      const float fex = d2f(d_add(sx, ox)), fey = d2f(d_add(sy, oy)), fez = d2f(d_add(sz, oz));
+      if (FAST) st = fast ? line_status_fast(m, fox, foy, foz, fex, fey, fez) : line_status_exact(m, fox, foy, foz, fex, fey, fez);
+      else st = line_status(m.ks, fox, foy, foz, fex, fey, fez, cell, COUNT ? &nsteps : nullptr);
+    }
+    unsigned b = __ballot_sync(0xffffffffu, st != CELL_FREE);
+    unsigned mine = b & gmask;
+    // lowest lane of my group that failed = first ray in lattice order (every lane shuffles)
+    int first = mine ? (__ffs(mine) - 1) : (int)(threadIdx.x & 31);
+    int got = __shfl_sync(0xffffffffu, st, first);
+    if (COUNT && !done && (!mine || (int)(threadIdx.x & 31) <= first)) *steps_acc += (unsigned long long)nsteps;
+    if (!done && mine) {
+      result = got;
+      done = true;
+    }
+    if (__all_sync(0xffffffffu, done)) break;
+  }
+  return result;
+}
+
+// lane's ray offset in the first chunk of the lattice
+__device__ __forceinline__ void lane_offset(const RayLattice& lat, int lig, double& ox, double& oy, double& oz) {
+  ox = oy = oz = 0.0;
+  if (lig < lat.rays) {
+    const int nyz = lat.n[1] * lat.n[2];
+    int ix = lig / nyz, rem = lig - ix * nyz;
+    int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
+    ox = lat.off[0][ix]; oy = lat.off[1][iy]; oz = lat.off[2][iz];
+  }
+}
+
+// One axis of the key box ALL rays of a pair stay in.  The lattice offsets run from off_first to
+// off_last, and adding an offset and narrowing to float are both monotone, so the extreme rays
+// bound the rest: start keys in [key(f(t+first)), key(f(t+last))], end keys likewise for s; plus the
+// one-voxel overshoot beyond the end on the side the pair travels to (none when s == t: then every
+// ray has a zero direction component on this axis).  False when a key leaves the 16-bit space.
+__device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, double s, double off_first, double off_last,
+                                             int& lo, int& hi) {
+  int o_lo, o_hi, e_lo, e_hi;
+  if (!coord_to_key(ks, (double)d2f(d_add(t, off_first)), o_lo) || !coord_to_key(ks, (double)d2f(d_add(t, off_last)), o_hi) ||
+      !coord_to_key(ks, (double)d2f(d_add(s, off_first)), e_lo) || !coord_to_key(ks, (double)d2f(d_add(s, off_last)), e_hi))
+    return false;
+  if (s > t) { lo = o_lo; hi = e_hi + 1; }
+  else if (s < t) { lo = e_lo - 1; hi = o_hi; }
+  else { lo = o_lo; hi = o_hi; }
+  return true;
+}
+
+// Cheap verdict on one ray before any DDA arithmetic: RAY_FREE / RAY_BLOCKED are final, RAY_WALK
+// means the exact walk has to decide.  `fast` enables the key-box shortcut of line_status_fast.
+enum { RAY_FREE = 0, RAY_BLOCKED = 1, RAY_WALK = 2 };
+__device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float ox, float oy, float oz, float ex, float ey,
+                                            float ez) {
+  int kx, ky, kz, ekx, eky, ekz;
+  if (!coord_to_key(m.ks, (double)ox, kx) || !coord_to_key(m.ks, (double)oy, ky) || !coord_to_key(m.ks, (double)oz, kz) ||
+      !coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
+    return RAY_FREE;  // out of key range: upstream leaves the ray empty
+  if (kx == ekx && ky == eky && kz == ekz) return RAY_FREE;
+  if (fast) {
+    const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
+    const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
+    const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
+    if (!box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) return RAY_FREE;
+  }
+  if (map_blocked(m, kx, ky, kz)) return RAY_BLOCKED;  // the start voxel is the first one the walk tests
+  return RAY_WALK;
+}
+
+constexpr int RAY_TABLE_MAX = 256;
+struct EdgeSmemSort {
+  int2 buf[EDGE_WARPS][32];
+};
+struct EdgeSmem {
+  RayLattice lat;
+  double ray_off[RAY_TABLE_MAX][3];  // offset of ray q, when the lattice has <= RAY_TABLE_MAX rays
+  EdgeSmemSort sort;
+  double far_end[EDGE_WARPS][32][3];  // far-end coordinates of the batch's pairs
+  int slots[EDGE_WARPS][32];          // batch slots that still need rays, compacted
+  unsigned queue[EDGE_WARPS][64];     // (slot << 20 | ray) waiting for the exact walk
+  int okey[EDGE_WARPS][32][3];        // origin keys of the first 32 rays of the row (they do not depend on the pair)
+};
+
+__device__ __forceinline__ void ray_offset(const EdgeSmem& sm, int q, double& ox, double& oy, double& oz) {
+  if (sm.lat.rays <= RAY_TABLE_MAX) {
+    ox = sm.ray_off[q][0]; oy = sm.ray_off[q][1]; oz = sm.ray_off[q][2];
+  } else {
+    const int nyz = sm.lat.n[1] * sm.lat.n[2];
+    int ix = q / nyz, rem = q - ix * nyz;
+    int iy = rem / sm.lat.n[2], iz = rem - iy * sm.lat.n[2];
+    ox = sm.lat.off[0][ix]; oy = sm.lat.off[1][iy]; oz = sm.lat.off[2][iz];
+  }
+}
+
+// Exact walks for the first `count` (<= 32) queue entries of this warp; returns the slots found blocked.
+__device__ __forceinline__ unsigned run_walks(const DeviceMap& m, const EdgeSmem& sm, int warp, int lane, int count,
+                                              unsigned blockedmask, double px, double py, double pz) {
+  unsigned bit = 0;
+  if (lane < count) {
+    const unsigned e = sm.queue[warp][lane];
+    const int k = (int)(e >> 20), q = (int)(e & 0xfffffu);
+    if (!((blockedmask >> k) & 1u)) {
+      double ox, oy, oz;
+      ray_offset(sm, q, ox, oy, oz);
+      const double* f = sm.far_end[warp][k];
+      int st = line_status_exact(m, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
+                                 d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)));
+      if (st != CELL_FREE) bit = 1u << k;
+    }
+  }
+  return __reduce_or_sync(0xffffffffu, bit);
+}
+
+// Edge test, one warp per source row.  Work is shed in stages, none of which can change a result
+// (DESIGN.md §5): (1) rows whose reach is free in the coarse pyramid were flagged by k_count;
+// (2) per pair, one lane each: the key box all its rays stay in holds no blocked voxel -> accepted;
+// (3) per ray: the ray's own key box is free -> ray free; (4) the exact DDA walk.
+// The instrumented variant (COUNT) runs every ray through the exact walk.
+#ifndef EDGE_MIN_BLOCKS
+#define EDGE_MIN_BLOCKS 4
+#endif
+// order one row's pairs by list index (reference adjacency is in list order): rank sort.
+// n <= 32: returns this lane's pair after sorting (in registers); else sorts candA -> candB in global memory.
+__device__ __forceinline__ int2 sort_row_pairs(EdgeSmemSort& sb, int warp, int lane, const int2* __restrict__ candA,
+                                               int2* candB, long long off, int n) {
+  int2 c0 = make_int2(0, 0);
+  if (n <= 32) {
+    int2 mine = (lane < n) ? candA[off + lane] : make_int2(0, 0x7fffffff);
+    int key = mine.y & 0x7fffffff;
+    int rank = 0;
+    for (int k = 0; k < n; ++k) rank += ((__shfl_sync(0xffffffffu, mine.y, k) & 0x7fffffff) < key);
+    if (lane < n) sb.buf[warp][rank] = mine;
+    __syncwarp();
+    if (lane < n) c0 = sb.buf[warp][lane];
+    __syncwarp();
+  } else {
+    for (int e = lane; e < n; e += 32) {
+      int2 mine = candA[off + e];
+      int key = mine.y & 0x7fffffff;
+      int rank = 0;
+      for (int k = 0; k < n; ++k) rank += ((candA[off + k].y & 0x7fffffff) < key);
+      candB[off + rank] = mine;
+    }
+    __syncwarp();
+  }
+  return c0;
+}
+
+// Rows the edge kernel does not have to look at — no map, reach free in the pyramid, or no pair at
+// all: every pair is an edge.  One warp per row: sort by list index, write.
+__global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long long* __restrict__ cand_off,
+                                                     const uint8_t* __restrict__ row_free, const int2* __restrict__ candA,
+                                                     int2* candB, int* __restrict__ acc, int* __restrict__ deg, long long pair_cap) {
+  __shared__ EdgeSmemSort sb;
+  if (cand_off[a.nrows] > pair_cap) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = blockIdx.x * EDGE_WARPS + warp;
+  if (t >= a.nrows) return;
+  const int s = a.rows ? a.rows[t] : t;
+  const int r = (int)(a.sorted_idx[s] - a.lo);
+  const long long off = cand_off[r];
+  const int n = (int)(cand_off[r + 1] - off);
+  if (a.use_map && !row_free[r] && n > 0) return;  // a work row: k_edges writes it
+  if (n == 0) {
+    if (lane == 0) deg[r] = 0;
+    return;
+  }
+  int2 c0 = sort_row_pairs(sb, warp, lane, candA, candB, off, n);
+  if (n <= 32) {
+    if (lane < n) acc[off + lane] = c0.y & 0x7fffffff;
+  } else {
+    for (int e = lane; e < n; e += 32) acc[off + e] = candB[off + e].y & 0x7fffffff;
+  }
+  if (lane == 0) deg[r] = n;
+}
+
+template <bool COUNT>
+__device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& m, EdgeSmem& sm, const int warp, const int lane,
+                                         const int t, const long long* __restrict__ cand_off,
+                                         const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
+                                         int* __restrict__ deg, unsigned long long* counters) {
+  const RayLattice& lat = sm.lat;
+  const int s = a.rows ? a.rows[t] : t;
+  const int r = (int)(a.sorted_idx[s] - a.lo);
+  const long long off = cand_off[r];
+  const int n = (int)(cand_off[r + 1] - off);
+  const int2 c0 = sort_row_pairs(sm.sort, warp, lane, candA, candB, off, n);
+
+  const double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
+  const int R = lat.rays;
+  const bool fast = a.use_pyramid != 0;
+  // Row-level verdicts: every ray starts at p + offset whatever the pair, and the start voxel is the
+  // first one a walk tests.  A ray whose start voxel is blocked therefore rejects every pair of this
+  // row for which that ray is not empty (its end key differs from its start key).
+  unsigned startmask = 0;
+  if (!COUNT && fast && R <= 32) {
+    bool blk = false;
+    if (lane < R) {
+      double ox, oy, oz;
+      ray_offset(sm, lane, ox, oy, oz);
+      int kx, ky, kz;
+      if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
+          coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz)) {
+        sm.okey[warp][lane][0] = kx; sm.okey[warp][lane][1] = ky; sm.okey[warp][lane][2] = kz;
+        blk = map_blocked(m, kx, ky, kz) != 0;
+      }
+    }
+    startmask = __ballot_sync(0xffffffffu, blk);
+    __syncwarp();
+  }
+  int nacc = 0;
+  unsigned n_box = 0, n_lat = 0;
+  unsigned long long nsteps = 0;
+  for (int base = 0; base < n; base += 32) {
+    const int nb = min(32, n - base);
+    int2 c = (n <= 32) ? c0 : ((lane < nb) ? candB[off + base + lane] : make_int2(0, 0));
+    const bool mine_valid = lane < nb;
+    const bool same = mine_valid && (c.y & 0x80000000);
+    // this lane's pair: coordinates of the far end
+    double qx = 0, qy = 0, qz = 0;
+    if (mine_valid) { qx = a.sx[c.x]; qy = a.sy[c.x]; qz = a.sz[c.x]; }
+    bool rejected = false;
+    bool needs = mine_valid && !same;
+    // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
+    if (needs && startmask) {
+      for (unsigned mb = startmask; mb; mb &= mb - 1) {
+        const int q = __ffs(mb) - 1;
+        double ox, oy, oz;
+        ray_offset(sm, q, ox, oy, oz);
+        int ekx, eky, ekz;
+        if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
+            coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
+            (ekx != sm.okey[warp][q][0] || eky != sm.okey[warp][q][1] || ekz != sm.okey[warp][q][2])) {
+          needs = false;
+          rejected = true;
+          break;
+        }
+      }
+    }
+    // stage 2b: the pair's key box (one lane per pair)
+    if (!COUNT && fast && needs) {
+      int lox, hix, loy, hiy, loz, hiz;
+      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
+          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
+          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
+          !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz))
+        needs = false;
+    }
+    unsigned need = __ballot_sync(0xffffffffu, needs);
+    unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs && !rejected);  // same-position or box-free pairs
+    n_box += __popc(accmask & ~__ballot_sync(0xffffffffu, same));
+    n_lat += __popc(need);
+    if (COUNT) {
+      // instrumented run: every ray through the exact walk, counted with the reference's
+      // sequential semantics (rays in lattice order, stop after the first non-free ray)
+      BlockedGlobal glob_fn;
+      glob_fn.m = &m;
+      const int G = R >= 32 ? 32 : R, EPI = 32 / G;
+      const int sub = lane / G, lig = lane - sub * G;
+      double o0x, o0y, o0z;
+      lane_offset(lat, lig, o0x, o0y, o0z);
+      while (need) {
+        const int kk = __fns(need, 0, sub + 1);
+        const bool have = (sub < EPI) && kk >= 0 && kk < 32;
+        const int src = have ? kk : 0;
+        const double ex = __shfl_sync(0xffffffffu, qx, src), ey = __shfl_sync(0xffffffffu, qy, src),
+                     ez = __shfl_sync(0xffffffffu, qz, src);
+        int st = swept_status<true, false>(m, lat, glob_fn, have, G, sub, lig, o0x, o0y, o0z, px, py, pz, ex, ey, ez, &nsteps);
+        unsigned took = 0, okm = 0;
+        for (int g = 0; g < EPI; ++g) {
+          int kg = __shfl_sync(0xffffffffu, have ? kk : -1, g * G);
+          int sg = __shfl_sync(0xffffffffu, st, g * G);
+          if (kg >= 0) {
+            took |= 1u << kg;
+            if (sg == CELL_FREE) okm |= 1u << kg;
+          }
+        }
+        accmask |= okm;
+        need &= ~took;
+      }
+    } else if (need) {
+      // stages 3-4: all (pair, ray) items of the batch flattened over the lanes.  A cheap verdict per
+      // ray first; rays that need the exact walk are queued and walked 32 at a time, so the warp
+      // stays full whatever the number of rays per pair, and a pair found blocked drops its other rays.
+      if (needs) sm.slots[warp][__popc(need & ((1u << lane) - 1u))] = lane;
+      if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
+      __syncwarp();
+      const int W = __popc(need) * R;
+      unsigned blockedmask = 0;
+      int qn = 0;
+      for (int w0 = 0; w0 < W; w0 += 32) {
+        const int w = w0 + lane;
+        int verdict = RAY_FREE, k = 0, q = 0;
+        if (w < W) {
+          const int p = w / R;
+          q = w - p * R;
+          k = sm.slots[warp][p];
+          if (!((blockedmask >> k) & 1u)) {
+            double ox, oy, oz;
+            ray_offset(sm, q, ox, oy, oz);
+            const double* f = sm.far_end[warp][k];
+            verdict = ray_precheck(m, fast, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
+                                   d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)));
+          }
+        }
+        blockedmask |= __reduce_or_sync(0xffffffffu, verdict == RAY_BLOCKED ? (1u << k) : 0u);
+        const bool push = verdict == RAY_WALK && !((blockedmask >> k) & 1u);
+        const unsigned pb = __ballot_sync(0xffffffffu, push);
+        if (push) sm.queue[warp][qn + __popc(pb & ((1u << lane) - 1u))] = ((unsigned)k << 20) | (unsigned)q;
+        qn += __popc(pb);
+        __syncwarp();
+        if (qn >= 32) {
+          blockedmask |= run_walks(m, sm, warp, lane, 32, blockedmask, px, py, pz);
+          const unsigned moved = (lane + 32 < qn) ? sm.queue[warp][lane + 32] : 0u;
+          __syncwarp();
+          sm.queue[warp][lane] = moved;
+          qn -= 32;
+          __syncwarp();
+        }
+      }
+      if (qn > 0) blockedmask |= run_walks(m, sm, warp, lane, qn, blockedmask, px, py, pz);
+      __syncwarp();
+      accmask |= need & ~blockedmask;
+    }
+    if ((accmask >> lane) & 1u) acc[off + nacc + __popc(accmask & ((1u << lane) - 1u))] = c.y & 0x7fffffff;
+    nacc += __popc(accmask);
+  }
+  if (lane == 0) {
+    deg[r] = nacc;
+    if (n_box) atomicAdd(counters + 5, (unsigned long long)n_box);
+    if (n_lat) atomicAdd(counters + 6, (unsigned long long)n_lat);
+  }
+  if (COUNT) {
+    for (int o = 16; o; o >>= 1) nsteps += __shfl_xor_sync(0xffffffffu, nsteps, o);
+    if (lane == 0 && nsteps) atomicAdd(counters + 3, nsteps);
+  }
+  __syncwarp();
+}
+
+// Persistent edge kernel: a fixed grid (EDGE_MIN_BLOCKS CTAs per SM); every warp draws the next work
+// row with a ticket, so a row that needs many walks does not hold seven finished warps hostage.
+template <bool COUNT>
+__global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
+k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
+        const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
+        int* __restrict__ deg, unsigned long long* counters, long long pair_cap) {
+  __shared__ EdgeSmem sm;
+  if (cand_off[a.nrows] > pair_cap) return;
+  RayLattice& lat = sm.lat;
+  for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
+  __syncthreads();
+  if (lat.rays <= RAY_TABLE_MAX) {
+    const int nyz = lat.n[1] * lat.n[2];
+    for (int q = threadIdx.x; q < lat.rays; q += blockDim.x) {
+      int ix = q / nyz, rem = q - ix * nyz;
+      int iy = rem / lat.n[2], iz = rem - iy * lat.n[2];
+      sm.ray_off[q][0] = lat.off[0][ix]; sm.ray_off[q][1] = lat.off[1][iy]; sm.ray_off[q][2] = lat.off[2][iz];
+    }
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned long long n_work = counters[7];
+  for (;;) {
+    unsigned long long i = 0;
+    if (lane == 0) i = atomicAdd(counters + 4, 1ull);
+    i = __shfl_sync(0xffffffffu, i, 0);
+    if (i >= n_work) break;
+    edge_row<COUNT>(a, m, sm, warp, lane, work_rows[i], cand_off, candA, candB, acc, deg, counters);
+  }
+}
+
+// CSR compaction: one warp per row, coalesced copy of the accepted prefix
+__global__ void k_compact(const long long* __restrict__ cand_off, const int* __restrict__ deg,
+                          const long long* __restrict__ row_ptr, const int* __restrict__ acc, int* __restrict__ col,
+                          int nrows, long long pair_cap) {
+  if (cand_off[nrows] > pair_cap) return;
+  int r = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  int lane = threadIdx.x & 31;
+  if (r >= nrows) return;
+  long long src = cand_off[r], dst = row_ptr[r];
+  int d = deg[r];
+  for (int e = lane; e < d; e += 32) col[dst + e] = acc[src + e];
+}
+
+// Multi-GPU CSR assembly: every rank holds the all-gathered, padded blocks of all ranks
+// (row_ptr blocks of stride_r entries whose entry [rows_g] is the block's edge count; column blocks
+// of stride_e entries).  One CTA per block rebases and copies: the whole-graph CSR without a host
+// round trip.  bases[g] = first row of block g; out_row_ptr[total_rows] is written by the last block.
+__global__ void k_assemble_blocks(const long long* __restrict__ rp_all, const int* __restrict__ col_all, int world,
+                                  long long stride_r, long long stride_e, const long long* __restrict__ row_base,
+                                  long long* __restrict__ out_rp, int* __restrict__ out_col, long long* __restrict__ overflow) {
+  const int g = blockIdx.y;
+  const long long rows = row_base[g + 1] - row_base[g];
+  long long ebase = 0;
+  for (int k = 0; k < g; ++k) ebase += rp_all[k * stride_r + (row_base[k + 1] - row_base[k])];
+  const long long* rp = rp_all + g * stride_r;
+  const long long edges = rp[rows];
+  if (edges > stride_e) {  // a block did not fit its slot: tell the host, which regathers with larger slots
+    if (threadIdx.x == 0 && blockIdx.x == 0) atomicMax((unsigned long long*)overflow, (unsigned long long)edges);
+    return;
+  }
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  for (long long i = tid; i < rows; i += nth) out_rp[row_base[g] + i] = rp[i] + ebase;
+  if (g == world - 1 && tid == 0) out_rp[row_base[g] + rows] = ebase + edges;
+  const int* col = col_all + g * stride_e;
+  for (long long i = tid; i < edges; i += nth) out_col[ebase + i] = col[i];
+}
+
+
+}  // namespace

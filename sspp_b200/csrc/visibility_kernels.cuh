@@ -1,0 +1,287 @@
+// visibility_kernels.cuh — coverage visibility: frustum planes, point binning, in-frustum gather, occlusion rays, per-viewpoint sort.
+// Part of the single translation unit sspp_gpu.cu (included there, in order); not a stand-alone header.
+#pragma once
+
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// coverage visibility (spec v1): frustum planes -> in-frustum pairs -> one castRay each
+// ------------------------------------------------------------------------------------------------
+struct PointGrid {
+  double min[3];
+  double inv_cell;
+  int n[3];
+};
+__device__ __forceinline__ int pgrid_axis(const PointGrid& g, double v, int a) {
+  int c = (int)floor((v - g.min[a]) * g.inv_cell);
+  return c < 0 ? 0 : (c >= g.n[a] ? g.n[a] - 1 : c);
+}
+
+struct ViewRec {       // one per viewpoint, built on the device from the pose
+  float pl[6][4];      // left, right, top, bottom, far, near
+  float T[3];
+  int c0[3], c1[3];    // inclusive cell range of the frustum's bounding box in the point grid
+};
+
+__device__ __forceinline__ void cross3f(const float a[3], const float b[3], float o[3]) {
+  o[0] = f_sub(f_mul(a[1], b[2]), f_mul(a[2], b[1]));
+  o[1] = f_sub(f_mul(a[2], b[0]), f_mul(a[0], b[2]));
+  o[2] = f_sub(f_mul(a[0], b[1]), f_mul(a[1], b[0]));
+}
+__device__ __forceinline__ float dot3f(const float a[3], const float b[3]) {
+  return f_add(f_add(f_mul(a[0], b[0]), f_mul(a[1], b[1])), f_mul(a[2], b[2]));
+}
+
+// fr = (vh, hw, near, far): 2*tan(vfov/2), 2*tan(hfov/2) evaluated on the host
+__global__ void k_view_setup(const double* __restrict__ poses, int64_t nv, float vh, float hw, float np_dist, float fp_dist,
+                             PointGrid g, ViewRec* __restrict__ out) {
+  int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nv) return;
+  const double* P = poses + 7 * v;
+  double x = P[3], y = P[4], z = P[5], w = P[6];
+  // tf::Matrix3x3::setRotation in double
+  double d = d_add(d_add(d_add(d_mul(x, x), d_mul(y, y)), d_mul(z, z)), d_mul(w, w));
+  double s = d_div(2.0, d);
+  double xs = d_mul(x, s), ys = d_mul(y, s), zs = d_mul(z, s);
+  double wx = d_mul(w, xs), wy = d_mul(w, ys), wz = d_mul(w, zs);
+  double xx = d_mul(x, xs), xy = d_mul(x, ys), xz = d_mul(x, zs);
+  double yy = d_mul(y, ys), yz = d_mul(y, zs), zz = d_mul(z, zs);
+  float view[3] = {d2f(d_sub(1.0, d_add(yy, zz))), d2f(d_add(xy, wz)), d2f(d_sub(xz, wy))};
+  float up[3] = {d2f(d_sub(xy, wz)), d2f(d_sub(1.0, d_add(xx, zz))), d2f(d_add(yz, wx))};
+  float right[3] = {d2f(d_add(xz, wy)), d2f(d_sub(yz, wx)), d2f(d_sub(1.0, d_add(xx, yy)))};
+  float T[3] = {d2f(P[0]), d2f(P[1]), d2f(P[2])};
+  float np_h = f_mul(vh, np_dist), np_w = f_mul(hw, np_dist), fp_h = f_mul(vh, fp_dist), fp_w = f_mul(hw, fp_dist);
+  float fp_c[3], np_c[3], fp_tl[3], fp_tr[3], fp_bl[3], fp_br[3], np_tl[3], np_tr[3], np_bl[3], np_br[3];
+  for (int i = 0; i < 3; ++i) {
+    fp_c[i] = f_add(T[i], f_mul(view[i], fp_dist));
+    np_c[i] = f_add(T[i], f_mul(view[i], np_dist));
+    float fu = f_div(f_mul(up[i], fp_h), 2.0f), fr = f_div(f_mul(right[i], fp_w), 2.0f);
+    float nu = f_div(f_mul(up[i], np_h), 2.0f), nr = f_div(f_mul(right[i], np_w), 2.0f);
+    fp_tl[i] = f_sub(f_add(fp_c[i], fu), fr);
+    fp_tr[i] = f_add(f_add(fp_c[i], fu), fr);
+    fp_bl[i] = f_sub(f_sub(fp_c[i], fu), fr);
+    fp_br[i] = f_add(f_sub(fp_c[i], fu), fr);
+    np_tl[i] = f_sub(f_add(np_c[i], nu), nr);
+    np_tr[i] = f_add(f_add(np_c[i], nu), nr);
+    np_bl[i] = f_sub(f_sub(np_c[i], nu), nr);
+    np_br[i] = f_add(f_sub(np_c[i], nu), nr);
+  }
+  ViewRec R;
+  float e1[3], e2[3], a[3], b[3], c[3], dd[3];
+  for (int i = 0; i < 3; ++i) { e1[i] = f_sub(fp_bl[i], fp_br[i]); e2[i] = f_sub(fp_tr[i], fp_br[i]); }
+  cross3f(e1, e2, R.pl[4]);
+  R.pl[4][3] = -dot3f(fp_c, R.pl[4]);
+  for (int i = 0; i < 3; ++i) { e1[i] = f_sub(np_tr[i], np_br[i]); e2[i] = f_sub(np_bl[i], np_br[i]); }
+  cross3f(e1, e2, R.pl[5]);
+  R.pl[5][3] = -dot3f(np_c, R.pl[5]);
+  for (int i = 0; i < 3; ++i) {
+    a[i] = f_sub(fp_bl[i], T[i]); b[i] = f_sub(fp_br[i], T[i]); c[i] = f_sub(fp_tr[i], T[i]); dd[i] = f_sub(fp_tl[i], T[i]);
+  }
+  cross3f(dd, a, R.pl[0]);
+  cross3f(b, c, R.pl[1]);
+  cross3f(c, dd, R.pl[2]);
+  cross3f(a, b, R.pl[3]);
+  for (int k = 0; k < 4; ++k) R.pl[k][3] = -dot3f(T, R.pl[k]);
+  for (int i = 0; i < 3; ++i) R.T[i] = T[i];
+  // bounding box of the eight corners, grown by a rounding allowance, in grid cells
+  for (int i = 0; i < 3; ++i) {
+    float lo = fminf(fminf(fminf(fp_tl[i], fp_tr[i]), fminf(fp_bl[i], fp_br[i])), fminf(fminf(np_tl[i], np_tr[i]), fminf(np_bl[i], np_br[i])));
+    float hi = fmaxf(fmaxf(fmaxf(fp_tl[i], fp_tr[i]), fmaxf(fp_bl[i], fp_br[i])), fmaxf(fmaxf(np_tl[i], np_tr[i]), fmaxf(np_bl[i], np_br[i])));
+    double eps = 1e-3 + 1e-4 * ((double)fabsf(T[i]) + (double)fp_dist);
+    R.c0[i] = pgrid_axis(g, (double)lo - eps, i);
+    R.c1[i] = pgrid_axis(g, (double)hi + eps, i);
+    if (!(hi >= lo)) { R.c0[i] = 0; R.c1[i] = g.n[i] - 1; }  // NaN pose: scan everything, planes reject all
+  }
+  out[v] = R;
+}
+
+__device__ __forceinline__ bool in_frustum_dev(const ViewRec& R, float px, float py, float pz) {
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    float val = f_add(f_add(f_add(f_mul(px, R.pl[k][0]), f_mul(py, R.pl[k][1])), f_mul(pz, R.pl[k][2])), R.pl[k][3]);
+    if (!(val <= 0.0f)) return false;
+  }
+  return true;
+}
+
+__global__ void k_pts_bbox(const float* __restrict__ xyz, int64_t n, unsigned long long* bbox) {
+  unsigned long long mn[3] = {~0ull, ~0ull, ~0ull}, mx[3] = {0, 0, 0};
+  unsigned long long bad = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    for (int a = 0; a < 3; ++a) {
+      double v = (double)xyz[3 * i + a];
+      if (!isfinite(v)) { ++bad; continue; }
+      unsigned long long e = enc_f64(v);
+      mn[a] = min(mn[a], e);
+      mx[a] = max(mx[a], e);
+    }
+  for (int a = 0; a < 3; ++a)
+    for (int o = 16; o; o >>= 1) {
+      mn[a] = min(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = max(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  for (int o = 16; o; o >>= 1) bad += __shfl_xor_sync(0xffffffffu, bad, o);
+  if ((threadIdx.x & 31) == 0) {
+    for (int a = 0; a < 3; ++a) { atomicMin(bbox + a, mn[a]); atomicMax(bbox + 3 + a, mx[a]); }
+    if (bad) atomicAdd(bbox + 6, bad);
+  }
+}
+
+__global__ void k_pts_hist(const float* __restrict__ xyz, int64_t n, PointGrid g, int* __restrict__ cell_of, int* cell_count) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int cx = pgrid_axis(g, (double)xyz[3 * i], 0), cy = pgrid_axis(g, (double)xyz[3 * i + 1], 1), cz = pgrid_axis(g, (double)xyz[3 * i + 2], 2);
+  int c = (cz * g.n[1] + cy) * g.n[0] + cx;
+  cell_of[i] = c;
+  atomicAdd(cell_count + c, 1);
+}
+
+__global__ void k_pts_scatter(const float* __restrict__ xyz, int64_t n, const int* __restrict__ cell_of, int* cursor,
+                              int* __restrict__ sorted_idx, float4* __restrict__ sp) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n || cell_of[i] < 0) return;
+  int pos = atomicAdd(cursor + cell_of[i], 1);
+  sorted_idx[pos] = (int)i;
+  sp[pos] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], __int_as_float((int)i));
+}
+
+// one warp per viewpoint: in-frustum points of the cells its bounding box touches.
+// FILL == false: count only.  FILL == true: write (viewpoint, binned position) per ray.
+template <bool FILL>
+__global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__ views, int64_t v0, int nv, PointGrid g,
+                                                     const int* __restrict__ cell_start, const float4* __restrict__ sp,
+                                                     int* __restrict__ ray_count, const long long* __restrict__ ray_off,
+                                                     int* __restrict__ ray_view, int* __restrict__ ray_pt) {
+  int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  int lane = threadIdx.x & 31;
+  if (w >= nv) return;
+  const ViewRec R = views[v0 + w];
+  long long base = FILL ? ray_off[w] : 0;
+  int filled = 0;
+  for (int cz = R.c0[2]; cz <= R.c1[2]; ++cz)
+    for (int cy = R.c0[1]; cy <= R.c1[1]; ++cy) {
+      int cb = (cz * g.n[1] + cy) * g.n[0];
+      int b = cell_start[cb + R.c0[0]], e = cell_start[cb + R.c1[0] + 1];
+      for (int j0 = b; j0 < e; j0 += 32) {
+        int j = j0 + lane;
+        bool in = false;
+        if (j < e) {
+          float4 p = sp[j];
+          in = in_frustum_dev(R, p.x, p.y, p.z);
+        }
+        unsigned bal = __ballot_sync(0xffffffffu, in);
+        if (FILL && in) {
+          long long o = base + filled + __popc(bal & ((1u << lane) - 1u));
+          ray_view[o] = w;
+          ray_pt[o] = j;
+        }
+        filled += __popc(bal);
+      }
+    }
+  if (!FILL && lane == 0) ray_count[w] = filled;
+}
+
+// one thread per occlusion ray
+__global__ void __launch_bounds__(256) k_view_rays(DeviceMap m, const ViewRec* __restrict__ views, int64_t v0,
+                                                   const float4* __restrict__ sp, const int* __restrict__ ray_view,
+                                                   const int* __restrict__ ray_pt, long long nrays, uint8_t* __restrict__ vis,
+                                                   int* vis_count) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  bool visible = false;
+  int w = -1;
+  if (i < nrays) {
+    w = ray_view[i];
+    const ViewRec& R = views[v0 + w];
+    float4 p = sp[ray_pt[i]];
+    float ox = R.T[0], oy = R.T[1], oz = R.T[2];
+    float dx = f_sub(p.x, ox), dy = f_sub(p.y, oy), dz = f_sub(p.z, oz);
+    CellStatusFn cell;
+    cell.m = &m;
+    int hx, hy, hz;
+    bool hit = cast_ray(m.ks, ox, oy, oz, dx, dy, dz, true, norm3f(dx, dy, dz), cell, hx, hy, hz);
+    if (!hit) visible = true;
+    else {
+      int kx, ky, kz;
+      visible = coord_to_key(m.ks, (double)p.x, kx) && coord_to_key(m.ks, (double)p.y, ky) &&
+                coord_to_key(m.ks, (double)p.z, kz) && kx == hx && ky == hy && kz == hz;
+    }
+    vis[i] = visible ? 1 : 0;
+  }
+  // rays of one viewpoint are contiguous: aggregate the count per warp where the warp is uniform
+  unsigned bal = __ballot_sync(0xffffffffu, visible);
+  int w0 = __shfl_sync(0xffffffffu, w, 0);
+  bool uniform = __all_sync(0xffffffffu, w == w0 || w < 0);
+  if (uniform) {
+    if ((threadIdx.x & 31) == 0 && bal && w0 >= 0) atomicAdd(vis_count + w0, __popc(bal));
+  } else if (visible) {
+    atomicAdd(vis_count + w, 1);
+  }
+}
+
+// one warp per viewpoint: compact the visible rays' ORIGINAL point indices
+__global__ void k_view_compact(int nv, const long long* __restrict__ ray_off, const uint8_t* __restrict__ vis,
+                               const int* __restrict__ ray_pt, const float4* __restrict__ sp,
+                               const long long* __restrict__ vis_ptr, int* __restrict__ out) {
+  int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+  int lane = threadIdx.x & 31;
+  if (w >= nv) return;
+  long long b = ray_off[w], e = ray_off[w + 1], o = vis_ptr[w];
+  for (long long j0 = b; j0 < e; j0 += 32) {
+    long long j = j0 + lane;
+    bool v = (j < e) && vis[j];
+    unsigned bal = __ballot_sync(0xffffffffu, v);
+    if (v) out[o + __popc(bal & ((1u << lane) - 1u))] = __float_as_int(sp[ray_pt[j]].w);
+    o += __popc(bal);
+  }
+}
+
+// ascending sort of every viewpoint's index list: one CTA per viewpoint, all-ascending bitonic
+// network (flip + half-cleaners), virtual +inf padding beyond the segment
+__device__ __forceinline__ void cmpswap(int* a, long long i, long long j, long long len) {
+  if (j < len) {
+    int x = a[i], y = a[j];
+    if (x > y) { a[i] = y; a[j] = x; }
+  }
+}
+__global__ void __launch_bounds__(256) k_segment_sort(int nv, const long long* __restrict__ ptr, int* data) {
+  extern __shared__ int sh[];
+  const int SM_CAP = 8192;
+  for (int w = blockIdx.x; w < nv; w += gridDim.x) {
+    long long b = ptr[w], len = ptr[w + 1] - b;
+    if (len < 2) continue;
+    int* a = data + b;
+    bool in_smem = len <= SM_CAP;
+    if (in_smem) {
+      for (int i = threadIdx.x; i < len; i += blockDim.x) sh[i] = a[i];
+      a = sh;
+    }
+    __syncthreads();
+    long long P = 1;
+    while (P < len) P <<= 1;
+    for (long long k = 2; k <= P; k <<= 1) {
+      // flip: i in the lower half of its k-block is compared with its mirror
+      for (long long t = threadIdx.x; t < P / 2; t += blockDim.x) {
+        long long blk = t / (k / 2), o = t % (k / 2);
+        long long i = blk * k + o, j = blk * k + (k - 1 - o);
+        if (i < len) cmpswap(a, i, j, len);
+      }
+      __syncthreads();
+      for (long long h = k / 4; h >= 1; h >>= 1) {
+        for (long long t = threadIdx.x; t < P / 2; t += blockDim.x) {
+          long long blk = t / h, o = t % h;
+          long long i = blk * 2 * h + o, j = i + h;
+          if (i < len) cmpswap(a, i, j, len);
+        }
+        __syncthreads();
+      }
+    }
+    if (in_smem) {
+      int* g = data + b;
+      for (int i = threadIdx.x; i < len; i += blockDim.x) g[i] = sh[i];
+    }
+    __syncthreads();
+  }
+}
+
+
+}  // namespace
