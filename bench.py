@@ -428,7 +428,19 @@ def main():
     except Exception:
         l2_gbps = None
     ph = np.mean(np.array(phase_ms), axis=0)
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    # DRAM traffic of the dominant kernel per launch: from the committed `ncu --set full` capture of this command
+    traffic, traffic_src = None, None
+    try:
+        txt = open(os.path.join(REPO, "profiles", "r01_k_edges_ncu_summary.txt")).read().split("\n")
+        rd = [float(l.split()[1]) for l in txt if l.startswith("dram__bytes_read.sum")]
+        wr = [float(l.split()[1]) for l in txt if l.startswith("dram__bytes_write.sum")]
+        if rd and wr and not distributed:
+            traffic = (rd[0] + wr[0]) * 1e6
+            traffic_src = "profiles/r01_k_edges_ncu_summary.txt (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, Mbyte)"
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": traffic_src,
                 "kernel": "k_edges", "kernel_ms": k_ms, "kernel_share_of_step": k_ms / (total_ms / K),
                 "algorithmic_bytes": alg_bytes, "peak_source": peak_src,
                 "bytes_model": "24*C + 4*steps + 4*E + 32*N with C=%d in-radius pairs, steps=%d voxel lookups (counted on the "

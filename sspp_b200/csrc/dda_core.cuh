@@ -198,6 +198,17 @@ SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float di
   if (sx == 0 && sy == 0 && sz == 0) return false;
   const bool max_range_set = (max_range > 0.0);
   const double maxrange_sq = d_mul(max_range, max_range);
+  // squared distance of the current voxel centre from the origin, one term per axis: upstream rebuilds
+  // all three every step; only the axis that moved changes, so the other two terms are kept
+  // (each term is the float product (c - o)^2 widened to double; the sum keeps upstream's order)
+  double qx = 0.0, qy = 0.0, qz = 0.0;
+  if (max_range_set) {
+    float ddx = f_sub(d2f(key_to_coord(ks, kx)), ox), ddy = f_sub(d2f(key_to_coord(ks, ky)), oy),
+          ddz = f_sub(d2f(key_to_coord(ks, kz)), oz);
+    qx = (double)f_mul(ddx, ddx);
+    qy = (double)f_mul(ddy, ddy);
+    qz = (double)f_mul(ddz, ddz);
+  }
   for (int it = 0; it < 262144; ++it) {
     int dim;
     if (tx < ty) dim = (tx < tz) ? 0 : 2;
@@ -205,21 +216,21 @@ SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float di
     if (dim == 0) {
       if ((sx < 0 && kx == 0) || (sx > 0 && kx == 65535)) return false;
       kx += sx; tx = d_add(tx, dtx);
+      if (max_range_set) { float dd = f_sub(d2f(key_to_coord(ks, kx)), ox); qx = (double)f_mul(dd, dd); }
     } else if (dim == 1) {
       if ((sy < 0 && ky == 0) || (sy > 0 && ky == 65535)) return false;
       ky += sy; ty = d_add(ty, dty);
+      if (max_range_set) { float dd = f_sub(d2f(key_to_coord(ks, ky)), oy); qy = (double)f_mul(dd, dd); }
     } else {
       if ((sz < 0 && kz == 0) || (sz > 0 && kz == 65535)) return false;
       kz += sz; tz = d_add(tz, dtz);
+      if (max_range_set) { float dd = f_sub(d2f(key_to_coord(ks, kz)), oz); qz = (double)f_mul(dd, dd); }
     }
     if (max_range_set) {
-      // end = keyToCoord(key) narrowed to float; squared distance: float products summed in double
-      float cx = d2f(key_to_coord(ks, kx)), cy = d2f(key_to_coord(ks, ky)), cz = d2f(key_to_coord(ks, kz));
-      float ddx = f_sub(cx, ox), ddy = f_sub(cy, oy), ddz = f_sub(cz, oz);
       double d2 = 0.0;
-      d2 = d_add(d2, (double)f_mul(ddx, ddx));
-      d2 = d_add(d2, (double)f_mul(ddy, ddy));
-      d2 = d_add(d2, (double)f_mul(ddz, ddz));
+      d2 = d_add(d2, qx);
+      d2 = d_add(d2, qy);
+      d2 = d_add(d2, qz);
       if (d2 > maxrange_sq) return false;
     }
     if (steps) ++*steps;

@@ -73,6 +73,18 @@ struct CellStatusFn {
   __device__ __forceinline__ int operator()(int kx, int ky, int kz) const { return map_cell_status(*m, kx, ky, kz); }
 };
 
+// castRay cell functor when unknown cells are ignored: only the occupied plane matters (a key
+// outside the window is unknown, i.e. passed through)
+struct CellOccupiedOnly {
+  const DeviceMap* m;
+  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const {
+    int x = kx - m->kmin[0], y = ky - m->kmin[1], z = kz - m->kmin[2];
+    if ((unsigned)x >= (unsigned)m->dims[0] || (unsigned)y >= (unsigned)m->dims[1] || (unsigned)z >= (unsigned)m->dims[2])
+      return CELL_FREE;
+    return ((__ldg(m->occ + map_word(*m, x >> 5, y, z)) >> (x & 31)) & 1u) ? CELL_OCCUPIED : CELL_FREE;
+  }
+};
+
 struct BlockedGlobal {
   const DeviceMap* m;
   __device__ __forceinline__ int operator()(int kx, int ky, int kz) const { return map_blocked(*m, kx, ky, kz); }

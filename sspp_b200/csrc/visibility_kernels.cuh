@@ -195,7 +195,7 @@ __global__ void __launch_bounds__(256) k_view_rays(DeviceMap m, const ViewRec* _
     float4 p = sp[ray_pt[i]];
     float ox = R.T[0], oy = R.T[1], oz = R.T[2];
     float dx = f_sub(p.x, ox), dy = f_sub(p.y, oy), dz = f_sub(p.z, oz);
-    CellStatusFn cell;
+    CellOccupiedOnly cell;  // ignoreUnknown = true: unknown cells are walked through
     cell.m = &m;
     int hx, hy, hz;
     bool hit = cast_ray(m.ks, ox, oy, oz, dx, dy, dz, true, norm3f(dx, dy, dz), cell, hx, hy, hz);

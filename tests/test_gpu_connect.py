@@ -278,3 +278,20 @@ def test_device_block_assembly(eng, orc):
     eng.synchronize()
     assert int(over.item()) == small + 1
     w.close()
+
+
+@pytest.mark.parametrize("res,extent,n", [(0.3, 8.0, 4000), (0.5, 7.0, 2500), (0.1, 6.0, 1200)])
+def test_dense_rows_with_map(eng, orc, res, extent, n):
+    """rows with far more than 32 pairs (batches of 32, global-memory rank sort) with a map, at 27, 18 and
+    245 rays per pair; also the instrumented step count on such rows"""
+    n_vox = 64 if res >= 0.3 else 128
+    w = make_map(eng, orc, res, True, n_vox=n_vox, seed=31, region=extent * 1.2, n_boxes=10, n_spheres=6)
+    nodes = scenes.uniform_nodes(n, extent=extent, seed=17)
+    st, cnt = assert_same_graph(eng, orc, w, nodes, 1.5)
+    assert st.in_radius_pairs / n > 40
+    eng.set_nodes(nodes)
+    sc = eng.connect(radius=1.5, box=BOX, count_steps=True)
+    rp, col = eng.connect_fetch(sc)
+    rp_o, col_o, _ = orc.connect(w, nodes, 1.5, BOX)
+    assert np.array_equal(col, col_o) and sc.voxel_steps == cnt[2]
+    w.close()
