@@ -154,6 +154,17 @@ void ref_get_nodes(void* h, double* poses, int32_t* ids) {
   }
 }
 
+// file formats of the reference (src/pathplanner.cpp:204-359), driven through its own code
+void ref_load_regular_grid(void* h, const char* f1, const char* f2, const char* f3) {
+  Quiet q;
+  ((RefPlanner*)h)->planner->loadRegularGrid(f1, f2, f3);
+}
+void ref_save_search_space(void* h, const char* fn) { ((RefPlanner*)h)->planner->saveSearchSpace(fn); }
+void ref_load_search_space(void* h, const char* fn) {
+  Quiet q;
+  ((RefPlanner*)h)->planner->loadSearchSpace(fn);
+}
+
 void ref_disconnect(void* h) { ((RefPlanner*)h)->planner->disconnectNodes(); }
 
 // runs the reference's O(N^2) connectNodes; returns MAXNODES (= connection count it printed)

@@ -178,6 +178,14 @@ int sspph_load_regular_grid(void* p, const char* f1, const char* f2, const char*
   Handle* h = (Handle*)p;
   GUARD(h, h->planner->loadRegularGrid(f1, f2, f3));
 }
+int sspph_save_search_space(void* p, const char* fn) {
+  Handle* h = (Handle*)p;
+  GUARD(h, h->planner->saveSearchSpace(fn));
+}
+int sspph_load_search_space(void* p, const char* fn) {
+  Handle* h = (Handle*)p;
+  GUARD(h, h->planner->loadSearchSpace(fn));
+}
 int64_t sspph_num_nodes(void* p) { return (int64_t)((Handle*)p)->planner->flatten().size(); }
 void sspph_get_nodes(void* p, double* poses, int32_t* ids) {
   Handle* h = (Handle*)p;

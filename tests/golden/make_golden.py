@@ -90,5 +90,56 @@ def main():
     p.close()
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and "--extra" not in sys.argv:
     main()
+
+
+def casarea_map():
+    """resources/casarea_s.png through resources/map.yaml (res 0.05, origin (-16,-12,0), occupied when
+    (255-gray)/255 > 0.65, free when < 0.196, else unknown; image row 0 is the top = largest y), extruded
+    over z in [-1, 1) m: the S1m variant of SURVEY.md §8(d).  Returns key_min, dims, occ, known bit planes."""
+    from PIL import Image
+    sys.path.insert(0, os.path.join(HERE, "..", ".."))
+    from sspp_b200 import scenes
+    a = np.array(Image.open("/root/reference/resources/casarea_s.png").convert("L")).astype(np.float64)
+    p = (255.0 - a) / 255.0
+    occ2 = (p > 0.65)[::-1]          # row 0 of the flipped image = smallest y
+    free2 = (p < 0.196)[::-1]
+    nz = 40
+    occ = np.repeat(occ2[None], nz, axis=0)
+    known = np.repeat((occ2 | free2)[None], nz, axis=0)
+    key_min = np.array([32768 - 320, 32768 - 240, 32768 - 20], dtype=np.int32)   # origin (-16,-12,-1) at res 0.05
+    dims = np.array([640, 480, nz], dtype=np.int32)
+    return key_min, dims, scenes.pack_bits(occ), scenes.pack_bits(known), occ2, (occ2 | free2)
+
+
+def make_casarea():
+    O = oracle_lib.Oracle(oracle_lib.LIB_REF)
+    key_min, dims, occ, known, occ2, known2 = casarea_map()
+    w = O.world(0.05, True)
+    w.build_dense(key_min, dims, occ, known)
+    p = O.planner(1.5, w)
+    p.set_goal([5, 5, 0.5, 0, 0, 0, 0], 0.6)
+    p.generate_grid([0, 0, 0], [10, 10, 1], 1.0, False, 90.0)
+    poses, ids = p.nodes()
+    E = p.connect()
+    rp, col = p.csr()
+    path, created, expanded = p.astar([-2, -5, 0.5, 0, 0, 0, 0])
+    np.savez_compressed(os.path.join(HERE, "casarea_s1m.npz"), occ2d=np.packbits(occ2, axis=1), known2d=np.packbits(known2, axis=1),
+                        poses=poses, row_ptr=rp, col_idx=col, path=path, created=created, expanded=expanded, connections=E,
+                        collision_calls=p.collision_calls())
+    print("casarea", len(poses), E, p.collision_calls(), created, expanded, len(path))
+    p.close()
+    w.close()
+
+
+def make_cam_fixture():
+    rows = np.loadtxt("/root/reference/resources/SearchSpaceCam_1.5m_1to4_NEW.txt", max_rows=14765)
+    sel = rows[::37][:400]   # spread over the whole file: 8 yaws, all heights
+    np.savez_compressed(os.path.join(HERE, "cam_fixture_poses.npz"), poses=sel)
+    print("cam poses", sel.shape)
+
+
+if __name__ == "__main__" and "--extra" in sys.argv:
+    make_casarea()
+    make_cam_fixture()

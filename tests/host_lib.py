@@ -44,6 +44,8 @@ def lib():
         L.sspph_generate_grid.argtypes = [vp, vp, vp, ctypes.c_float, ctypes.c_int, ctypes.c_float, ctypes.c_int]
         L.sspph_insert_nodes.argtypes = [vp, vp, i64]
         L.sspph_load_regular_grid.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p]
+        L.sspph_save_search_space.argtypes = [vp, ctypes.c_char_p]
+        L.sspph_load_search_space.argtypes = [vp, ctypes.c_char_p]
         L.sspph_num_nodes.restype = i64
         L.sspph_num_nodes.argtypes = [vp]
         L.sspph_get_nodes.argtypes = [vp, vp, vp]
@@ -151,6 +153,12 @@ class HostPlanner:
 
     def load_regular_grid(self, f1, f2, f3):
         self._ck(self.L.sspph_load_regular_grid(self.h, f1.encode(), f2.encode(), f3.encode()))
+
+    def save_search_space(self, fn):
+        self._ck(self.L.sspph_save_search_space(self.h, fn.encode()))
+
+    def load_search_space(self, fn):
+        self._ck(self.L.sspph_load_search_space(self.h, fn.encode()))
 
     def nodes(self):
         n = self.L.sspph_num_nodes(self.h)

@@ -183,6 +183,15 @@ class RefPlanner:
         self.L.ref_get_nodes(self.h, _p(P), _p(ids))
         return P, ids
 
+    def load_regular_grid(self, f1, f2, f3):
+        self.L.ref_load_regular_grid(self.h, f1.encode(), f2.encode(), f3.encode())
+
+    def save_search_space(self, fn):
+        self.L.ref_save_search_space(self.h, fn.encode())
+
+    def load_search_space(self, fn):
+        self.L.ref_load_search_space(self.h, fn.encode())
+
     def disconnect(self):
         self.L.ref_disconnect(self.h)
 
@@ -254,6 +263,9 @@ class Oracle:
             L.ref_num_nodes.argtypes = [vp]
             L.ref_get_nodes.argtypes = [vp, vp, vp]
             L.ref_disconnect.argtypes = [vp]
+            L.ref_load_regular_grid.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p]
+            L.ref_save_search_space.argtypes = [vp, ctypes.c_char_p]
+            L.ref_load_search_space.argtypes = [vp, ctypes.c_char_p]
             L.ref_connect.restype = lng
             L.ref_connect.argtypes = [vp]
             L.ref_collision_calls.restype = lng

@@ -295,3 +295,22 @@ def test_dense_rows_with_map(eng, orc, res, extent, n):
     rp_o, col_o, _ = orc.connect(w, nodes, 1.5, BOX)
     assert np.array_equal(col, col_o) and sc.voxel_steps == cnt[2]
     w.close()
+
+
+def test_casarea_map_golden(eng):
+    """BASELINE config 1 with a map (S1m): resources/casarea_s.png via resources/map.yaml (res 0.05, 847 rays per
+    pair), extruded over z in [-1,1); adjacency from the reference's compiled sources (tests/golden/make_golden.py)"""
+    g = np.load(os.path.join(GOLD, "casarea_s1m.npz"))
+    occ2 = np.unpackbits(g["occ2d"], axis=1)[:, :640].astype(bool)
+    known2 = np.unpackbits(g["known2d"], axis=1)[:, :640].astype(bool)
+    nz = 40
+    occ = scenes.pack_bits(np.repeat(occ2[None], nz, axis=0))
+    known = scenes.pack_bits(np.repeat(known2[None], nz, axis=0))
+    eng.map_create(0.05, [32768 - 320, 32768 - 240, 32768 - 20], [640, 480, nz], True)
+    eng.map_upload_dense(occ, known)
+    eng.set_nodes(g["poses"][:, :3])
+    for pyr in (True, False):
+        st = eng.connect(radius=1.5, box=BOX, use_pyramid=pyr)
+        rp, col = eng.connect_fetch(st)
+        assert st.rays_per_pair == 847 and st.tested_pairs == int(g["collision_calls"])
+        assert np.array_equal(rp, g["row_ptr"]) and np.array_equal(col, g["col_idx"])

@@ -117,3 +117,25 @@ def test_coverage_heuristic_plans_a_view_path(eng, orc):
         assert abs(cov[k] - 100.0 * len(union) / len(pts)) < 1e-9
     p.close()
     w.close()
+
+
+def test_casarea_scenario_through_the_mirror(eng):
+    """config 1 on the casarea map: grid -> connectNodes (GPU, 847 rays per pair) -> A*, against the path the
+    reference's compiled sources found on the same map"""
+    from sspp_b200 import scenes
+    g = np.load(os.path.join(GOLD, "casarea_s1m.npz"))
+    occ2 = np.unpackbits(g["occ2d"], axis=1)[:, :640].astype(bool)
+    known2 = np.unpackbits(g["known2d"], axis=1)[:, :640].astype(bool)
+    nz = 40
+    p = host_lib.HostPlanner(1.5, device=0)
+    p.map_create(0.05, [32768 - 320, 32768 - 240, 32768 - 20], [640, 480, nz], True)
+    p.map_upload_dense(scenes.pack_bits(np.repeat(occ2[None], nz, axis=0)), scenes.pack_bits(np.repeat(known2[None], nz, axis=0)))
+    p.set_goal([5, 5, 0.5, 0, 0, 0, 0], 0.6)
+    p.generate_grid([0, 0, 0], [10, 10, 1], 1.0, False, 90.0)
+    assert np.array_equal(p.nodes()[0], g["poses"])
+    edges, tested = p.connect()
+    assert (edges, tested) == (int(g["connections"]), int(g["collision_calls"]))
+    path, created, expanded, _ = p.astar([-2, -5, 0.5, 0, 0, 0, 0])
+    assert len(path) > 5 and np.array_equal(path, g["path"])
+    assert (created, expanded) == (int(g["created"]), int(g["expanded"]))
+    p.close()

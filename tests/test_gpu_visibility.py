@@ -71,3 +71,37 @@ def test_visibility_large_segments_sorted(eng, orc):
     assert st.visible_pairs > 8192
     assert np.array_equal(vp, vp_o) and np.array_equal(idx, idx_o)
     w.close()
+
+
+def test_visibility_with_reference_camera_poses(eng, orc):
+    """sensor poses taken from the reference's own viewpoint fixture (resources/SearchSpaceCam_1.5m_1to4_NEW.txt,
+    400 rows spread over the file: eight yaws, tilted cameras, heights -1.5..18 m) against a synthetic
+    aircraft-like model (ellipsoid fuselage + wing slab) voxelised at 0.25 m — SURVEY.md S2"""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cam_fixture_poses.npz"))
+    poses = g["poses"]
+    res, n = 0.25, 320
+    half = n // 2
+    c = (np.arange(n) - half + 0.5) * res
+    zc = (np.arange(96) - 8 + 0.5) * res          # z from -2 m to 22 m
+    Z, Y, X = np.meshgrid(zc, c, c, indexing="ij")
+    fus = (X / 30.0) ** 2 + (Y / 3.0) ** 2 + ((Z - 5.0) / 3.0) ** 2 <= 1.0
+    wing = (np.abs(X) < 4.0) & (np.abs(Y) < 30.0) & (np.abs(Z - 4.5) < 0.6)
+    occ = fus | wing
+    known = np.ones_like(occ)
+    ob, kb = scenes.pack_bits(occ), scenes.pack_bits(known)
+    km, dm = [32768 - half, 32768 - half, 32768 - 8], [n, n, 96]
+    eng.map_create(res, km, dm, True)
+    eng.map_upload_dense(ob, kb)
+    w = orc.world(res, True)
+    w.build_dense(km, dm, ob, kb)
+    pts = scenes.surface_points(ob, kb, np.array(km), np.array(dm), res, 60000, seed=1234)
+    eng.set_model_points(pts)
+    st, vp, idx = eng.visibility(poses, 58.0, 45.0, 0.7, 6.0)
+    sel = np.nonzero(np.diff(vp) > 0)[0][:48]                     # viewpoints that see something, plus a few that do not
+    sel = np.concatenate([sel, np.nonzero(np.diff(vp) == 0)[0][:8]])
+    assert len(sel) > 20 and st.visible_pairs > 0
+    vp_o, idx_o, rays_o, _ = w.visibility(poses[sel], 58.0, 45.0, 0.7, 6.0, pts)
+    for k, v in enumerate(sel):
+        assert np.array_equal(idx[vp[v]:vp[v + 1]], idx_o[vp_o[k]:vp_o[k + 1]]), v
+    w.close()

@@ -150,3 +150,48 @@ def test_sensor_pose_composition(built):
     yaw = np.pi / 2
     out = host_lib.robot2sensor([1.0, 0, 0.5], [0, 0, 0], [[2, 3, 4, 0, 0, np.sin(yaw / 2), np.cos(yaw / 2)]])
     assert np.allclose(out[0, :3], [2, 4, 4.5], atol=1e-12)
+
+
+def test_file_formats_match_reference(ref, tmp_path):
+    """loadRegularGrid (three pose files in lock-step), saveSearchSpace (14 columns, 3 decimals) and
+    loadSearchSpace — including the reference's habit of pushing the last edge twice when the file ends
+    with a newline (src/pathplanner.cpp:319-356) — against the reference's own code"""
+    g = np.load(os.path.join(GOLD, "uav_fixture_R25.npz"))
+    poses = g["poses"][::-1][:400]                      # file order = insertion order = reverse list order
+    cams = [poses.copy(), poses.copy()]
+    cams[0][:, 2] -= 0.055
+    cams[1][:, 0] += 0.1
+    files = []
+    for k, arr in enumerate([poses] + cams):
+        fn = str(tmp_path / f"ss{k}.txt")
+        np.savetxt(fn, arr, fmt="%.6f")
+        files.append(fn)
+    r = ref.planner(2.5)
+    r.load_regular_grid(*files)
+    p = host_lib.HostPlanner(2.5)
+    p.load_regular_grid(*files)
+    (pr, ir), (ph, ih) = r.nodes(), p.nodes()
+    assert len(ph) > 50 and np.array_equal(ph, pr) and np.array_equal(ih, ir)
+    # same graph on both sides, then save with each implementation: identical bytes
+    r.connect()
+    rp, col = r.csr()
+    p.set_adjacency(rp, col)
+    p.connect()
+    f_ref, f_host = str(tmp_path / "ref_edges.txt"), str(tmp_path / "host_edges.txt")
+    r.save_search_space(f_ref)
+    p.save_search_space(f_host)
+    assert open(f_ref, "rb").read() == open(f_host, "rb").read() and os.path.getsize(f_ref) > 1000
+    # load the edge list back with each implementation: same nodes, same adjacency (3-decimal poses,
+    # last edge doubled)
+    r2 = ref.planner(2.5)
+    r2.load_search_space(f_ref)
+    p2 = host_lib.HostPlanner(2.5)
+    p2.load_search_space(f_ref)
+    (pr2, _), (ph2, _) = r2.nodes(), p2.nodes()
+    assert np.array_equal(ph2, pr2)
+    rp_r, col_r = r2.csr()
+    rp_h, col_h = p2.csr()
+    assert np.array_equal(rp_h, rp_r) and np.array_equal(col_h, col_r)
+    assert len(col_r) == len(col) + 1   # the doubled last edge
+    for x in (r, p, r2, p2):
+        x.close()
