@@ -35,6 +35,10 @@ class PathPlanner : public Astar {
   void loadRegularGrid(const char* robotFile, const char* sensor1File, const char* sensor2File);
   void saveSearchSpace(const char* filename);
   bool loadSearchSpace(const char* filename);
+  // lossless binary form of the whole graph: poses and sensor poses as doubles, ids,
+  // adjacency as CSR over list indices.  The text format above keeps three decimals and drops ids.
+  void saveSearchSpaceBinary(const char* filename);
+  bool loadSearchSpaceBinary(const char* filename);
 
   std::vector<Sensors> robotSensors;
   bool sampleOrientations = false, samplesFiltering = false, multiAgentSupport = false, insertSearchSpace = true;

@@ -186,6 +186,14 @@ int sspph_load_search_space(void* p, const char* fn) {
   Handle* h = (Handle*)p;
   GUARD(h, h->planner->loadSearchSpace(fn));
 }
+int sspph_save_binary(void* p, const char* fn) {
+  Handle* h = (Handle*)p;
+  GUARD(h, h->planner->saveSearchSpaceBinary(fn));
+}
+int sspph_load_binary(void* p, const char* fn) {
+  Handle* h = (Handle*)p;
+  GUARD(h, h->planner->loadSearchSpaceBinary(fn));
+}
 int64_t sspph_num_nodes(void* p) { return (int64_t)((Handle*)p)->planner->flatten().size(); }
 void sspph_get_nodes(void* p, double* poses, int32_t* ids) {
   Handle* h = (Handle*)p;

@@ -284,4 +284,93 @@ bool PathPlanner::loadSearchSpace(const char* fileName) {
   }
   return true;
 }
+// ---- lossless binary graph file ------------------------------------------------------------------
+// layout (little endian): magic "SSPPCSR1", u64 n, u64 E, u64 sensors_per_node, then per node in LIST
+// order: i32 id, 7 doubles pose, sensors_per_node x 7 doubles; then (n+1) i64 row_ptr, E i32 col_idx.
+namespace {
+const char kMagic[8] = {'S', 'S', 'P', 'P', 'C', 'S', 'R', '1'};
+void put_pose(std::ofstream& out, const geometry_msgs::Pose& p) {
+  const double v[7] = {p.position.x, p.position.y, p.position.z, p.orientation.x, p.orientation.y, p.orientation.z, p.orientation.w};
+  out.write((const char*)v, sizeof(v));
+}
+bool get_pose(std::ifstream& in, geometry_msgs::Pose& p) {
+  double v[7];
+  if (!in.read((char*)v, sizeof(v))) return false;
+  p.position.x = v[0]; p.position.y = v[1]; p.position.z = v[2];
+  p.orientation.x = v[3]; p.orientation.y = v[4]; p.orientation.z = v[5]; p.orientation.w = v[6];
+  return true;
+}
+}  // namespace
+
+void PathPlanner::saveSearchSpaceBinary(const char* filename) {
+  const std::vector<SearchSpaceNode*>& list = flatten();
+  std::ofstream out(filename, std::ios::binary);
+  if (!out) throw SSPPException(std::string("saveSearchSpaceBinary: cannot open ") + filename);
+  uint64_t n = list.size(), E = 0, ns = list.empty() ? 0 : list[0]->sensorLocation.poses.size();
+  for (SearchSpaceNode* t : list) {
+    E += t->children.size();
+    if (t->sensorLocation.poses.size() != ns) throw SSPPException("saveSearchSpaceBinary: nodes carry different numbers of sensor poses");
+  }
+  out.write(kMagic, 8);
+  out.write((const char*)&n, 8);
+  out.write((const char*)&E, 8);
+  out.write((const char*)&ns, 8);
+  for (SearchSpaceNode* t : list) {
+    int32_t id = t->id;
+    out.write((const char*)&id, 4);
+    put_pose(out, t->location);
+    for (const geometry_msgs::Pose& sp : t->sensorLocation.poses) put_pose(out, sp);
+  }
+  int64_t off = 0;
+  for (SearchSpaceNode* t : list) {
+    out.write((const char*)&off, 8);
+    off += (int64_t)t->children.size();
+  }
+  out.write((const char*)&off, 8);
+  for (SearchSpaceNode* t : list)
+    for (SearchSpaceNode* c : t->children) {
+      int32_t j = c->index;
+      out.write((const char*)&j, 4);
+    }
+}
+
+// replaces the current search space; the list order, the ids and the children order come back exactly
+bool PathPlanner::loadSearchSpaceBinary(const char* filename) {
+  std::ifstream in(filename, std::ios::binary);
+  if (!in) throw SSPPException(std::string("loadSearchSpaceBinary: cannot open ") + filename);
+  char magic[8];
+  uint64_t n = 0, E = 0, ns = 0;
+  if (!in.read(magic, 8) || memcmp(magic, kMagic, 8) != 0) throw SSPPException("loadSearchSpaceBinary: not an SSPPCSR1 file");
+  in.read((char*)&n, 8);
+  in.read((char*)&E, 8);
+  in.read((char*)&ns, 8);
+  std::vector<geometry_msgs::Pose> poses(n);
+  std::vector<geometry_msgs::PoseArray> sens(n);
+  std::vector<int32_t> ids(n);
+  for (uint64_t i = 0; i < n; ++i) {
+    if (!in.read((char*)&ids[i], 4) || !get_pose(in, poses[i])) throw SSPPException("loadSearchSpaceBinary: truncated node table");
+    sens[i].poses.resize(ns);
+    for (uint64_t k = 0; k < ns; ++k)
+      if (!get_pose(in, sens[i].poses[k])) throw SSPPException("loadSearchSpaceBinary: truncated node table");
+  }
+  std::vector<int64_t> rp(n + 1);
+  std::vector<int32_t> col(E);
+  if (!in.read((char*)rp.data(), (std::streamsize)((n + 1) * 8)) || (E && !in.read((char*)col.data(), (std::streamsize)(E * 4))))
+    throw SSPPException("loadSearchSpaceBinary: truncated adjacency");
+  if (rp[n] != (int64_t)E) throw SSPPException("loadSearchSpaceBinary: row_ptr and edge count disagree");
+  freeSearchSpace();
+  // head insertion reverses: insert from the tail of the stored list so the list order comes back
+  for (uint64_t i = n; i-- > 0;) {
+    SearchSpaceNode* t = insertNode(poses[i], sens[i], ids[i]);
+    if (t->id != ids[i]) throw SSPPException("loadSearchSpaceBinary: duplicate pose in file");
+  }
+  const std::vector<SearchSpaceNode*>& list = flatten();
+  for (uint64_t i = 0; i < n; ++i)
+    for (int64_t e = rp[i]; e < rp[i + 1]; ++e) {
+      if (col[e] < 0 || (uint64_t)col[e] >= n) throw SSPPException("loadSearchSpaceBinary: column index out of range");
+      list[i]->children.push_back(list[(size_t)col[e]]);
+    }
+  MAXNODES = (long)E;
+  return true;
+}
 }  // namespace SSPP

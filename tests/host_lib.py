@@ -46,6 +46,8 @@ def lib():
         L.sspph_load_regular_grid.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p]
         L.sspph_save_search_space.argtypes = [vp, ctypes.c_char_p]
         L.sspph_load_search_space.argtypes = [vp, ctypes.c_char_p]
+        L.sspph_save_binary.argtypes = [vp, ctypes.c_char_p]
+        L.sspph_load_binary.argtypes = [vp, ctypes.c_char_p]
         L.sspph_num_nodes.restype = i64
         L.sspph_num_nodes.argtypes = [vp]
         L.sspph_get_nodes.argtypes = [vp, vp, vp]
@@ -159,6 +161,12 @@ class HostPlanner:
 
     def load_search_space(self, fn):
         self._ck(self.L.sspph_load_search_space(self.h, fn.encode()))
+
+    def save_binary(self, fn):
+        self._ck(self.L.sspph_save_binary(self.h, fn.encode()))
+
+    def load_binary(self, fn):
+        self._ck(self.L.sspph_load_binary(self.h, fn.encode()))
 
     def nodes(self):
         n = self.L.sspph_num_nodes(self.h)

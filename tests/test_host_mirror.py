@@ -195,3 +195,30 @@ def test_file_formats_match_reference(ref, tmp_path):
     assert len(col_r) == len(col) + 1   # the doubled last edge
     for x in (r, p, r2, p2):
         x.close()
+
+
+def test_binary_graph_file_round_trip(built, tmp_path):
+    """the lossless binary dump brings back list order, ids, full-precision poses and the children order;
+    A* over the reloaded graph walks the same path"""
+    g = np.load(os.path.join(GOLD, "dht_known_answer.npz"))
+    p = host_lib.HostPlanner(1.5)
+    p.generate_grid([0, 0, 0], [10, 10, 2], 1.0, True, 90.0)
+    p.set_adjacency(g["row_ptr"], g["col_idx"])
+    p.connect()
+    fn = str(tmp_path / "graph.ssppcsr")
+    p.save_binary(fn)
+    q = host_lib.HostPlanner(1.5)
+    q.load_binary(fn)
+    (pp, ip), (pq, iq) = p.nodes(), q.nodes()
+    assert np.array_equal(pp, pq) and np.array_equal(ip, iq)
+    rp, col = q.csr()
+    assert np.array_equal(rp, g["row_ptr"]) and np.array_equal(col, g["col_idx"])
+    q.set_goal([4, 4, 2, 0, 0, 0, 0], 1.0)
+    path, created, expanded, _ = q.astar([0, 0, 0, 0, 0, 0, 0])
+    assert np.array_equal(path, g["path"]) and (created, expanded) == (9480, 153)
+    with open(fn, "r+b") as f:
+        f.write(b"XXXX")
+    with pytest.raises(host_lib.HostError):
+        host_lib.HostPlanner(1.5).load_binary(fn)
+    p.close()
+    q.close()
