@@ -165,6 +165,18 @@ void ref_load_search_space(void* h, const char* fn) {
   ((RefPlanner*)h)->planner->loadSearchSpace(fn);
 }
 
+// PathPlanner::connectToNN (src/pathplanner.cpp:658-763) with the kd-tree stand-in (exact brute-force 1-NN)
+void ref_connect_to_nn(void* h, const float* hull1, long n1, const float* hull2, long n2, float orient_res) {
+  Quiet q;
+  RefPlanner* R = (RefPlanner*)h;
+  R->planner->orientationResolution = orient_res;
+  pcl::PointCloud<pcl::PointXYZ> a, b;
+  for (long i = 0; i < n1; ++i) a.push_back(pcl::PointXYZ(hull1[3 * i], hull1[3 * i + 1], hull1[3 * i + 2]));
+  for (long i = 0; i < n2; ++i) b.push_back(pcl::PointXYZ(hull2[3 * i], hull2[3 * i + 1], hull2[3 * i + 2]));
+  R->planner->connectToNN(a, b);
+}
+long ref_maxnodes(void* h) { return ((RefPlanner*)h)->planner->MAXNODES; }
+
 void ref_disconnect(void* h) { ((RefPlanner*)h)->planner->disconnectNodes(); }
 
 // runs the reference's O(N^2) connectNodes; returns MAXNODES (= connection count it printed)

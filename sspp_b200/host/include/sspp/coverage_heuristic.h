@@ -35,8 +35,23 @@ class CoverageHeuristic : public DistanceHeuristic {
                                      double maxDist, pcl::PointCloud<pcl::PointXYZ>& globalCloud,
                                      std::vector<pcl::PointCloud<pcl::PointXYZ> >& accuracyClusters,
                                      double accuracyThreshhold) override;
-  // share of the model not yet covered by the union of `waypoints`' visible sets (pointCloudDiff of the interface)
+  // share of the model not yet covered by the union of `waypoints`' visible sets
   double uncoveredShare(const std::vector<const SearchSpaceNode*>& waypoints);
+  // batched sample filter: validity of every sample (one call), visibility of the valid ones' sensor poses
+  // (one call); kept samples add what they see to the running coverage of the sampling loop
+  bool filterAllPoses(const std::vector<geometry_msgs::Pose>& poses, const std::vector<geometry_msgs::PoseArray>& sensorPoses,
+                      std::vector<uint8_t>& valid) override;
+  // uncovered share of the model after the samples kept so far; diff = the uncovered model points
+  double pointCloudDiff(pcl::PointCloud<pcl::PointXYZ>::Ptr globalCloudPtr, pcl::PointCloud<pcl::PointXYZ>::Ptr& pointCloudDiffPtr) override;
+  // Euclidean clusters (connected components of the radius graph at `clusterTolerance`) of at least minClusterSize points
+  void clusteringPointCloud(std::vector<pcl::PointCloud<pcl::PointXYZ> >& clusters, pcl::PointCloud<pcl::PointXYZ>::Ptr diff) override;
+  // sampling box of a cluster: its bounding box grown by `standoff` on every side
+  void findClusterBB(pcl::PointCloud<pcl::PointXYZ> cluster, geometry_msgs::Vector3& gridSize, geometry_msgs::Pose& gridStart) override;
+  void setClustering(double tolerance, int minSize) { clusterTolerance = tolerance; minClusterSize = minSize; }
+  void setStandoff(double d) { standoff = d; }
+  void resetCoverage() { std::fill(covered_.begin(), covered_.end(), 0); coveredCount = 0; }
+  int64_t coveredCount = 0;   // model points seen by the samples kept so far
+  std::vector<int32_t> clusterLabels(const float* xyz, int64_t n);  // component label per point (-1 = dropped as too small)
   const std::vector<int32_t>& visibleFrom(const SearchSpaceNode* wp);
   int64_t raysCast = 0;        // occlusion rays cast so far
   int64_t visibilityCalls = 0; // batched engine calls so far
@@ -47,6 +62,10 @@ class CoverageHeuristic : public DistanceHeuristic {
   double hfov = 58.0, vfov = 45.0, nearD = 0.7, farD = 6.0;
   double coverageTarget = 100.0, coverageTolerance = 0.0;
   std::unordered_map<const SearchSpaceNode*, std::vector<int32_t> > seen_;  // way-point -> sorted visible indices
+  std::vector<float> model_;        // host copy of the model points (pointCloudDiff hands the uncovered ones back)
+  std::vector<uint8_t> covered_;    // per model point: seen by a kept sample
+  double clusterTolerance = 0.6, standoff = 3.0;
+  int minClusterSize = 10;
   void ensureVisible(const std::vector<const SearchSpaceNode*>& wps);
   void score(Node* n);
 };

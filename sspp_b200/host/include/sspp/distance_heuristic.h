@@ -34,6 +34,7 @@ class DistanceHeuristic : public Heuristic {
   bool connectAll(const double* xyz, int64_t n, double radius, int position_mode, std::vector<int64_t>& row_ptr,
                   std::vector<int32_t>& col) override;
   bool filterAll(const double* xyz, int64_t n, std::vector<uint8_t>& valid) override;
+  void connectionConditionAll(const double* starts, const double* ends, int64_t n, std::vector<uint8_t>& ok) override;
   // node validity is an extension (the reference answers true): off unless asked for
   void setFilterByValidity(bool on) { filterByValidity = on; }
   // false = the manager==NULL behaviour of the reference (every in-radius pair accepted) while still

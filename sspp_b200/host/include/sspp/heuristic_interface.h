@@ -41,10 +41,25 @@ class Heuristic {
   // xyz: n x 3 positions in list order; row_ptr: n+1; col: filled with list indices.
   virtual bool connectAll(const double* /*xyz*/, int64_t /*n*/, double /*radius*/, int /*position_mode*/,
                           std::vector<int64_t>& /*row_ptr*/, std::vector<int32_t>& /*col*/) { return false; }
+  // isConnectionConditionSatisfied for n segments (positions only) in one call.  Default: the per-pair virtual.
+  virtual void connectionConditionAll(const double* starts, const double* ends, int64_t n, std::vector<uint8_t>& ok) {
+    ok.assign((size_t)n, 0);
+    for (int64_t i = 0; i < n; ++i) {
+      geometry_msgs::Pose a, b;
+      a.position.x = starts[3 * i]; a.position.y = starts[3 * i + 1]; a.position.z = starts[3 * i + 2];
+      b.position.x = ends[3 * i]; b.position.y = ends[3 * i + 1]; b.position.z = ends[3 * i + 2];
+      ok[(size_t)i] = isConnectionConditionSatisfied(a, b) ? 1 : 0;
+    }
+  }
   // calculateHeuristic for all children of one expansion, in the order the search will consume them.
   // Default: one call per node, exactly what the reference's loop does (src/astar.cpp:318).
   virtual void calculateHeuristicAll(std::vector<Node*>& nodes) {
     for (Node* n : nodes) calculateHeuristic(n);
+  }
+  // isFilteringConditionSatisfied for many samples with their sensor poses in one call; false = not offered.
+  virtual bool filterAllPoses(const std::vector<geometry_msgs::Pose>& /*poses*/,
+                              const std::vector<geometry_msgs::PoseArray>& /*sensorPoses*/, std::vector<uint8_t>& /*valid*/) {
+    return false;
   }
   // Validity of many poses in one call (isFilteringConditionSatisfied batched); false = not offered.
   virtual bool filterAll(const double* /*xyz*/, int64_t /*n*/, std::vector<uint8_t>& /*valid*/) { return false; }

@@ -26,6 +26,13 @@ class PathPlanner : public Astar {
                            bool insertSearchSpace = true);
   void connectNodes();
   void connectClustersInternalNodes(SearchSpaceNode* space, double connRadius);
+  // links every point of cloudHull2 to its nearest point of cloudHull1, in all yaw combinations
+  void connectToNN(pcl::PointCloud<pcl::PointXYZ> cloudHull1, pcl::PointCloud<pcl::PointXYZ> cloudHull2);
+  // coverage-driven refinement: sample, connect, find what is still uncovered, cluster it, re-sample the
+  // clusters at a finer resolution, connect each stage to the previous one; until <= 1 % is uncovered
+  void dynamicNodesGenerationAndConnection(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize, double startRes,
+                                           double resDecrement);
+  long checkSearchSpaceDuplications();
   void disconnectNodes();
   void blockPath(Node* path);
   Node* startSearch(Pose startPose);

@@ -42,8 +42,8 @@ class InjectedHeuristic : public DistanceHeuristic {
 };
 }  // namespace
 
-#define GUARD(h, body)                         \
-  try { body; return 0; }                      \
+#define GUARD(h, ...)                          \
+  try { __VA_ARGS__; return 0; }               \
   catch (const std::exception& e) { (h)->err = e.what(); return 1; }
 
 extern "C" {
@@ -216,6 +216,52 @@ int sspph_set_adjacency(void* p, const int64_t* row_ptr, const int32_t* col, int
   ih->cl.assign(col, col + row_ptr[n]);
   return 0;
 }
+int sspph_connect_to_nn(void* p, const float* hull1, int64_t n1, const float* hull2, int64_t n2, float orient_res) {
+  Handle* h = (Handle*)p;
+  GUARD(h, {
+    h->planner->orientationResolution = orient_res;
+    pcl::PointCloud<pcl::PointXYZ> a, b;
+    for (int64_t i = 0; i < n1; ++i) a.push_back(pcl::PointXYZ(hull1[3 * i], hull1[3 * i + 1], hull1[3 * i + 2]));
+    for (int64_t i = 0; i < n2; ++i) b.push_back(pcl::PointXYZ(hull2[3 * i], hull2[3 * i + 1], hull2[3 * i + 2]));
+    h->planner->connectToNN(a, b);
+  });
+}
+int64_t sspph_maxnodes(void* p) { return ((Handle*)p)->planner->MAXNODES; }
+int64_t sspph_duplicate_edges(void* p) { return ((Handle*)p)->planner->checkSearchSpaceDuplications(); }
+
+// coverage-driven dynamic sampling (PathPlanner::dynamicNodesGenerationAndConnection); out: [0] nodes, [1] MAXNODES,
+// [2] model points covered by the kept samples
+int sspph_dynamic_sampling(void* p, const double start[3], const double size[3], double start_res, double res_decrement,
+                           int64_t out[3]) {
+  Handle* h = (Handle*)p;
+  if (!h->coverage) { h->err = "not a coverage planner"; return 1; }
+  geometry_msgs::Pose s;
+  s.position.x = start[0]; s.position.y = start[1]; s.position.z = start[2];
+  geometry_msgs::Vector3 z;
+  z.x = size[0]; z.y = size[1]; z.z = size[2];
+  GUARD(h, {
+    h->planner->dynamicNodesGenerationAndConnection(s, z, start_res, res_decrement);
+    out[0] = (int64_t)h->planner->flatten().size();
+    out[1] = h->planner->MAXNODES;
+    out[2] = h->coverage->coveredCount;
+  });
+}
+int sspph_set_clustering(void* p, double tolerance, int min_size, double standoff) {
+  Handle* h = (Handle*)p;
+  if (!h->coverage) { h->err = "not a coverage planner"; return 1; }
+  h->coverage->setClustering(tolerance, min_size);
+  h->coverage->setStandoff(standoff);
+  return 0;
+}
+int sspph_cluster_labels(void* p, const float* xyz, int64_t n, int32_t* labels) {
+  Handle* h = (Handle*)p;
+  if (!h->coverage) { h->err = "not a coverage planner"; return 1; }
+  GUARD(h, {
+    std::vector<int32_t> l = h->coverage->clusterLabels(xyz, n);
+    for (int64_t i = 0; i < n; ++i) labels[i] = l[(size_t)i];
+  });
+}
+
 void sspph_disconnect(void* p) { ((Handle*)p)->planner->disconnectNodes(); }
 int sspph_connect(void* p, int64_t* n_edges, int64_t* tested) {
   Handle* h = (Handle*)p;

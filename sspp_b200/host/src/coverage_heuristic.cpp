@@ -12,6 +12,9 @@ void CoverageHeuristic::setModelPoints(const float* xyz, int64_t n) {
   world_->setModelPoints(xyz, n);
   modelSize = n;
   seen_.clear();
+  model_.assign(xyz, xyz + 3 * n);
+  covered_.assign((size_t)n, 0);
+  coveredCount = 0;
 }
 
 void CoverageHeuristic::setFrustum(double h, double v, double n, double f) {
@@ -126,5 +129,113 @@ double CoverageHeuristic::uncoveredShare(const std::vector<const SearchSpaceNode
     u.swap(m);
   }
   return modelSize ? 1.0 - (double)u.size() / (double)modelSize : 0.0;
+}
+bool CoverageHeuristic::filterAllPoses(const std::vector<geometry_msgs::Pose>& poses, const std::vector<geometry_msgs::PoseArray>& sensorPoses,
+                                       std::vector<uint8_t>& valid) {
+  const size_t n = poses.size();
+  valid.assign(n, 0);
+  if (n == 0) return true;
+  std::vector<uint8_t> st(n, GpuWorld::kFree);
+  if (world_->hasMap()) {
+    std::vector<double> xyz(n * 3);
+    for (size_t i = 0; i < n; ++i) { xyz[3 * i] = poses[i].position.x; xyz[3 * i + 1] = poses[i].position.y; xyz[3 * i + 2] = poses[i].position.z; }
+    const double box[3] = {0.5, 0.5, 0.3};
+    world_->validity(xyz.data(), (int64_t)n, box, st.data());
+  }
+  std::vector<double> sp;
+  std::vector<size_t> owner;
+  for (size_t i = 0; i < n; ++i) {
+    if (st[i] != GpuWorld::kFree) continue;
+    for (const geometry_msgs::Pose& s : sensorPoses[i].poses) {
+      const double v[7] = {s.position.x, s.position.y, s.position.z, s.orientation.x, s.orientation.y, s.orientation.z, s.orientation.w};
+      sp.insert(sp.end(), v, v + 7);
+      owner.push_back(i);
+    }
+  }
+  if (owner.empty()) return true;
+  std::vector<int64_t> view_ptr;
+  std::vector<int32_t> idx;
+  int64_t rays = 0;
+  world_->visibility(sp.data(), (int64_t)owner.size(), hfov, vfov, nearD, farD, view_ptr, idx, &rays);
+  raysCast += rays;
+  ++visibilityCalls;
+  for (size_t v = 0; v < owner.size(); ++v) {
+    if (view_ptr[v + 1] == view_ptr[v]) continue;
+    valid[owner[v]] = 1;
+    for (int64_t e = view_ptr[v]; e < view_ptr[v + 1]; ++e)
+      if (!covered_[(size_t)idx[(size_t)e]]) { covered_[(size_t)idx[(size_t)e]] = 1; ++coveredCount; }
+  }
+  return true;
+}
+
+double CoverageHeuristic::pointCloudDiff(pcl::PointCloud<pcl::PointXYZ>::Ptr, pcl::PointCloud<pcl::PointXYZ>::Ptr& diff) {
+  if (!diff) diff.reset(new pcl::PointCloud<pcl::PointXYZ>);
+  diff->points.clear();
+  for (int64_t i = 0; i < modelSize; ++i)
+    if (!covered_[(size_t)i]) diff->points.push_back(pcl::PointXYZ(model_[3 * i], model_[3 * i + 1], model_[3 * i + 2]));
+  return modelSize ? (double)diff->points.size() / (double)modelSize : 0.0;
+}
+
+// connected components of the radius graph, built by the engine's own radius search (no map)
+std::vector<int32_t> CoverageHeuristic::clusterLabels(const float* xyz, int64_t n) {
+  std::vector<int32_t> label((size_t)n, -1);
+  if (n == 0) return label;
+  std::vector<double> d((size_t)n * 3);
+  for (int64_t i = 0; i < 3 * n; ++i) d[(size_t)i] = xyz[i];
+  std::vector<int64_t> rp;
+  std::vector<int32_t> col;
+  const double box[3] = {0, 0, 0};
+  world_->connect(d.data(), n, clusterTolerance, box, false, 0, rp, col);
+  std::vector<int32_t> stack;
+  int32_t next = 0;
+  for (int64_t s = 0; s < n; ++s) {
+    if (label[(size_t)s] != -1) continue;
+    std::vector<int32_t> members;
+    stack.assign(1, (int32_t)s);
+    label[(size_t)s] = -2;
+    while (!stack.empty()) {
+      int32_t u = stack.back();
+      stack.pop_back();
+      members.push_back(u);
+      for (int64_t e = rp[(size_t)u]; e < rp[(size_t)u + 1]; ++e) {
+        int32_t v = col[(size_t)e];
+        if (label[(size_t)v] == -1) { label[(size_t)v] = -2; stack.push_back(v); }
+      }
+    }
+    const int32_t id = ((int)members.size() >= minClusterSize) ? next++ : -3;
+    for (int32_t m : members) label[(size_t)m] = id;
+  }
+  for (int32_t& l : label) if (l == -3) l = -1;
+  return label;
+}
+
+void CoverageHeuristic::clusteringPointCloud(std::vector<pcl::PointCloud<pcl::PointXYZ> >& clusters, pcl::PointCloud<pcl::PointXYZ>::Ptr diff) {
+  clusters.clear();
+  if (!diff || diff->points.empty()) return;
+  const int64_t n = (int64_t)diff->points.size();
+  std::vector<float> xyz((size_t)n * 3);
+  for (int64_t i = 0; i < n; ++i) { xyz[3 * i] = diff->points[(size_t)i].x; xyz[3 * i + 1] = diff->points[(size_t)i].y; xyz[3 * i + 2] = diff->points[(size_t)i].z; }
+  std::vector<int32_t> label = clusterLabels(xyz.data(), n);
+  int32_t k = -1;
+  for (int32_t l : label) k = std::max(k, l);
+  clusters.resize((size_t)(k + 1));
+  for (int64_t i = 0; i < n; ++i)
+    if (label[(size_t)i] >= 0) clusters[(size_t)label[(size_t)i]].push_back(diff->points[(size_t)i]);
+}
+
+void CoverageHeuristic::findClusterBB(pcl::PointCloud<pcl::PointXYZ> cluster, geometry_msgs::Vector3& gridSize, geometry_msgs::Pose& gridStart) {
+  if (cluster.points.empty()) { gridSize = geometry_msgs::Vector3(); return; }
+  double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+  for (const pcl::PointXYZ& p : cluster.points) {
+    const double v[3] = {p.x, p.y, p.z};
+    for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], v[a]); hi[a] = std::max(hi[a], v[a]); }
+  }
+  gridStart.position.x = 0.5 * (lo[0] + hi[0]);
+  gridStart.position.y = 0.5 * (lo[1] + hi[1]);
+  gridStart.position.z = 0.5 * (lo[2] + hi[2]);
+  gridStart.orientation.w = 1;
+  gridSize.x = (hi[0] - lo[0]) + 2 * standoff;
+  gridSize.y = (hi[1] - lo[1]) + 2 * standoff;
+  gridSize.z = (hi[2] - lo[2]) + 2 * standoff;
 }
 }  // namespace SSPP

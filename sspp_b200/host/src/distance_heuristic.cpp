@@ -51,6 +51,14 @@ bool DistanceHeuristic::connectAll(const double* xyz, int64_t n, double radius, 
   return true;
 }
 
+void DistanceHeuristic::connectionConditionAll(const double* starts, const double* ends, int64_t n, std::vector<uint8_t>& ok) {
+  ok.assign((size_t)n, 1);
+  if (!world || !world->hasMap() || !useMap || n == 0) return;  // manager == NULL: every pair passes
+  std::vector<uint8_t> st((size_t)n);
+  world->checkSegments(starts, ends, n, box, st.data());
+  for (int64_t i = 0; i < n; ++i) ok[(size_t)i] = st[(size_t)i] == GpuWorld::kFree;
+}
+
 bool DistanceHeuristic::filterAll(const double* xyz, int64_t n, std::vector<uint8_t>& valid) {
   valid.assign((size_t)n, 1);
   if (!filterByValidity || !world || n == 0) return true;

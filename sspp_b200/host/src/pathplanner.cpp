@@ -1,6 +1,7 @@
 // PathPlanner (reference src/pathplanner.cpp).  Cited lines are the reference's.
 #include "sspp/pathplanner.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -86,19 +87,24 @@ void PathPlanner::generateRegularGrid(geometry_msgs::Pose gridStartPose, geometr
           samples.push_back(pose);
         }
       }
+  std::vector<geometry_msgs::PoseArray> sensorPosesAll(samples.size());
+  for (size_t i = 0; i < samples.size(); ++i)
+    for (size_t j = 0; j < robotSensors.size(); ++j) sensorPosesAll[i].poses.push_back(robotSensors[j].robot2sensorTransformation(samples[i]));
   std::vector<uint8_t> keep(samples.size(), 1);
   const bool filter_here = samplesFiltering && sampleOrientations;  // the reference filters only in the orientation branch (:151)
   bool batched = false;
   if (filter_here && heuristic) {
-    std::vector<double> xyz(samples.size() * 3);
-    for (size_t i = 0; i < samples.size(); ++i) {
-      xyz[3 * i] = samples[i].position.x; xyz[3 * i + 1] = samples[i].position.y; xyz[3 * i + 2] = samples[i].position.z;
+    batched = heuristic->filterAllPoses(samples, sensorPosesAll, keep);
+    if (!batched) {
+      std::vector<double> xyz(samples.size() * 3);
+      for (size_t i = 0; i < samples.size(); ++i) {
+        xyz[3 * i] = samples[i].position.x; xyz[3 * i + 1] = samples[i].position.y; xyz[3 * i + 2] = samples[i].position.z;
+      }
+      batched = heuristic->filterAll(xyz.data(), (int64_t)samples.size(), keep);
     }
-    batched = heuristic->filterAll(xyz.data(), (int64_t)samples.size(), keep);
   }
   for (size_t i = 0; i < samples.size(); ++i) {
-    geometry_msgs::PoseArray sensorPoses;
-    for (size_t j = 0; j < robotSensors.size(); ++j) sensorPoses.poses.push_back(robotSensors[j].robot2sensorTransformation(samples[i]));
+    geometry_msgs::PoseArray& sensorPoses = sensorPosesAll[i];
     if (filter_here) {
       const double desiredMaxDepth = 6.9;
       const double maxErrorThresh = 0.0000285 * desiredMaxDepth * desiredMaxDepth;
@@ -165,6 +171,128 @@ void PathPlanner::connectClustersInternalNodes(SearchSpaceNode* space, double co
       ++added;
     }
   MAXNODES += added;
+}
+
+// number of repeated (parent pose, child pose) connections (:569-610; the reference prints it, O(E^2);
+// here a sort of the index pairs)
+long PathPlanner::checkSearchSpaceDuplications() {
+  const std::vector<SearchSpaceNode*>& list = flatten();
+  std::vector<std::pair<int, int> > e;
+  for (SearchSpaceNode* t : list)
+    for (SearchSpaceNode* c : t->children) e.push_back(std::make_pair(t->index, c->index));
+  std::sort(e.begin(), e.end());
+  long dup = 0;
+  for (size_t i = 1; i < e.size(); ++i) dup += (e[i] == e[i - 1]);
+  return dup;
+}
+
+// For every point of hull 2 its nearest point of hull 1 (the reference asks a kd-tree for the 1-NN;
+// squared float distances, first minimum wins), then every yaw of the one against every yaw of the
+// other: nodes that exist in the search space are linked in both directions when the straight segment
+// passes the heuristic's connection test — one batched test for all segments instead of one per yaw
+// pair, the test only depends on the positions (:658-763).
+void PathPlanner::connectToNN(pcl::PointCloud<pcl::PointXYZ> hull1, pcl::PointCloud<pcl::PointXYZ> hull2) {
+  if (hull1.points.empty() || hull2.points.empty()) return;
+  if (!heuristic) throw SSPPException("connectToNN: no heuristic set");
+  const size_t n2 = hull2.points.size();
+  std::vector<int> nn(n2);
+  for (size_t i = 0; i < n2; ++i) {
+    const pcl::PointXYZ& q = hull2.points[i];
+    int best = 0;
+    float bd = -1;
+    for (size_t j = 0; j < hull1.points.size(); ++j) {
+      const pcl::PointXYZ& p = hull1.points[j];
+      float d = (p.x - q.x) * (p.x - q.x) + (p.y - q.y) * (p.y - q.y) + (p.z - q.z) * (p.z - q.z);
+      if (bd < 0 || d < bd) { bd = d; best = (int)j; }
+    }
+    nn[i] = best;
+  }
+  std::vector<double> starts(n2 * 3), ends(n2 * 3);
+  for (size_t i = 0; i < n2; ++i) {
+    const pcl::PointXYZ& q = hull2.points[i];
+    const pcl::PointXYZ& p = hull1.points[(size_t)nn[i]];
+    starts[3 * i] = q.x; starts[3 * i + 1] = q.y; starts[3 * i + 2] = q.z;   // node -> nearest, as the reference calls it
+    ends[3 * i] = p.x; ends[3 * i + 1] = p.y; ends[3 * i + 2] = p.z;
+  }
+  std::vector<uint8_t> ok;
+  heuristic->connectionConditionAll(starts.data(), ends.data(), (int64_t)n2, ok);
+  const int orientationsNum = 360.0f / orientationResolution;
+  long numConnections = 0;
+  for (size_t i = 0; i < n2; ++i) {
+    geometry_msgs::Pose node, nearest;
+    node.position.x = starts[3 * i]; node.position.y = starts[3 * i + 1]; node.position.z = starts[3 * i + 2];
+    nearest.position.x = ends[3 * i]; nearest.position.y = ends[3 * i + 1]; nearest.position.z = ends[3 * i + 2];
+    const bool same_place = isPositionEqual(node.position, nearest.position);
+    double yaw1 = 0.0;
+    for (int k = 0; k < orientationsNum; ++k) {
+      node.orientation = quaternion_from_yaw(yaw1);
+      double yaw2 = 0.0;
+      for (int m = 0; m < orientationsNum; ++m) {
+        nearest.orientation = quaternion_from_yaw(yaw2);
+        yaw2 += (orientationResolution * M_PI / 180.0f);
+        if (samePosition(node, nearest)) continue;
+        if (!same_place && !ok[i]) continue;
+        SearchSpaceNode* a = nodeExists(node);
+        SearchSpaceNode* b = nodeExists(nearest);
+        if (a && b) {
+          a->children.push_back(b);
+          b->children.push_back(a);
+          numConnections += 2;
+        }
+      }
+      yaw1 += (orientationResolution * M_PI / 180.0f);
+    }
+  }
+  MAXNODES += numConnections;
+}
+
+// (:765-891) with the coverage heuristic's pointCloudDiff / clusteringPointCloud / findClusterBB
+void PathPlanner::dynamicNodesGenerationAndConnection(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize, double startRes,
+                                                      double resDecrement) {
+  if (!heuristic) throw SSPPException("dynamicNodesGenerationAndConnection: no heuristic set");
+  double res = startRes;
+  generateRegularGrid(gridStartPose, gridSize, (float)startRes, true, 45, true, true);
+  SearchSpaceNode* S = insertTempSearchSpace(robotFilteredPoses, sensorsFilteredPoses);
+  double connRadius = std::sqrt((res * res) + (res * res)) + 0.01;
+  connectClustersInternalNodes(S, connRadius);
+  freeTempSearchSpace(S);
+  pcl::PointCloud<pcl::PointXYZ> hullCloud1;
+  for (const geometry_msgs::Pose& p : robotFilteredPoses.poses) hullCloud1.push_back(pcl::PointXYZ((float)p.position.x, (float)p.position.y, (float)p.position.z));
+  robotFilteredPoses.poses.clear();
+  sensorsFilteredPoses.clear();
+  for (;;) {
+    pcl::PointCloud<pcl::PointXYZ>::Ptr globalCloudPtr(new pcl::PointCloud<pcl::PointXYZ>);
+    globalCloudPtr->points = globalCloud.points;
+    pcl::PointCloud<pcl::PointXYZ>::Ptr diffPtr(new pcl::PointCloud<pcl::PointXYZ>);
+    const double uncovered = heuristic->pointCloudDiff(globalCloudPtr, diffPtr);
+    if (uncovered <= 0.01) break;
+    std::vector<pcl::PointCloud<pcl::PointXYZ> > clusters;
+    heuristic->clusteringPointCloud(clusters, diffPtr);
+    for (size_t i = 0; i < accuracyClusters.size(); ++i) clusters.push_back(accuracyClusters[i]);
+    accuracyClusters.clear();
+    res -= resDecrement;
+    connRadius = std::sqrt((res * res) + (res * res)) + 0.01;
+    if (!(res > 0)) break;
+    pcl::PointCloud<pcl::PointXYZ> clustersCloudHull;
+    for (size_t i = 0; i < clusters.size(); ++i) {
+      geometry_msgs::Pose clusterGridStart;
+      geometry_msgs::Vector3 clusterGridSize;
+      heuristic->findClusterBB(clusters[i], clusterGridSize, clusterGridStart);
+      for (size_t j = sensorsFilteredPoses.size(); j < robotSensors.size(); ++j) sensorsFilteredPoses.push_back(geometry_msgs::PoseArray());
+      generateRegularGrid(clusterGridStart, clusterGridSize, (float)res, true, 45, true, true);
+      if (robotFilteredPoses.poses.size() > 1) {
+        SearchSpaceNode* T = insertTempSearchSpace(robotFilteredPoses, sensorsFilteredPoses);
+        connectClustersInternalNodes(T, connRadius);
+        freeTempSearchSpace(T);
+      }
+      for (const geometry_msgs::Pose& p : robotFilteredPoses.poses)
+        clustersCloudHull.push_back(pcl::PointXYZ((float)p.position.x, (float)p.position.y, (float)p.position.z));
+      robotFilteredPoses.poses.clear();
+      sensorsFilteredPoses.clear();
+    }
+    connectToNN(hullCloud1, clustersCloudHull);
+    hullCloud1.points = clustersCloudHull.points;
+  }
 }
 
 void PathPlanner::disconnectNodes() {

@@ -60,6 +60,14 @@ def lib():
         L.sspph_astar.restype = i64
         L.sspph_astar.argtypes = [vp, vp, vp, i64, vp, vp, i64]
         L.sspph_robot2sensor.argtypes = [vp, vp, vp, i64, vp]
+        L.sspph_connect_to_nn.argtypes = [vp, vp, i64, vp, i64, ctypes.c_float]
+        L.sspph_maxnodes.restype = i64
+        L.sspph_maxnodes.argtypes = [vp]
+        L.sspph_duplicate_edges.restype = i64
+        L.sspph_duplicate_edges.argtypes = [vp]
+        L.sspph_dynamic_sampling.argtypes = [vp, vp, vp, ctypes.c_double, ctypes.c_double, vp]
+        L.sspph_set_clustering.argtypes = [vp, ctypes.c_double, ctypes.c_int, ctypes.c_double]
+        L.sspph_cluster_labels.argtypes = [vp, vp, i64, vp]
         L.sspph_create_coverage.restype = vp
         L.sspph_create_coverage.argtypes = [ctypes.c_double, ctypes.c_int, vp, vp] + [ctypes.c_double] * 4
         L.sspph_set_model_points.argtypes = [vp, vp, i64]
@@ -141,6 +149,31 @@ class HostPlanner:
         c = np.zeros(2, dtype=np.int64)
         self.L.sspph_coverage_counters(self.h, _p(c))
         return int(c[0]), int(c[1])
+
+    def connect_to_nn(self, hull1, hull2, orient_res):
+        a = np.ascontiguousarray(hull1, dtype=np.float32).reshape(-1, 3)
+        b = np.ascontiguousarray(hull2, dtype=np.float32).reshape(-1, 3)
+        self._ck(self.L.sspph_connect_to_nn(self.h, _p(a), len(a), _p(b), len(b), orient_res))
+
+    def maxnodes(self):
+        return self.L.sspph_maxnodes(self.h)
+
+    def duplicate_edges(self):
+        return self.L.sspph_duplicate_edges(self.h)
+
+    def dynamic_sampling(self, start, size, start_res, res_decrement):
+        out = np.zeros(3, dtype=np.int64)
+        self._ck(self.L.sspph_dynamic_sampling(self.h, _p(_f64(start)), _p(_f64(size)), start_res, res_decrement, _p(out)))
+        return int(out[0]), int(out[1]), int(out[2])
+
+    def set_clustering(self, tolerance, min_size, standoff):
+        self._ck(self.L.sspph_set_clustering(self.h, tolerance, min_size, standoff))
+
+    def cluster_labels(self, pts):
+        a = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+        lab = np.zeros(len(a), dtype=np.int32)
+        self._ck(self.L.sspph_cluster_labels(self.h, _p(a), len(a), _p(lab)))
+        return lab
 
     def set_filter_by_validity(self, on):
         self.L.sspph_set_filter_by_validity(self.h, int(bool(on)))

@@ -192,6 +192,14 @@ class RefPlanner:
     def load_search_space(self, fn):
         self.L.ref_load_search_space(self.h, fn.encode())
 
+    def connect_to_nn(self, hull1, hull2, orient_res):
+        a = np.ascontiguousarray(hull1, dtype=np.float32).reshape(-1, 3)
+        b = np.ascontiguousarray(hull2, dtype=np.float32).reshape(-1, 3)
+        self.L.ref_connect_to_nn(self.h, _p(a), len(a), _p(b), len(b), orient_res)
+
+    def maxnodes(self):
+        return self.L.ref_maxnodes(self.h)
+
     def disconnect(self):
         self.L.ref_disconnect(self.h)
 
@@ -263,6 +271,9 @@ class Oracle:
             L.ref_num_nodes.argtypes = [vp]
             L.ref_get_nodes.argtypes = [vp, vp, vp]
             L.ref_disconnect.argtypes = [vp]
+            L.ref_connect_to_nn.argtypes = [vp, vp, lng, vp, lng, ctypes.c_float]
+            L.ref_maxnodes.restype = lng
+            L.ref_maxnodes.argtypes = [vp]
             L.ref_load_regular_grid.argtypes = [vp, ctypes.c_char_p, ctypes.c_char_p, ctypes.c_char_p]
             L.ref_save_search_space.argtypes = [vp, ctypes.c_char_p]
             L.ref_load_search_space.argtypes = [vp, ctypes.c_char_p]

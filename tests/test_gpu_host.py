@@ -139,3 +139,91 @@ def test_casarea_scenario_through_the_mirror(eng):
     assert len(path) > 5 and np.array_equal(path, g["path"])
     assert (created, expanded) == (int(g["created"]), int(g["expanded"]))
     p.close()
+
+
+def test_connect_to_nn_with_map_matches_reference(eng, ref):
+    """connectToNN with a map behind the heuristic: the reference tests every yaw pair through
+    getLineStatusBoundingBox; the mirror tests each segment once on the GPU — same links"""
+    from sspp_b200 import scenes
+    res = 0.3
+    km, dm, occ, known = scenes.synthetic_map(n_vox=64, res=res, seed=13, n_boxes=14, n_spheres=8, region=16.0)
+    w = ref.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    r = ref.planner(1.5, w)
+    p = host_lib.HostPlanner(1.5, device=0)
+    p.map_create(res, km, dm, True)
+    p.map_upload_dense(occ, known)
+    for pl in (r, p):
+        pl.generate_grid([0, 0, 0], [8, 8, 1], 1.0, True, 90.0)
+        pl.generate_grid([0.5, 0.5, 0.5], [6, 6, 0], 0.5, True, 90.0)
+    rng = np.random.RandomState(7)
+    hull1 = np.stack([rng.randint(-4, 5, 80), rng.randint(-4, 5, 80), rng.choice([-0.5, 0.5], 80)], axis=1).astype(np.float32)
+    hull2 = np.stack([rng.randint(-5, 8, 120) * 0.5, rng.randint(-5, 8, 120) * 0.5, np.full(120, 0.5)], axis=1).astype(np.float32)
+    r.connect_to_nn(hull1, hull2, 90.0)
+    p.connect_to_nn(hull1, hull2, 90.0)
+    (rp_r, col_r), (rp_h, col_h) = r.csr(), p.csr()
+    assert 0 < len(col_r)
+    assert np.array_equal(rp_h, rp_r) and np.array_equal(col_h, col_r)
+    r.close()
+    p.close()
+    w.close()
+
+
+def test_clustering_is_connected_components(eng):
+    """clusteringPointCloud of the coverage heuristic = connected components of the radius graph (built by the
+    engine's radius search), small components dropped — checked against scipy on the same points"""
+    from scipy.sparse import coo_matrix
+    from scipy.sparse.csgraph import connected_components
+    from scipy.spatial import cKDTree
+    cam = dict(mount_xyz=[0, 0, 0], mount_rpy=[0, 0, 0], hfov=58.0, vfov=45.0, near=0.7, far=6.0)
+    p = host_lib.HostPlanner(1.5, device=0, coverage=cam)
+    rng = np.random.RandomState(1)
+    blobs = [rng.normal(c, 0.4, (n, 3)) for c, n in (((0, 0, 0), 400), ((5, 0, 0), 300), ((0, 6, 1), 200), ((9, 9, 9), 4))]
+    pts = np.concatenate(blobs + [rng.uniform(-12, 12, (30, 3))]).astype(np.float32)
+    tol = 0.5
+    p.set_clustering(tol, 10, 3.0)
+    lab = p.cluster_labels(pts)
+    d = pts.astype(np.float64)
+    pairs = cKDTree(d).query_pairs(tol, output_type="ndarray")
+    # the engine's predicate is sqrt(d2) <= tol in double; the KD-tree uses the same closed ball
+    A = coo_matrix((np.ones(len(pairs)), (pairs[:, 0], pairs[:, 1])), shape=(len(pts), len(pts)))
+    ncomp, comp = connected_components(A, directed=False)
+    sizes = np.bincount(comp)
+    for c in range(ncomp):
+        members = np.nonzero(comp == c)[0]
+        labs = np.unique(lab[members])
+        assert len(labs) == 1
+        assert (labs[0] >= 0) == (sizes[c] >= 10)
+    big = [c for c in range(ncomp) if sizes[c] >= 10]
+    assert len(np.unique(lab[lab >= 0])) == len(big) >= 3
+    p.close()
+
+
+def test_dynamic_sampling_loop(eng):
+    """PathPlanner::dynamicNodesGenerationAndConnection with the coverage heuristic: coarse samples first, then
+    finer samples around what is still unseen, stages linked by connectToNN; coverage can only grow and the
+    graph stays connected enough to plan on"""
+    from sspp_b200 import scenes
+    res = 0.25
+    km, dm, occ, known = scenes.synthetic_map(n_vox=96, res=res, seed=4, n_boxes=6, n_spheres=4, region=10.0)
+    pts = scenes.surface_points(occ, known, km, dm, res, 20000, seed=45)
+    cam = dict(mount_xyz=[0.0, 0.0, 0.0], mount_rpy=[0.0, 0.0, 0.0], hfov=90.0, vfov=70.0, near=0.3, far=7.0)
+    coarse = host_lib.HostPlanner(1.6, device=0, coverage=cam)
+    coarse.map_create(res, km, dm, True)
+    coarse.map_upload_dense(occ, known)
+    coarse.set_model_points(pts)
+    coarse.set_clustering(0.6, 10, 2.0)
+    n0, e0, cov0 = coarse.dynamic_sampling([0, 0, 0], [16, 16, 6], 4.0, 5.0)   # decrement > start: the coarse stage only
+    fine = host_lib.HostPlanner(1.6, device=0, coverage=cam)
+    fine.map_create(res, km, dm, True)
+    fine.map_upload_dense(occ, known)
+    fine.set_model_points(pts)
+    fine.set_clustering(0.6, 10, 2.0)
+    n1, e1, cov1 = fine.dynamic_sampling([0, 0, 0], [16, 16, 6], 4.0, 1.5)     # stages at 4.0, 2.5, 1.0
+    assert n0 > 0 and cov0 > 0
+    assert n1 > n0 and e1 > e0 and cov1 > cov0          # refinement adds way-points, links and coverage
+    assert cov1 <= len(pts)
+    rp, col = fine.csr()
+    assert len(col) == e1 and col.max() < n1
+    coarse.close()
+    fine.close()

@@ -222,3 +222,30 @@ def test_binary_graph_file_round_trip(built, tmp_path):
         host_lib.HostPlanner(1.5).load_binary(fn)
     p.close()
     q.close()
+
+
+def test_connect_to_nn_matches_reference(ref):
+    """PathPlanner::connectToNN (src/pathplanner.cpp:658-763): nearest neighbour per hull point, all yaw
+    pairs, links in both directions, nodes looked up by pose — same adjacency as the reference's code"""
+    r = ref.planner(1.5)
+    p = host_lib.HostPlanner(1.5)
+    for pl in (r, p):
+        pl.generate_grid([0, 0, 0], [6, 6, 1], 1.0, True, 90.0)        # integer / half coordinates: exact as float
+        pl.generate_grid([0.5, 0.5, 0.5], [4, 4, 0], 0.5, True, 90.0)
+    n = len(p.nodes()[0])
+    p.set_adjacency(np.zeros(n + 1, dtype=np.int64), np.zeros(0, dtype=np.int32))
+    rng = np.random.RandomState(3)
+    hull1 = np.stack([rng.randint(-3, 4, 40), rng.randint(-3, 4, 40), rng.choice([-0.5, 0.5], 40)], axis=1).astype(np.float32)
+    hull2 = np.stack([rng.randint(-3, 6, 60) * 0.5, rng.randint(-3, 6, 60) * 0.5, np.full(60, 0.5)], axis=1).astype(np.float32)
+    hull2[:5] = hull1[:5]            # same position: linked across yaws without a test
+    hull2[5] = [9.25, 9.25, 9.25]    # not a node: no link
+    r.connect_to_nn(hull1, hull2, 90.0)
+    p.connect_to_nn(hull1, hull2, 90.0)
+    (rp_r, col_r), (rp_h, col_h) = r.csr(), p.csr()
+    assert len(col_r) > 100
+    assert np.array_equal(rp_h, rp_r) and np.array_equal(col_h, col_r)
+    # (the reference's two-argument-less constructor leaves MAXNODES uninitialised, src/pathplanner.cpp:40-50, so its
+    # value after `+= numConnections` is not comparable; the mirror starts from 0)
+    assert p.maxnodes() == len(col_h)
+    r.close()
+    p.close()
