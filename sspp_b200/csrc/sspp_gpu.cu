@@ -114,7 +114,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->occ, &ctx->known, &ctx->blocked, &ctx->cblocked, &ctx->map_stage, &ctx->logodds, &ctx->scan_free,
-                    &ctx->scan_occ, &ctx->pc_pts, &ctx->pc_keys, &ctx->pc_vals, &ctx->xyz, &ctx->bbox,
+                    &ctx->scan_occ, &ctx->pc_pts, &ctx->pc_keys, &ctx->pc_vals, &ctx->xyz, &ctx->bbox, &ctx->vis_bbox,
                     &ctx->cell_of, &ctx->cell_start, &ctx->cell_cursor, &ctx->sorted_idx, &ctx->sx, &ctx->sy, &ctx->sz,
                     &ctx->rows, &ctx->row_flag, &ctx->row_free, &ctx->cand_count, &ctx->cand_off, &ctx->candA, &ctx->candB,
                     &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice, &ctx->work_rows,
@@ -974,13 +974,14 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
   float np_dist = (float)fr->near_dist, fp_dist = (float)fr->far_dist;
 
   // --- bin the model points (cell edge = far/4)
-  CK(ctx->bbox.reserve(7 * 8));
+  // (its own buffer: ctx->bbox may hold the queued, not yet read bounding box of the node set)
+  CK(ctx->vis_bbox.reserve(7 * 8));
   unsigned long long init[7] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
-  CK(cudaMemcpyAsync(ctx->bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
-  k_pts_bbox<<<std::min(ceil_div(np, 256), 148 * 8), 256, 0, st>>>(ctx->pts.as<float>(), np, ctx->bbox.as<unsigned long long>());
+  CK(cudaMemcpyAsync(ctx->vis_bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  k_pts_bbox<<<std::min(ceil_div(np, 256), 148 * 8), 256, 0, st>>>(ctx->pts.as<float>(), np, ctx->vis_bbox.as<unsigned long long>());
   LAUNCHED(ctx);
   unsigned long long hb[7];
-  CK(cudaMemcpyAsync(hb, ctx->bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(hb, ctx->vis_bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
   if (hb[6]) return fail(ctx, SSPP_ERR_INVALID, "visibility: model points must be finite");
   PointGrid g;

@@ -105,3 +105,19 @@ def test_visibility_with_reference_camera_poses(eng, orc):
     for k, v in enumerate(sel):
         assert np.array_equal(idx[vp[v]:vp[v + 1]], idx_o[vp_o[k]:vp_o[k + 1]]), v
     w.close()
+
+
+def test_interleaved_calls_do_not_share_state(eng, orc):
+    """set_nodes -> visibility -> connect: the visibility pass must not disturb the node store's queued
+    bounding box (regression test for a shared scratch buffer)"""
+    w, pts = scene(eng, orc)
+    nodes = scenes.uniform_nodes(1500, extent=14.0, seed=3)
+    eng.set_nodes(nodes)
+    eng.set_model_points(pts + 40.0)          # far from the nodes: a very different bounding box
+    poses = scenes.viewpoints_near(pts, 16, standoff=3.0, seed=2)
+    eng.visibility(poses, 58.0, 45.0, 0.7, 6.0)
+    st = eng.connect(radius=1.6)
+    rp, col = eng.connect_fetch(st)
+    rp_o, col_o, _ = orc.connect(w, nodes, 1.6)
+    assert np.array_equal(rp, rp_o) and np.array_equal(col, col_o)
+    w.close()
