@@ -254,10 +254,17 @@ __device__ __forceinline__ bool box_maybe_blocked(const DeviceMap& m, int lox, i
   for (int w = w0; w <= w1; ++w) {
     const int b0 = (w == w0) ? (x0 & 31) : 0, b1 = (w == w1) ? (x1 & 31) : 31;
     const uint32_t mask = (b1 == 31 ? 0xffffffffu : ((1u << (b1 + 1)) - 1u)) & ~((1u << b0) - 1u);
-    for (int z = z0; z <= z1; ++z) {
-      const uint32_t* row = m.blocked + map_word(m, w, 0, z);
-      for (int y = y0; y <= y1; ++y) any |= __ldg(row + y) & mask;
+    uint32_t acc = 0;
+    const uint32_t* col = m.blocked + map_word(m, w, y0, z0);
+    for (int z = z0; z <= z1; ++z, col += m.dims[1]) {
+      // the y run is a few consecutive words: eight predicated loads at a time, all in flight together
+      for (int yb = 0; yb <= y1 - y0; yb += 8) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (yb + k <= y1 - y0) acc |= __ldg(col + yb + k);
+      }
     }
+    any |= acc & mask;
   }
   return any != 0;
 }

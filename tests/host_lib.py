@@ -232,7 +232,7 @@ class HostPlanner:
         self.L.sspph_get_csr(self.h, _p(rp), _p(col), E)
         return rp, col[:E]
 
-    def astar(self, start_pose, cap=4096, cap_order=1 << 20):
+    def astar(self, start_pose, cap=4096, cap_order=1 << 16):
         path = np.zeros((cap, 10))
         stats = np.zeros(2, dtype=np.int64)
         order = np.full(cap_order, -1, dtype=np.int32)
