@@ -60,42 +60,54 @@ __global__ void k_cell_hist(const double* __restrict__ xyz, int64_t n, NodeGrid 
   atomicAdd(cell_count + c, 1);
 }
 
+// One record per binned node, in cell order: position and list index together, 32 bytes, so that a
+// candidate costs one aligned 32-byte read (two 128-bit loads) instead of four scattered ones.
+struct __align__(32) NodeRec {
+  double x, y, z;
+  long long idx;  // list index of the node
+};
+__device__ __forceinline__ NodeRec load_node(const NodeRec* p) {
+  const double2 a = *reinterpret_cast<const double2*>(p);
+  const double2 b = *(reinterpret_cast<const double2*>(p) + 1);
+  NodeRec r;
+  r.x = a.x; r.y = a.y; r.z = b.x;
+  r.idx = __double_as_longlong(b.y);
+  return r;
+}
+
 __global__ void k_cell_scatter(const double* __restrict__ xyz, int64_t n, const int* __restrict__ cell_of, int* cursor,
-                               int* __restrict__ sorted_idx, double* __restrict__ sx, double* __restrict__ sy,
-                               double* __restrict__ sz) {
+                               NodeRec* __restrict__ sn) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n || cell_of[i] < 0) return;
   int pos = atomicAdd(cursor + cell_of[i], 1);
-  sorted_idx[pos] = (int)i;
-  sx[pos] = xyz[3 * i];
-  sy[pos] = xyz[3 * i + 1];
-  sz[pos] = xyz[3 * i + 2];
+  NodeRec r;
+  r.x = xyz[3 * i]; r.y = xyz[3 * i + 1]; r.z = xyz[3 * i + 2];
+  r.idx = i;
+  sn[pos] = r;
 }
 
 // Order the members of every cell by list index, so the whole pipeline is run-to-run deterministic
 // (the scatter above lands them in atomic order).  Cells hold a handful of nodes: insertion sort.
-__global__ void k_cell_sort(const int* __restrict__ cell_start, int ncells, int* sorted_idx, double* sx, double* sy, double* sz) {
+__global__ void k_cell_sort(const int* __restrict__ cell_start, int ncells, NodeRec* sn) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= ncells) return;
   int b = cell_start[c], e = cell_start[c + 1];
   for (int i = b + 1; i < e; ++i) {
-    int k = sorted_idx[i];
-    double x = sx[i], y = sy[i], z = sz[i];
+    NodeRec k = sn[i];
     int j = i - 1;
-    while (j >= b && sorted_idx[j] > k) {
-      sorted_idx[j + 1] = sorted_idx[j]; sx[j + 1] = sx[j]; sy[j + 1] = sy[j]; sz[j + 1] = sz[j];
+    while (j >= b && sn[j].idx > k.idx) {
+      sn[j + 1] = sn[j];
       --j;
     }
-    sorted_idx[j + 1] = k; sx[j + 1] = x; sy[j + 1] = y; sz[j + 1] = z;
+    sn[j + 1] = k;
   }
 }
 
-// rows of a shard: flag sorted positions whose list index is in [lo, hi)
 // n_sorted_ptr: how many nodes were binned (device side); positions beyond it hold nothing
-__global__ void k_row_flags(const int* __restrict__ sorted_idx, int64_t n, const int* __restrict__ n_sorted_ptr, int64_t lo,
+__global__ void k_row_flags(const NodeRec* __restrict__ sn, int64_t n, const int* __restrict__ n_sorted_ptr, int64_t lo,
                             int64_t hi, int* __restrict__ flag) {
   int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < n) flag[s] = (s < *n_sorted_ptr && sorted_idx[s] >= lo && sorted_idx[s] < hi) ? 1 : 0;
+  if (s < n) flag[s] = (s < *n_sorted_ptr && sn[s].idx >= lo && sn[s].idx < hi) ? 1 : 0;
 }
 __global__ void k_row_scatter(const int* __restrict__ flag, const int* __restrict__ pos, int64_t n, int* __restrict__ rows) {
   int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -150,10 +162,7 @@ __device__ bool row_reach_is_free(const DeviceMap& m, double px, double py, doub
 struct ConnectArgs {
   NodeGrid g;
   const int* cell_start;
-  const int* sorted_idx;
-  const double* sx;
-  const double* sy;
-  const double* sz;
+  const NodeRec* sn;  // binned nodes, cell order
   const int* rows;  // sorted positions of the rows to process, or NULL = all
   int nrows;
   int64_t lo;  // first list index of this shard
@@ -183,8 +192,9 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
   bool is_work = false;
   if (t < a.nrows) {
     int s = a.rows ? a.rows[t] : t;
-    double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
-    int r = (int)(a.sorted_idx[s] - a.lo);
+    const NodeRec me = load_node(a.sn + s);
+    const double px = me.x, py = me.y, pz = me.z;
+    int r = (int)(me.idx - a.lo);
     int cx = grid_cell_axis(a.g, px, 0), cy = grid_cell_axis(a.g, py, 1), cz = grid_cell_axis(a.g, pz, 2);
     int x0 = max(cx - 1, 0), x1 = min(cx + 1, a.g.n[0] - 1);
     int cnt = 0, tst = 0;
@@ -195,9 +205,10 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
         int b = a.cell_start[base + x0], e = a.cell_start[base + x1 + 1];
         for (int j = b; j < e; ++j) {
           if (j == s) continue;
-          int pc = pair_class(a.sx[j], a.sy[j], a.sz[j], px, py, pz, a.r2max, a.mode);
+          const NodeRec o = load_node(a.sn + j);
+          int pc = pair_class(o.x, o.y, o.z, px, py, pz, a.r2max, a.mode);
           if (FILL) {
-            if (pc) cand[w++] = make_int2(j, a.sorted_idx[j] | (pc == 2 ? (int)0x80000000 : 0));
+            if (pc) cand[w++] = make_int2(j, (int)o.idx | (pc == 2 ? (int)0x80000000 : 0));
           } else {
             cnt += (pc != 0);
             tst += (pc == 1);
@@ -473,7 +484,7 @@ __global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long l
   const int t = blockIdx.x * EDGE_WARPS + warp;
   if (t >= a.nrows) return;
   const int s = a.rows ? a.rows[t] : t;
-  const int r = (int)(a.sorted_idx[s] - a.lo);
+  const int r = (int)(a.sn[s].idx - a.lo);
   const long long off = cand_off[r];
   const int n = (int)(cand_off[r + 1] - off);
   if (a.use_map && !row_free[r] && n > 0) return;  // a work row: k_edges writes it
@@ -497,12 +508,13 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
                                          int* __restrict__ deg, unsigned long long* counters) {
   const RayLattice& lat = sm.lat;
   const int s = a.rows ? a.rows[t] : t;
-  const int r = (int)(a.sorted_idx[s] - a.lo);
+  const NodeRec me = load_node(a.sn + s);
+  const int r = (int)(me.idx - a.lo);
   const long long off = cand_off[r];
   const int n = (int)(cand_off[r + 1] - off);
   const int2 c0 = sort_row_pairs(sm.sort, warp, lane, candA, candB, off, n);
 
-  const double px = a.sx[s], py = a.sy[s], pz = a.sz[s];
+  const double px = me.x, py = me.y, pz = me.z;
   const int R = lat.rays;
   const bool fast = a.use_pyramid != 0;
   // Row-level verdicts: every ray starts at p + offset whatever the pair, and the start voxel is the
@@ -534,7 +546,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     const bool same = mine_valid && (c.y & 0x80000000);
     // this lane's pair: coordinates of the far end
     double qx = 0, qy = 0, qz = 0;
-    if (mine_valid) { qx = a.sx[c.x]; qy = a.sy[c.x]; qz = a.sz[c.x]; }
+    if (mine_valid) { const NodeRec o = load_node(a.sn + c.x); qx = o.x; qy = o.y; qz = o.z; }
     bool rejected = false;
     bool needs = mine_valid && !same;
     // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair

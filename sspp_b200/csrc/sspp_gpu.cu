@@ -556,10 +556,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->cell_of.reserve((size_t)n * 4));
   CK(ctx->cell_start.reserve((size_t)(ncells + 1) * 4));
   CK(ctx->cell_cursor.reserve((size_t)(ncells + 1) * 4));
-  CK(ctx->sorted_idx.reserve((size_t)n * 4));
-  CK(ctx->sx.reserve((size_t)n * 8));
-  CK(ctx->sy.reserve((size_t)n * 8));
-  CK(ctx->sz.reserve((size_t)n * 8));
+  CK(ctx->sx.reserve((size_t)n * sizeof(NodeRec)));
   CK(cudaMemsetAsync(ctx->cell_cursor.p, 0, (size_t)(ncells + 1) * 4, st));
   k_cell_hist<<<ceil_div(n, 256), 256, 0, st>>>(ctx->xyz.as<double>(), n, g, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>());
   LAUNCHED(ctx);
@@ -569,11 +566,9 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   }
   CK(cudaMemcpyAsync(ctx->cell_cursor.p, ctx->cell_start.p, (size_t)ncells * 4, cudaMemcpyDeviceToDevice, st));
   k_cell_scatter<<<ceil_div(n, 256), 256, 0, st>>>(ctx->xyz.as<double>(), n, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>(),
-                                                   ctx->sorted_idx.as<int>(), ctx->sx.as<double>(), ctx->sy.as<double>(),
-                                                   ctx->sz.as<double>());
+                                                   ctx->sx.as<NodeRec>());
   LAUNCHED(ctx);
-  k_cell_sort<<<ceil_div(ncells, 256), 256, 0, st>>>(ctx->cell_start.as<int>(), (int)ncells, ctx->sorted_idx.as<int>(),
-                                                     ctx->sx.as<double>(), ctx->sy.as<double>(), ctx->sz.as<double>());
+  k_cell_sort<<<ceil_div(ncells, 256), 256, 0, st>>>(ctx->cell_start.as<int>(), (int)ncells, ctx->sx.as<NodeRec>());
   LAUNCHED(ctx);
 
   // rows of this shard, in cell order
@@ -583,7 +578,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
     CK(ctx->rows.reserve((size_t)(n + 1) * 4 + (size_t)nrows * 4));
     int* pos = ctx->rows.as<int>();
     int* rows_w = pos + (n + 1);
-    k_row_flags<<<ceil_div(n, 256), 256, 0, st>>>(ctx->sorted_idx.as<int>(), n, ctx->cell_start.as<int>() + ncells, lo, hi,
+    k_row_flags<<<ceil_div(n, 256), 256, 0, st>>>(ctx->sx.as<NodeRec>(), n, ctx->cell_start.as<int>() + ncells, lo, hi,
                                                  ctx->row_flag.as<int>());
     LAUNCHED(ctx);
     int rc = scan_exclusive<int>(ctx, ctx->row_flag.as<int>(), n, pos);
@@ -598,10 +593,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   ConnectArgs a;
   a.g = g;
   a.cell_start = ctx->cell_start.as<int>();
-  a.sorted_idx = ctx->sorted_idx.as<int>();
-  a.sx = ctx->sx.as<double>();
-  a.sy = ctx->sy.as<double>();
-  a.sz = ctx->sz.as<double>();
+  a.sn = ctx->sx.as<NodeRec>();
   a.rows = rows;
   a.nrows = (int)nrows;
   a.lo = lo;
