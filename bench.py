@@ -40,12 +40,23 @@ METRIC = "collision-checked edges/s (connectNodes graph build, 1M nodes / 512^3 
 UNIT = "edges/s"
 
 
-def workload_config(n_gpus):
-    return {"workload": "S4a: 512^3 voxels @0.3 m (seed 42, 400 boxes + 200 spheres), 10^6 nodes on a 100^3 lattice @1.0 m, "
-                        "R=1.5, box (0.5,0.5,0.3) -> 27 rays/pair, treat_unknown_as_occupied",
-            "nodes": LATTICE ** 3, "voxels": N_VOX ** 3, "radius": RADIUS, "box": list(BOX),
-            "parallelism": "rows%d" % n_gpus,
-            "l2": "flushed between timed steps (256 MiB write, outside the timed events); per-step scratch (~0.4 GB) also exceeds L2"}
+def workload_config(n_gpus, regions=1, assembler=None):
+    w = ("S4a: 512^3 voxels @0.3 m (seed 42, 400 boxes + 200 spheres), 10^6 nodes on a 100^3 lattice @1.0 m, "
+         "R=1.5, box (0.5,0.5,0.3) -> 27 rays/pair, treat_unknown_as_occupied")
+    if regions > 1:
+        w = ("S4a x %d (weak scaling): ONE map of 512 x 512 x %d voxels = %d S4a regions stacked along z (seeds 42..%d), ONE search "
+             "space of %d x 10^6 nodes (a 100^3 lattice per region), map and node set replicated on every GPU, rank g owns "
+             "the source rows of region g; " % (regions, 512 * regions, regions, 41 + regions, regions)) + w
+    c = {"workload": w, "nodes": regions * LATTICE ** 3, "voxels": regions * N_VOX ** 3, "radius": RADIUS, "box": list(BOX),
+         "parallelism": "rows%d" % n_gpus,
+         "l2": "flushed between timed steps (256 MiB write, outside the timed events); per-step scratch (~0.4 GB) also exceeds L2"}
+    if assembler:
+        c["csr_assembly"] = assembler
+    return c
+
+
+def region_centre_z(g, regions):
+    return (g - (regions - 1) / 2.0) * N_VOX * RES
 
 
 # ------------------------------------------------------------------------------------------------
@@ -222,14 +233,14 @@ def run_reference_arm(args):
     pool.join()
     value = total_c / total_t
     kind = "reference" if have_ref else "port"
-    sample = ("%d worker processes (one per host core) x one %d^3 sub-lattice (%d nodes) of the S4a scene per step, each running "
+    sample = ("%d worker processes (one per host core) x one %d^3 sub-lattice (%d nodes) of the S4a scene (region 0) per step, each running "
               "%s connectNodes (O(N^2) pair scan + getLineStatusBoundingBox per pair) on its own octree window; %d tested pairs "
               "per step" % (procs, ln, ln ** 3, "the reference's own single-threaded" if have_ref else "the oracle port of",
                             total_c // max(args.steps, 1)))
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * total_t / max(args.steps, 1), "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f64+f32 (CPU)", "data": "synthetic",
-            "config": workload_config(args.gpus),
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f64+f32 (CPU)", "data": "synthetic",
+            "config": workload_config(args.gpus, args.gpus if (args.gpus > 1 and args.scaling == "weak") else 1),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -247,6 +258,10 @@ def main():
     ap.add_argument("--impl", default="sspp_b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-visibility", action="store_true")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="N>1: weak = one S4a region per GPU in one map / one search space (default); strong = S4a split over the GPUs")
+    ap.add_argument("--assembler", default="peer", choices=["peer", "nccl"],
+                    help="N>1: CSR assembly by the fused push kernel over NVLink peer memory (default) or by NCCL all-gather + packing")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
@@ -273,9 +288,27 @@ def main():
     W = max(args.warmup, 3)
     K = args.steps
 
-    # ---- scene (synthetic, identical on every rank: the map and the node set are replicated)
-    key_min, dims, occ, known = scenes.synthetic_map(n_vox=N_VOX, res=RES, seed=42)
-    nodes = scenes.lattice_nodes(LATTICE, 1.0)
+    # ---- scene (synthetic; the map and the node set are replicated on every rank).  Weak scaling: rank g
+    # generates region g (the S4a generator with seed 42+g) and the packed planes are all-gathered, so
+    # every rank uploads the same tall map; region g sits at z = region_centre_z(g).
+    regions = world if (distributed and args.scaling == "weak") else 1
+    key_min, dims, occ, known = scenes.synthetic_map(n_vox=N_VOX, res=RES, seed=42 + (rank if regions > 1 else 0))
+    occ0, known0, key_min0, dims0 = occ, known, key_min.copy(), dims.copy()  # this rank's region alone (visibility leg)
+    if regions > 1:
+        planes = torch.from_numpy(np.stack([occ, known]).view(np.int32)).cuda()
+        gathered = torch.empty((regions,) + tuple(planes.shape), dtype=planes.dtype, device="cuda")
+        dist.all_gather_into_tensor(gathered, planes)
+        allp = gathered.cpu().numpy().view(np.uint32)  # (region, plane, z, y, xw)
+        occ = np.ascontiguousarray(np.concatenate([allp[g, 0] for g in range(regions)], axis=0))
+        known = np.ascontiguousarray(np.concatenate([allp[g, 1] for g in range(regions)], axis=0))
+        del planes, gathered, allp
+        key_min = key_min.copy()
+        dims = dims.copy()
+        key_min[2] = 32768 - (N_VOX // 2) * regions
+        dims[2] = N_VOX * regions
+        key_min0[2] = key_min[2] + N_VOX * rank
+    nodes = np.ascontiguousarray(np.concatenate([scenes.lattice_nodes(LATTICE, 1.0, centre=(0.0, 0.0, region_centre_z(g, regions)))
+                                                 for g in range(regions)], axis=0))
     n = len(nodes)
     eng = Engine(local_rank)
     eng.map_create(RES, key_min, dims, True)
@@ -305,21 +338,28 @@ def main():
     assembler = None
     if distributed:
         from sspp_b200 import sharded
-        assembler = sharded.GpuCsrAssembler(eng, n, torch.device("cuda", local_rank))
+        cls = sharded.PeerCsrAssembler if args.assembler == "peer" else sharded.GpuCsrAssembler
+        assembler = cls(eng, n, torch.device("cuda", local_rank))
 
     def assemble_csr(st):
-        """N>1: all-gather the per-rank CSR blocks over NCCL and pack them on the device."""
+        """N>1: every rank ends the step holding the whole graph's CSR (peer-memory push, or NCCL all-gather + packing)."""
         if assembler is not None:
             return assembler.assemble(st)
 
+    split = []  # per timed step: host seconds in connect / in the CSR assembly (the latter includes waiting for the slowest rank)
+
     def step_resident():
+        t0 = time.perf_counter()
         st = eng.connect(radius=RADIUS, box=BOX, rows=rows)
+        t1 = time.perf_counter()
         assemble_csr(st)
+        split.append((t1 - t0, time.perf_counter() - t1))
         return st
 
     for _ in range(W):
         st = step_resident()
     tested_local = st.tested_pairs
+    split.clear()
     flush_l2()
     barrier()
     clocks = ClockSampler(local_rank)
@@ -364,6 +404,19 @@ def main():
     else:
         tested_all, edges_all = float(tested_local), float(st.edges)
     value = tested_all * K / (total_ms * 1e-3)
+    multi = None
+    if distributed:
+        mine = torch.tensor([np.mean([a for a, _ in split]) * 1e3, np.mean([b for _, b in split]) * 1e3,
+                             float(np.mean([p[0] for p in phase_ms])), float(tested_local)], dtype=torch.float64, device="cuda")
+        allm = torch.empty(world * 4, dtype=torch.float64, device="cuda")
+        dist.all_gather_into_tensor(allm, mine)
+        allm = allm.cpu().numpy().reshape(world, 4)
+        multi = {"connect_host_ms_per_rank": [round(float(x), 4) for x in allm[:, 0]],
+                 "assembly_host_ms_per_rank": [round(float(x), 4) for x in allm[:, 1]],
+                 "connect_device_ms_per_rank": [round(float(x), 4) for x in allm[:, 2]],
+                 "tested_pairs_per_rank": [int(x) for x in allm[:, 3]],
+                 "note": "assembly = counts all-gather + push kernel (or NCCL all-gather + packing) + closing barrier, "
+                         "host wall clock per rank; it includes the wait for the slowest rank's connect"}
 
     # ---- e2e: host buffers through the C ABI (pinned), copies inside the timed region
     pin_nodes = torch.from_numpy(nodes).pin_memory()
@@ -456,7 +509,7 @@ def main():
     if not args.no_visibility:
         try:
             NV, NP = 65536, 4_000_000
-            pts = scenes.surface_points(occ, known, key_min, dims, RES, NP, seed=45)
+            pts = scenes.surface_points(occ0, known0, key_min0, dims0, RES, NP, seed=45)
             poses = scenes.viewpoints_near(pts, NV, standoff=3.0, seed=46)
             eng.set_model_points(pts)
             eng.visibility(poses, 58.0, 45.0, 0.7, 6.0, fetch=False)
@@ -501,13 +554,13 @@ def main():
         cpu.pop("seconds", None)
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": K, "warmup": W,
-            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f64 distances + f32/f64 DDA + u32 bit planes", "data": "synthetic",
-            "config": workload_config(n_gpus),
+            "config": workload_config(n_gpus, regions, (args.assembler if distributed else None)),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": float(e2e_tot[0]) * 1e3 / K},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "visibility": vis,
-            "tested_pairs_per_step": tested_all, "edges_per_step": edges_all}
+            "tested_pairs_per_step": tested_all, "edges_per_step": edges_all, "multi_gpu": multi}
     print(json.dumps(line))
     if distributed:
         dist.barrier()

@@ -153,6 +153,31 @@ int sspp_gpu_connect_fetch_device(sspp_gpu_ctx* ctx, int64_t* row_ptr_device, in
 int sspp_gpu_assemble_csr_blocks(sspp_gpu_ctx* ctx, const int64_t* row_ptr_blocks_device, const int32_t* col_blocks_device,
                                  int world, int64_t row_stride, int64_t col_stride, const int64_t* row_base_device,
                                  int64_t* row_ptr_out_device, int32_t* col_out_device, int64_t* overflow_device);
+/* Multi-GPU assembly through NVLink peer memory — the compaction result and its all-gather as one
+ * kernel (no counterpart in the reference, which is one process; it realises SURVEY.md §8 e's exchange
+ * step).  Every rank owns one whole-graph CSR (row_ptr: total_rows+1 int64, col_idx: col_capacity
+ * int32) that its peers can address:
+ *   sspp_gpu_peer_buffer_create  cudaMalloc + cudaIpcGetMemHandle: the 64-byte handle is what the ranks
+ *                                exchange (any transport: an all-gather of 64 bytes per rank);
+ *   sspp_gpu_peer_buffer_open    cudaIpcOpenMemHandle of a peer's handle (another process, same box);
+ *   sspp_gpu_peer_buffer_release frees a created buffer / closes an opened one (destroy does it too).
+ * sspp_gpu_connect_push_csr then writes this rank's last CSR block, rebased by the edge counts of the
+ * lower ranks, into the buffers of all `world` ranks (entry [rank] = this rank's own buffer; host
+ * arrays of device pointers) on the context's stream.  edge_counts_device: `world` int64, the
+ * all-gathered edge counts of this connect; row_base_device: world+1 first-row indices.  If the
+ * graph's edge total exceeds col_capacity nothing is written and *overflow_device receives the total
+ * (every rank takes the same decision from the same counts).  The pushes of all ranks are complete —
+ * and the CSR may be read — after a barrier that follows this call on every rank; a rank must not start
+ * the next push before all ranks have finished reading (the all-gather of the next counts orders that).
+ * The result is byte-identical to the CSR of a one-GPU connect over all rows. */
+#define SSPP_MAX_PEERS 16
+#define SSPP_PEER_HANDLE_BYTES 64
+int sspp_gpu_peer_buffer_create(sspp_gpu_ctx* ctx, int64_t bytes, void** device_ptr, uint8_t handle[SSPP_PEER_HANDLE_BYTES]);
+int sspp_gpu_peer_buffer_open(sspp_gpu_ctx* ctx, const uint8_t handle[SSPP_PEER_HANDLE_BYTES], void** device_ptr);
+int sspp_gpu_peer_buffer_release(sspp_gpu_ctx* ctx, void* device_ptr);
+int sspp_gpu_connect_push_csr(sspp_gpu_ctx* ctx, int world, int rank, const int64_t* edge_counts_device,
+                              const int64_t* row_base_device, int64_t* const* row_ptr_peers, int32_t* const* col_idx_peers,
+                              int64_t col_capacity, int64_t* overflow_device);
 /* Device addresses of the last CSR (valid until the next connect on this context). */
 int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_device, const int32_t** col_idx_device);
 

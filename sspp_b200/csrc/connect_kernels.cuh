@@ -734,5 +734,65 @@ __global__ void k_assemble_blocks(const long long* __restrict__ rp_all, const in
   for (long long i = tid; i < edges; i += nth) out_col[ebase + i] = col[i];
 }
 
+// Multi-GPU CSR assembly fused with its all-gather: this rank's block goes straight into the
+// whole-graph CSR of EVERY rank through NVLink peer memory (plain stores to peer pointers), rebased
+// on the way, so no gathered staging copy and no separate packing pass exist.  Every rank computes
+// the same edge prefix from the same all-gathered counts, so all ranks take the same overflow
+// decision without talking.  Column stores are 16 bytes wide, aligned on the destination (the
+// destination offset ebase is the same for all peers, so one alignment fits all of them); peers are
+// visited starting with the rank's right-hand neighbour so that the ranks do not all write to the
+// same GPU at once.
+struct PushPeers {
+  long long* rp[SSPP_MAX_PEERS];
+  int* col[SSPP_MAX_PEERS];
+  int world, rank;
+};
+
+__global__ void __launch_bounds__(256)
+k_push_csr(PushPeers p, const long long* __restrict__ edge_counts, const long long* __restrict__ row_base,
+           const long long* __restrict__ rp, const int* __restrict__ col, long long col_capacity,
+           long long* __restrict__ overflow) {
+  long long ebase = 0, total = 0;
+  for (int k = 0; k < p.world; ++k) {
+    long long c = edge_counts[k];
+    if (k < p.rank) ebase += c;
+    total += c;
+  }
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  if (total > col_capacity) {
+    if (tid == 0) atomicMax((unsigned long long*)overflow, (unsigned long long)total);
+    return;
+  }
+  const long long edges = edge_counts[p.rank];
+  const long long r0 = row_base[p.rank], rows = row_base[p.rank + 1] - r0;
+  for (long long i = tid; i < rows; i += nth) {
+    long long v = rp[i] + ebase;
+    for (int j = 0; j < p.world; ++j) {
+      int k = p.rank + 1 + j;
+      if (k >= p.world) k -= p.world;
+      p.rp[k][r0 + i] = v;
+    }
+  }
+  if (p.rank == p.world - 1 && tid == 0)
+    for (int k = 0; k < p.world; ++k) p.rp[k][r0 + rows] = total;
+  long long head = (4 - (ebase & 3)) & 3;
+  if (head > edges) head = edges;
+  const long long nvec = (edges - head) >> 2, tail0 = head + (nvec << 2);
+  for (long long i = tid; i < head + (edges - tail0); i += nth) {
+    long long e = i < head ? i : tail0 + (i - head);
+    int v = col[e];
+    for (int k = 0; k < p.world; ++k) p.col[k][ebase + e] = v;
+  }
+  for (long long q = tid; q < nvec; q += nth) {
+    const int* s = col + head + (q << 2);
+    int4 v = make_int4(s[0], s[1], s[2], s[3]);
+    for (int j = 0; j < p.world; ++j) {
+      int k = p.rank + 1 + j;
+      if (k >= p.world) k -= p.world;
+      *reinterpret_cast<int4*>(p.col[k] + ebase + head + (q << 2)) = v;
+    }
+  }
+}
+
 
 }  // namespace

@@ -69,6 +69,9 @@ struct sspp_gpu_ctx {
   cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   float timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
+  // peer-addressable buffers (multi-GPU CSR assembly): created here / opened from a peer's IPC handle
+  std::vector<void*> peer_created, peer_opened;
+
   // generic query scratch
   DevBuf q0, q1, q2, q3, q4;
 

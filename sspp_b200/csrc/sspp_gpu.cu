@@ -121,6 +121,8 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
                     &ctx->q0, &ctx->q1, &ctx->q2, &ctx->q3, &ctx->q4, &ctx->pts, &ctx->vis_cnt, &ctx->vis_ptr,
                     &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters};
   for (DevBuf* b : bufs) b->release();
+  for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
+  for (void* q : ctx->peer_created) cudaFree(q);
   for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -745,6 +747,88 @@ int sspp_gpu_assemble_csr_blocks(sspp_gpu_ctx* ctx, const int64_t* row_ptr_block
   k_assemble_blocks<<<grid, 256, 0, ctx->stream>>>((const long long*)row_ptr_blocks_device, col_blocks_device, world, row_stride,
                                                    col_stride, (const long long*)row_base_device, (long long*)row_ptr_out_device,
                                                    col_out_device, (long long*)overflow_device);
+  LAUNCHED(ctx);
+  return SSPP_OK;
+}
+
+// ---- multi-GPU assembly through peer memory ---------------------------------------------------
+int sspp_gpu_peer_buffer_create(sspp_gpu_ctx* ctx, int64_t bytes, void** device_ptr, uint8_t handle[SSPP_PEER_HANDLE_BYTES]) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (bytes <= 0 || !device_ptr || !handle) return fail(ctx, SSPP_ERR_INVALID, "peer_buffer_create: bad argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == SSPP_PEER_HANDLE_BYTES, "IPC handle size");
+  CK(cudaSetDevice(ctx->device));
+  void* p = nullptr;
+  CK(cudaMalloc(&p, (size_t)bytes));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return cuda_fail(ctx, e, "cudaIpcGetMemHandle");
+  }
+  memcpy(handle, &h, SSPP_PEER_HANDLE_BYTES);
+  ctx->peer_created.push_back(p);
+  *device_ptr = p;
+  return SSPP_OK;
+}
+
+int sspp_gpu_peer_buffer_open(sspp_gpu_ctx* ctx, const uint8_t handle[SSPP_PEER_HANDLE_BYTES], void** device_ptr) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!handle || !device_ptr) return fail(ctx, SSPP_ERR_INVALID, "peer_buffer_open: null argument");
+  CK(cudaSetDevice(ctx->device));
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, SSPP_PEER_HANDLE_BYTES);
+  void* p = nullptr;
+  CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+  ctx->peer_opened.push_back(p);
+  *device_ptr = p;
+  return SSPP_OK;
+}
+
+int sspp_gpu_peer_buffer_release(sspp_gpu_ctx* ctx, void* device_ptr) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  auto c = std::find(ctx->peer_created.begin(), ctx->peer_created.end(), device_ptr);
+  if (c != ctx->peer_created.end()) {
+    ctx->peer_created.erase(c);
+    CK(cudaFree(device_ptr));
+    return SSPP_OK;
+  }
+  auto o = std::find(ctx->peer_opened.begin(), ctx->peer_opened.end(), device_ptr);
+  if (o != ctx->peer_opened.end()) {
+    ctx->peer_opened.erase(o);
+    CK(cudaIpcCloseMemHandle(device_ptr));
+    return SSPP_OK;
+  }
+  return fail(ctx, SSPP_ERR_INVALID, "peer_buffer_release: not a peer buffer of this context");
+}
+
+int sspp_gpu_connect_push_csr(sspp_gpu_ctx* ctx, int world, int rank, const int64_t* edge_counts_device,
+                              const int64_t* row_base_device, int64_t* const* row_ptr_peers, int32_t* const* col_idx_peers,
+                              int64_t col_capacity, int64_t* overflow_device) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!ctx->has_result) return fail(ctx, SSPP_ERR_STATE, "connect_push_csr: no connect result");
+  if (world < 1 || world > SSPP_MAX_PEERS || rank < 0 || rank >= world)
+    return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: world must be 1..SSPP_MAX_PEERS and rank inside it");
+  if (!edge_counts_device || !row_base_device || !row_ptr_peers || !col_idx_peers || !overflow_device || col_capacity < 0)
+    return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: null argument");
+  PushPeers p;
+  p.world = world;
+  p.rank = rank;
+  for (int k = 0; k < SSPP_MAX_PEERS; ++k) {
+    p.rp[k] = nullptr;
+    p.col[k] = nullptr;
+  }
+  for (int k = 0; k < world; ++k) {
+    if (!row_ptr_peers[k] || !col_idx_peers[k]) return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: null peer buffer");
+    if (((uintptr_t)col_idx_peers[k] & 15) != 0) return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: column buffers must be 16-byte aligned");
+    p.rp[k] = (long long*)row_ptr_peers[k];
+    p.col[k] = col_idx_peers[k];
+  }
+  CK(cudaSetDevice(ctx->device));
+  k_push_csr<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(p, (const long long*)edge_counts_device, (const long long*)row_base_device,
+                                                         ctx->row_ptr.as<long long>(), ctx->col_idx.as<int>(),
+                                                         (long long)col_capacity, (long long*)overflow_device);
   LAUNCHED(ctx);
   return SSPP_OK;
 }

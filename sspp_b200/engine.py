@@ -79,6 +79,10 @@ def load_library():
         "sspp_gpu_connect_fetch": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_connect_fetch_device": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_assemble_csr_blocks": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
+        "sspp_gpu_peer_buffer_create": (ctypes.c_int, [c_vp, c_i64, ctypes.POINTER(c_vp), c_vp]),
+        "sspp_gpu_peer_buffer_open": (ctypes.c_int, [c_vp, c_vp, ctypes.POINTER(c_vp)]),
+        "sspp_gpu_peer_buffer_release": (ctypes.c_int, [c_vp, c_vp]),
+        "sspp_gpu_connect_push_csr": (ctypes.c_int, [c_vp, ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
         "sspp_gpu_connect_result_device": (ctypes.c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
         "sspp_gpu_connect_nodes_host": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(ConnectParams), c_vp, c_vp,
                                                        c_i64, ctypes.POINTER(ConnectStats)]),
@@ -227,6 +231,28 @@ class Engine:
         """all arguments are raw device addresses (int) except the three integers"""
         self._ck(self.L.sspp_gpu_assemble_csr_blocks(self.h, c_vp(rp_blocks), c_vp(col_blocks), world, row_stride, col_stride,
                                                      c_vp(row_base), c_vp(rp_out), c_vp(col_out), c_vp(overflow)))
+
+    def peer_buffer_create(self, nbytes):
+        """-> (device address, 64-byte IPC handle as bytes) of a buffer other processes on this box can open"""
+        ptr, h = c_vp(), (ctypes.c_uint8 * 64)()
+        self._ck(self.L.sspp_gpu_peer_buffer_create(self.h, int(nbytes), ctypes.byref(ptr), h))
+        return ptr.value, bytes(h)
+
+    def peer_buffer_open(self, handle):
+        ptr, h = c_vp(), (ctypes.c_uint8 * 64).from_buffer_copy(handle)
+        self._ck(self.L.sspp_gpu_peer_buffer_open(self.h, h, ctypes.byref(ptr)))
+        return ptr.value
+
+    def peer_buffer_release(self, ptr):
+        self._ck(self.L.sspp_gpu_peer_buffer_release(self.h, c_vp(ptr)))
+
+    def connect_push_csr(self, world, rank, edge_counts, row_base, rp_peers, col_peers, col_capacity, overflow):
+        """edge_counts / row_base / overflow: raw device addresses; rp_peers / col_peers: lists of `world`
+        device addresses (entry [rank] = this rank's own buffers)"""
+        a = (c_vp * world)(*[c_vp(int(x)) for x in rp_peers])
+        b = (c_vp * world)(*[c_vp(int(x)) for x in col_peers])
+        self._ck(self.L.sspp_gpu_connect_push_csr(self.h, world, rank, c_vp(edge_counts), c_vp(row_base), a, b,
+                                                  int(col_capacity), c_vp(overflow)))
 
     def connect_result_device(self):
         a, b = c_vp(), c_vp()

@@ -5,6 +5,12 @@ search space, with the map and the node set replicated; no collective touches th
 one exchange step is the assembly of the CSR: an all-gather of (rows, edges) per rank, then of the
 padded row_ptr / col_idx blocks (NCCL has no all-gather-v), then every rank rebases the row pointers
 by the running edge count.  Works on any torch.distributed backend (nccl on GPUs, gloo in the tests).
+
+On the GPUs of one box the product path is PeerCsrAssembler: the ranks exchange CUDA IPC handles of
+their whole-graph CSR buffers once, and from then on every connect ends with ONE kernel per rank
+(sspp_gpu_connect_push_csr) that writes the rank's block, rebased, into all ranks' CSRs through
+NVLink peer memory; NCCL only carries the 8-byte edge counts and the closing barrier.
+GpuCsrAssembler (NCCL all-gather of padded slots + a packing kernel) stays as the comparison.
 """
 import torch
 import torch.distributed as dist
@@ -102,3 +108,97 @@ class GpuCsrAssembler:
             self.overflow.zero_()
             self._size_columns(int(stats.edges))
         raise RuntimeError("CSR assembly: column slots still too small after resizing")
+
+
+class _DeviceArray:
+    """A raw device address as a torch tensor (no copy) via __cuda_array_interface__."""
+
+    def __init__(self, ptr, n, typestr):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
+def device_view(ptr, n, dtype, device):
+    typestr = {torch.int64: "<i8", torch.int32: "<i4"}[dtype]
+    return torch.as_tensor(_DeviceArray(ptr, n, typestr), device=device)
+
+
+class PeerCsrAssembler:
+    """Whole-graph CSR on every rank, written by the ranks themselves over NVLink peer memory.
+
+    Per connect: all-gather of the edge counts (8 bytes per rank; it also tells the peers that this rank
+    is done reading the previous graph), sspp_gpu_connect_push_csr on the engine's stream, and a MAX
+    all-reduce of the overflow word as the closing barrier (after it every rank's pushes have landed).
+    The column buffers are sized on the first call and re-made, on all ranks alike, if a graph outgrows
+    them (every rank sees the same total, so the decision needs no extra message)."""
+
+    def __init__(self, eng, n_nodes, device):
+        self.eng = eng
+        self.world = dist.get_world_size()
+        self.rank = dist.get_rank()
+        self.device = device
+        self.n = n_nodes
+        base = [row_range(n_nodes, g, self.world)[0] for g in range(self.world)] + [n_nodes]
+        self.row_base = torch.tensor(base, dtype=torch.int64, device=device)
+        self.ext_stream = torch.cuda.ExternalStream(eng.stream(), device=device)
+        self.my_count = torch.zeros(1, dtype=torch.int64, device=device)
+        self.counts = torch.zeros(self.world, dtype=torch.int64, device=device)
+        self.overflow = torch.zeros(1, dtype=torch.int64, device=device)
+        self.rp_ptr, self.rp_peers = self._exchange((n_nodes + 1) * 8)
+        self.out_rp = device_view(self.rp_ptr, n_nodes + 1, torch.int64, device)
+        self.col_cap = 0
+        self.col_ptr, self.col_peers, self.out_col = None, None, None
+
+    def _exchange(self, nbytes):
+        """Create this rank's buffer and open every peer's: -> (own address, [address on rank g])."""
+        ptr, handle = self.eng.peer_buffer_create(nbytes)
+        mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(self.device)
+        allh = torch.empty(self.world * 64, dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(allh, mine)
+        raw = allh.cpu().numpy().tobytes()
+        peers = [ptr if g == self.rank else self.eng.peer_buffer_open(raw[g * 64:(g + 1) * 64]) for g in range(self.world)]
+        return ptr, peers
+
+    def _release(self, ptr, peers):
+        torch.cuda.synchronize()
+        for g, q in enumerate(peers):
+            if g != self.rank:
+                self.eng.peer_buffer_release(q)
+        dist.barrier()  # every importer has closed its mapping before the owner frees the memory
+        self.eng.peer_buffer_release(ptr)
+
+    def _size_columns(self, total):
+        if self.col_ptr is not None:
+            self._release(self.col_ptr, self.col_peers)
+        self.col_cap = ((int(total * 1.1) + 1024 + 3) // 4) * 4
+        self.col_ptr, self.col_peers = self._exchange(self.col_cap * 4)
+        self.out_col = device_view(self.col_ptr, self.col_cap, torch.int32, self.device)
+
+    def assemble(self, stats):
+        """stats: the ConnectStats of this rank's sspp_gpu_connect.  Returns (row_ptr, col_idx) device
+        tensors of the whole graph (col_idx is the buffer; row_ptr[-1] entries of it are valid)."""
+        cur = torch.cuda.current_stream()
+        self.my_count.fill_(int(stats.edges))
+        dist.all_gather_into_tensor(self.counts, self.my_count)
+        if self.col_cap == 0:
+            self._size_columns(int(self.counts.sum().item()))
+        for attempt in range(2):
+            self.ext_stream.wait_event(cur.record_event())
+            self.eng.connect_push_csr(self.world, self.rank, self.counts.data_ptr(), self.row_base.data_ptr(), self.rp_peers,
+                                      self.col_peers, self.col_cap, self.overflow.data_ptr())
+            cur.wait_event(self.ext_stream.record_event())
+            dist.all_reduce(self.overflow, op=dist.ReduceOp.MAX)
+            over = int(self.overflow.item())
+            if over == 0:
+                return self.out_rp, self.out_col
+            self.overflow.zero_()
+            self._size_columns(over)
+        raise RuntimeError("CSR assembly: column buffers still too small after resizing")
+
+    def close(self):
+        if self.col_ptr is not None:
+            self._release(self.col_ptr, self.col_peers)
+            self.col_ptr = None
+        if self.rp_ptr is not None:
+            self._release(self.rp_ptr, self.rp_peers)
+            self.rp_ptr = None

@@ -1,0 +1,154 @@
+"""Multi-GPU CSR assembly through peer memory (sspp_gpu_connect_push_csr): the blocks the ranks push
+must reproduce, byte for byte, the CSR of one connect over all rows.
+
+One GPU is enough for the kernel's logic: several contexts on the same device play the ranks and
+ordinary device tensors play the peers' buffers.  The CUDA-IPC path (one process per GPU, the real
+deployment) runs when the box has two or more GPUs and is skipped otherwise."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from sspp_b200 import scenes
+from sspp_b200.engine import Engine, SsppError
+
+pytestmark = pytest.mark.gpu
+BOX = (0.5, 0.5, 0.3)
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def scene(eng_list, n_vox=64, res=0.3, seed=5):
+    km, dm, occ, known = scenes.synthetic_map(n_vox=n_vox, res=res, seed=seed, n_boxes=8, n_spheres=6, region=n_vox * res * 0.75)
+    for e in eng_list:
+        e.map_create(res, km, dm, True)
+        e.map_upload_dense(occ, known)
+
+
+@pytest.mark.parametrize("world,cuts", [(1, None), (2, None), (3, (0.21, 0.55)), (5, None)])
+def test_push_equals_one_gpu_csr(eng, world, cuts):
+    import torch
+    dev = torch.device("cuda", 0)
+    nodes = scenes.uniform_nodes(6000, extent=13.0, seed=9)
+    n = len(nodes)
+    scene([eng])
+    eng.set_nodes(nodes)
+    st = eng.connect(radius=1.5, box=BOX)
+    rp_full, col_full = eng.connect_fetch(st)
+    assert st.edges > 1000
+
+    bounds = [0] + ([int(c * n) for c in cuts] if cuts else [(n * g) // world for g in range(1, world)]) + [n]
+    ranks = [Engine(0) for _ in range(world)]
+    try:
+        scene(ranks)
+        stats = []
+        for g, e in enumerate(ranks):
+            e.set_nodes(nodes)
+            stats.append(e.connect(radius=1.5, box=BOX, rows=(bounds[g], bounds[g + 1])))
+        counts = torch.tensor([s.edges for s in stats], dtype=torch.int64, device=dev)
+        assert int(counts.sum()) == st.edges
+        row_base = torch.tensor(bounds, dtype=torch.int64, device=dev)
+        cap = ((st.edges + 3) // 4) * 4 + 8
+        out_rp = [torch.full((n + 1,), -1, dtype=torch.int64, device=dev) for _ in range(world)]
+        out_col = [torch.full((cap,), -1, dtype=torch.int32, device=dev) for _ in range(world)]
+        over = torch.zeros(1, dtype=torch.int64, device=dev)
+        torch.cuda.synchronize()
+        for g, e in enumerate(ranks):
+            e.connect_push_csr(world, g, counts.data_ptr(), row_base.data_ptr(), [t.data_ptr() for t in out_rp],
+                               [t.data_ptr() for t in out_col], cap, over.data_ptr())
+        for e in ranks:
+            e.synchronize()
+        assert int(over.item()) == 0
+        for k in range(world):
+            assert np.array_equal(out_rp[k].cpu().numpy(), rp_full), "row_ptr of peer %d differs" % k
+            c = out_col[k].cpu().numpy()
+            assert np.array_equal(c[: st.edges], col_full), "col_idx of peer %d differs" % k
+            assert (c[st.edges:] == -1).all(), "push wrote past the graph's edges"
+
+        # a graph that does not fit: nothing is written, every rank reports the total
+        out_rp2 = torch.full((n + 1,), -1, dtype=torch.int64, device=dev)
+        out_col2 = torch.full((cap,), -1, dtype=torch.int32, device=dev)
+        ranks[0].connect_push_csr(world, 0, counts.data_ptr(), row_base.data_ptr(), [out_rp2.data_ptr()] * world,
+                                  [out_col2.data_ptr()] * world, st.edges - 1, over.data_ptr())
+        ranks[0].synchronize()
+        assert int(over.item()) == st.edges
+        assert (out_rp2 == -1).all() and (out_col2 == -1).all()
+    finally:
+        for e in ranks:
+            e.close()
+
+
+def test_push_argument_errors(eng):
+    import torch
+    dev = torch.device("cuda", 0)
+    t = torch.zeros(8, dtype=torch.int64, device=dev)
+    with pytest.raises(SsppError):  # no connect result yet
+        eng.connect_push_csr(1, 0, t.data_ptr(), t.data_ptr(), [t.data_ptr()], [t.data_ptr()], 8, t.data_ptr())
+    eng.set_nodes(scenes.lattice_nodes(4, 1.0))
+    eng.connect(radius=1.5, use_map=False)
+    with pytest.raises(SsppError):  # rank outside the world
+        eng.connect_push_csr(2, 2, t.data_ptr(), t.data_ptr(), [t.data_ptr()] * 2, [t.data_ptr()] * 2, 8, t.data_ptr())
+    with pytest.raises(SsppError):  # more ranks than SSPP_MAX_PEERS
+        eng.connect_push_csr(17, 0, t.data_ptr(), t.data_ptr(), [t.data_ptr()] * 17, [t.data_ptr()] * 17, 8, t.data_ptr())
+    with pytest.raises(SsppError):  # column buffer not 16-byte aligned
+        eng.connect_push_csr(1, 0, t.data_ptr(), t.data_ptr(), [t.data_ptr()], [t.data_ptr() + 4], 8, t.data_ptr())
+    with pytest.raises(SsppError):  # not a peer buffer of this context
+        eng.peer_buffer_release(t.data_ptr())
+    ptr, handle = eng.peer_buffer_create(4096)
+    assert ptr != 0 and len(handle) == 64
+    eng.peer_buffer_release(ptr)
+
+
+def _ipc_rank(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", device_id=dev)
+    from sspp_b200 import sharded
+    e = Engine(rank)
+    try:
+        scene([e])
+        nodes = scenes.uniform_nodes(20000, extent=13.0, seed=9)
+        n = len(nodes)
+        e.set_nodes(nodes)
+        asm = sharded.PeerCsrAssembler(e, n, dev)
+        lo, hi = sharded.row_range(n, rank, world)
+        ok = True
+        for radius in (1.0, 1.5, 1.0):  # the second graph outgrows the first one's column buffers
+            st = e.connect(radius=radius, box=BOX, rows=(lo, hi))
+            rp, col = asm.assemble(st)
+            rp, col = rp.cpu().numpy(), col.cpu().numpy()
+            sf = e.connect(radius=radius, box=BOX)
+            rpf, colf = e.connect_fetch(sf)
+            ok = ok and np.array_equal(rp, rpf) and np.array_equal(col[: sf.edges], colf)
+            dist.barrier()
+        asm.close()
+        q.put((rank, bool(ok)))
+    finally:
+        e.close()
+        dist.destroy_process_group()
+
+
+def test_peer_ipc_two_processes(built):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs on one box")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    world = 2
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_ipc_rank, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=240)
+    alive = [p for p in procs if p.is_alive()]
+    for p in alive:
+        p.kill()
+    assert not alive, "a rank hung"
+    res = sorted(q.get(timeout=5) for _ in range(world))
+    assert res == [(0, True), (1, True)]
