@@ -187,6 +187,18 @@ int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_de
 int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n, const sspp_connect_params* params,
                                 int64_t* row_ptr, int32_t* col_idx, int64_t col_capacity, sspp_connect_stats* stats);
 
+/* ---- node store: batched SearchSpace::insertNode --------------------------------------------
+ * Replaces the per-pose list scan of SearchSpace::insertNode / nodeExists (src/searchspace.cpp:69-105,
+ * 164-175) with samePosition / isEqual (include/sspp/utils.h:386-390, 231-239): poses (n x 7 doubles:
+ * x y z qx qy qz qw) are offered in insertion order; pose i is stored unless an already stored pose
+ * equals it in all seven components, fabs(a-b) < tolerance each (the reference's constant is 1E-12).
+ * keep[i] = 1 when pose i is stored.  dup_of (may be NULL): -1 for stored poses, else the insertion
+ * index of the node insertNode returns (nodeExists walks from the head, i.e. the LATEST stored match).
+ * *stored (may be NULL) = number of poses stored.  Same verdicts as the sequential scan, including
+ * the non-transitive chains a ~ b ~ c.  Positions must be finite (SSPP_ERR_INVALID otherwise). */
+int sspp_gpu_dedup_poses(sspp_gpu_ctx* ctx, const double* poses, int64_t n, double tolerance, uint8_t* keep, int64_t* dup_of,
+                         int64_t* stored);
+
 /* ---- batched segment / cell / ray queries --------------------------------------------------- */
 
 /* Replaces: n calls of OctomapManager::getLineStatusBoundingBox(start,end,box) (upstream; called at

@@ -8,6 +8,8 @@
 //                             DistanceHeuristic::isConnectionConditionSatisfied
 //                                                                 src/distance_heuristic.cpp:99-127
 //                             Dist                                include/sspp/utils.h:356-359
+//   orc_dedup_poses        <- SearchSpace::insertNode / nodeExists   src/searchspace.cpp:69-105,164-175
+//                             samePosition / isEqual                 include/sspp/utils.h:386-390,231-239
 //   orc_visibility         <- AUTHORED SPEC (CoverageHeuristic has no source in the reference,
 //                             SURVEY.md F1): PCL-FrustumCulling-style six-plane test in float,
 //                             then octomap castRay towards the point.  Stated in full below.
@@ -374,6 +376,30 @@ long orc_visibility(void* w, const double* poses, long nv, const float fr[4], co
   view_ptr[nv] = total;
   if (counters) { counters[0] = rays; counters[1] = steps; }
   return total;
+}
+
+// SearchSpace::insertNode over a batch, in insertion order (src/searchspace.cpp:69-105): pose i is
+// stored unless nodeExists (:164-175) finds a stored pose equal to it — samePosition, i.e. all seven
+// components with fabs(a-b) < 1E-12 (include/sspp/utils.h:231-239,386-390).  nodeExists walks the list
+// from the head, and the head is the LATEST stored node, so the node it returns is the matching
+// stored pose with the largest insertion index.  keep[i] = 1 when pose i was stored; dup_of[i] = -1
+// for stored poses, else the insertion index of the node insertNode returned.  Returns the number stored.
+long orc_dedup_poses(const double* poses, long n, uint8_t* keep, int64_t* dup_of) {
+  std::vector<long> stored;  // insertion indices, oldest first
+  for (long i = 0; i < n; ++i) {
+    const double* a = poses + 7 * i;
+    long found = -1;
+    for (long s = (long)stored.size() - 1; s >= 0 && found < 0; --s) {
+      const double* b = poses + 7 * stored[s];
+      bool same = true;
+      for (int c = 0; c < 7 && same; ++c) same = std::fabs(a[c] - b[c]) < 1E-12;
+      if (same) found = stored[s];
+    }
+    keep[i] = found < 0 ? 1 : 0;
+    if (dup_of) dup_of[i] = found;
+    if (found < 0) stored.push_back(i);
+  }
+  return (long)stored.size();
 }
 
 }  // extern "C"

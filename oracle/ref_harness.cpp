@@ -134,6 +134,14 @@ void ref_insert_node(void* h, const double pose[7]) {
   R->planner->insertNode(mkpose(pose));
 }
 
+// id of the node SearchSpace::insertNode returns: the new node's own id, or the stored node's when
+// the pose is refused (ids count insertNode calls, src/searchspace.cpp:64-67)
+long ref_insert_node_id(void* h, const double pose[7]) {
+  RefPlanner* R = (RefPlanner*)h;
+  SSPP::SearchSpaceNode* t = R->planner->insertNode(mkpose(pose));
+  return t ? (long)t->id : -1;
+}
+
 long ref_num_nodes(void* h) {
   RefPlanner* R = (RefPlanner*)h;
   long n = 0;

@@ -72,6 +72,9 @@ struct sspp_gpu_ctx {
   // peer-addressable buffers (multi-GPU CSR assembly): created here / opened from a peer's IPC handle
   std::vector<void*> peer_created, peer_opened;
 
+  // batched insertNode (pose de-duplication)
+  DevBuf dd_poses, dd_xyz, dd_state, dd_pend, dd_dup, dd_keep, dd_misc;
+
   // generic query scratch
   DevBuf q0, q1, q2, q3, q4;
 

@@ -32,6 +32,7 @@ using namespace sspp;
 #include "connect_kernels.cuh"
 #include "query_kernels.cuh"
 #include "visibility_kernels.cuh"
+#include "dedup_kernels.cuh"
 
 namespace {
 // ------------------------------------------------------------------------------------------------
@@ -119,7 +120,8 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
                     &ctx->rows, &ctx->row_flag, &ctx->row_free, &ctx->cand_count, &ctx->cand_off, &ctx->candA, &ctx->candB,
                     &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice, &ctx->work_rows,
                     &ctx->q0, &ctx->q1, &ctx->q2, &ctx->q3, &ctx->q4, &ctx->pts, &ctx->vis_cnt, &ctx->vis_ptr,
-                    &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters};
+                    &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
+                    &ctx->dd_pend, &ctx->dd_dup, &ctx->dd_keep, &ctx->dd_misc};
   for (DevBuf* b : bufs) b->release();
   for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
   for (void* q : ctx->peer_created) cudaFree(q);
@@ -856,6 +858,121 @@ int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n,
 int sspp_gpu_connect_timings(sspp_gpu_ctx* ctx, float ms[8]) {
   if (!ctx || !ms) return SSPP_ERR_INVALID;
   for (int i = 0; i < 8; ++i) ms[i] = ctx->timings[i];
+  return SSPP_OK;
+}
+
+// ---- batched SearchSpace::insertNode -----------------------------------------------------------
+int sspp_gpu_dedup_poses(sspp_gpu_ctx* ctx, const double* poses, int64_t n, double tolerance, uint8_t* keep, int64_t* dup_of,
+                         int64_t* stored) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (n < 0 || (n > 0 && (!poses || !keep))) return fail(ctx, SSPP_ERR_INVALID, "dedup_poses: null argument");
+  if (!(tolerance > 0.0) || !std::isfinite(tolerance)) return fail(ctx, SSPP_ERR_INVALID, "dedup_poses: tolerance must be > 0");
+  if (n >= (int64_t)0x7fffffff) return fail(ctx, SSPP_ERR_RANGE, "dedup_poses: pose indices must fit in int32");
+  if (stored) *stored = 0;
+  if (n == 0) return SSPP_OK;
+  CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  CK(ctx->dd_poses.reserve((size_t)n * 56));
+  CK(ctx->dd_xyz.reserve((size_t)n * 24));
+  CK(ctx->dd_state.reserve((size_t)n));
+  CK(ctx->dd_keep.reserve((size_t)n));
+  CK(ctx->dd_pend.reserve((size_t)n * 4));
+  CK(ctx->dd_misc.reserve(16 * 8));
+  unsigned long long* misc = ctx->dd_misc.as<unsigned long long>();  // [0..6] bounding box, [8..10] counters
+  static const unsigned long long init[16] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+  CK(cudaMemcpyAsync(misc, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  CK(cudaMemcpyAsync(ctx->dd_poses.p, poses, (size_t)n * 56, cudaMemcpyHostToDevice, st));
+  const double* dposes = ctx->dd_poses.as<double>();
+  k_pose_xyz<<<ceil_div(n, 256), 256, 0, st>>>(dposes, n, ctx->dd_xyz.as<double>());
+  LAUNCHED(ctx);
+  k_bbox<<<std::min(ceil_div(n, 256), 148 * 8), 256, 0, st>>>(ctx->dd_xyz.as<double>(), n, misc);
+  LAUNCHED(ctx);
+  unsigned long long hb[7];
+  CK(cudaMemcpyAsync(hb, misc, sizeof(hb), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (hb[6]) return fail(ctx, SSPP_ERR_INVALID, "dedup_poses: positions must be finite");
+
+  // grid: about one pose per cell, cell edge never below 4 x tolerance (so that every match of a pose
+  // lies in its own or an adjacent cell whatever the rounding of the cell index)
+  NodeGrid g;
+  double ext[3], volume = 1.0, max_ext = 0.0;
+  int axes = 0;
+  for (int a = 0; a < 3; ++a) {
+    g.min[a] = dec_f64(hb[a]);
+    g.max[a] = dec_f64(hb[3 + a]);
+    ext[a] = g.max[a] - g.min[a];
+    max_ext = std::max(max_ext, ext[a]);
+    if (ext[a] > 0) { volume *= ext[a]; ++axes; }
+  }
+  double cell = axes ? pow(volume / (double)n, 1.0 / axes) : 1.0;
+  cell = std::max(cell, std::max(4.0 * tolerance, max_ext * 1e-9));
+  if (!(cell > 0.0) || !std::isfinite(cell)) cell = 1.0;
+  for (;;) {
+    double total = 1;
+    for (int a = 0; a < 3; ++a) total *= floor(ext[a] / cell) + 2.0;
+    if (total <= (double)(1 << 24)) break;
+    cell *= 1.26;
+  }
+  g.inv_cell = 1.0 / cell;
+  int64_t ncells = 1;
+  for (int a = 0; a < 3; ++a) { g.n[a] = (int)floor(ext[a] * g.inv_cell) + 1; ncells *= g.n[a]; }
+
+  CK(ctx->cell_of.reserve((size_t)n * 4));
+  CK(ctx->cell_start.reserve((size_t)(ncells + 1) * 4));
+  CK(ctx->cell_cursor.reserve((size_t)(ncells + 1) * 4));
+  CK(ctx->sx.reserve((size_t)n * sizeof(NodeRec)));
+  CK(cudaMemsetAsync(ctx->cell_cursor.p, 0, (size_t)(ncells + 1) * 4, st));
+  k_cell_hist<<<ceil_div(n, 256), 256, 0, st>>>(ctx->dd_xyz.as<double>(), n, g, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>());
+  LAUNCHED(ctx);
+  {
+    int rc = scan_exclusive<int>(ctx, ctx->cell_cursor.as<int>(), ncells, ctx->cell_start.as<int>());
+    if (rc) return rc;
+  }
+  CK(cudaMemcpyAsync(ctx->cell_cursor.p, ctx->cell_start.p, (size_t)ncells * 4, cudaMemcpyDeviceToDevice, st));
+  k_cell_scatter<<<ceil_div(n, 256), 256, 0, st>>>(ctx->dd_xyz.as<double>(), n, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>(),
+                                                   ctx->sx.as<NodeRec>());
+  LAUNCHED(ctx);
+
+  uint8_t* state = ctx->dd_state.as<uint8_t>();
+  int* pend = ctx->dd_pend.as<int>();
+  unsigned long long* counters = misc + 8;
+  k_dedup_first<<<ceil_div(n, 256), 256, 0, st>>>(g, ctx->cell_start.as<int>(), ctx->sx.as<NodeRec>(), n, dposes, tolerance, state,
+                                                  pend, counters);
+  LAUNCHED(ctx);
+  unsigned long long hc[3] = {0, 0, 0};
+  CK(cudaMemcpyAsync(hc, counters, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const int64_t npend = (int64_t)hc[0];
+  unsigned long long waiting = npend;
+  while (waiting > 0) {
+    CK(cudaMemsetAsync(counters + 1, 0, 8, st));
+    k_dedup_round<<<ceil_div(npend, 256), 256, 0, st>>>(g, ctx->cell_start.as<int>(), ctx->sx.as<NodeRec>(), dposes, tolerance,
+                                                       state, pend, npend, counters);
+    LAUNCHED(ctx);
+    unsigned long long left = 0;
+    CK(cudaMemcpyAsync(&left, counters + 1, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    // the pending pose with the smallest index always resolves, so every round makes progress
+    if (left >= waiting) return fail(ctx, SSPP_ERR_CUDA, "dedup_poses: a round resolved nothing");
+    waiting = left;
+  }
+  if (dup_of) {
+    CK(ctx->dd_dup.reserve((size_t)n * 8));
+    k_dedup_init_dup<<<ceil_div(n, 256), 256, 0, st>>>(n, ctx->dd_dup.as<long long>());
+    LAUNCHED(ctx);
+    if (npend) {
+      k_dedup_final<<<ceil_div(npend, 256), 256, 0, st>>>(g, ctx->cell_start.as<int>(), ctx->sx.as<NodeRec>(), dposes, tolerance,
+                                                         state, pend, npend, ctx->dd_dup.as<long long>());
+      LAUNCHED(ctx);
+    }
+    CK(cudaMemcpyAsync(dup_of, ctx->dd_dup.p, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+  }
+  k_dedup_keep<<<ceil_div(n, 256), 256, 0, st>>>(state, n, ctx->dd_keep.as<uint8_t>(), counters);
+  LAUNCHED(ctx);
+  CK(cudaMemcpyAsync(keep, ctx->dd_keep.p, (size_t)n, cudaMemcpyDeviceToHost, st));
+  CK(cudaMemcpyAsync(hc, counters, sizeof(hc), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  if (stored) *stored = (int64_t)hc[2];
   return SSPP_OK;
 }
 

@@ -87,6 +87,7 @@ def load_library():
         "sspp_gpu_connect_nodes_host": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(ConnectParams), c_vp, c_vp,
                                                        c_i64, ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_timings": (ctypes.c_int, [c_vp, c_vp]),
+        "sspp_gpu_dedup_poses": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.c_double, c_vp, c_vp, ctypes.POINTER(c_i64)]),
         "sspp_gpu_check_segments": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp]),
         "sspp_gpu_check_segments_noalloc": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp]),
         "sspp_gpu_validity": (ctypes.c_int, [c_vp, c_vp, c_i64, c_vp, c_vp]),
@@ -271,6 +272,17 @@ class Engine:
         t = np.zeros(8, dtype=np.float32)
         self._ck(self.L.sspp_gpu_connect_timings(self.h, _p(t)))
         return t
+
+    # ---- node store
+    def dedup_poses(self, poses, tolerance=1e-12, want_dup_of=True):
+        """Batched SearchSpace::insertNode: (n,7) poses in insertion order -> (keep uint8[n], dup_of int64[n] or None, stored)."""
+        P = np.ascontiguousarray(poses, dtype=np.float64).reshape(-1, 7)
+        keep = np.zeros(len(P), dtype=np.uint8)
+        dup = np.zeros(len(P), dtype=np.int64) if want_dup_of else None
+        stored = c_i64(0)
+        self._ck(self.L.sspp_gpu_dedup_poses(self.h, _p(P), len(P), float(tolerance), _p(keep),
+                                             _p(dup) if dup is not None else None, ctypes.byref(stored)))
+        return keep, dup, stored.value
 
     # ---- queries
     def check_segments(self, starts, ends, box=(0.5, 0.5, 0.3)):

@@ -176,6 +176,11 @@ class RefPlanner:
         for i in range(len(P)):
             self.L.ref_insert_node(self.h, _p(P[i]))
 
+    def insert_nodes_ids(self, poses):
+        """-> id of the node insertNode returned for every pose (its own id when stored)"""
+        P = _f64(poses, 7)
+        return np.array([self.L.ref_insert_node_id(self.h, _p(P[i])) for i in range(len(P))], dtype=np.int64)
+
     def nodes(self):
         n = self.L.ref_num_nodes(self.h)
         P = np.zeros((n, 7))
@@ -258,6 +263,8 @@ class Oracle:
         L.orc_cast_rays.argtypes = [vp, vp, vp, lng, ctypes.c_int, vp, vp, vp, vp]
         L.orc_frustum_consts.argtypes = [dbl, dbl, dbl, dbl, vp]
         L.orc_frustum_planes.argtypes = [vp, vp, vp]
+        L.orc_dedup_poses.restype = lng
+        L.orc_dedup_poses.argtypes = [vp, lng, vp, vp]
         L.orc_visibility.restype = lng
         L.orc_visibility.argtypes = [vp, vp, lng, vp, vp, lng, vp, vp, lng, vp]
         if self.has_ref:
@@ -267,6 +274,8 @@ class Oracle:
             L.ref_set_goal.argtypes = [vp, vp, dbl]
             L.ref_generate_grid.argtypes = [vp, vp, vp, ctypes.c_float, ctypes.c_int, ctypes.c_float]
             L.ref_insert_node.argtypes = [vp, vp]
+            L.ref_insert_node_id.restype = lng
+            L.ref_insert_node_id.argtypes = [vp, vp]
             L.ref_num_nodes.restype = lng
             L.ref_num_nodes.argtypes = [vp]
             L.ref_get_nodes.argtypes = [vp, vp, vp]
@@ -303,6 +312,14 @@ class Oracle:
         out = np.zeros(4, dtype=np.float32)
         self.L.orc_frustum_consts(hfov, vfov, near, far, _p(out))
         return out
+
+    def dedup_poses(self, poses):
+        """Restated SearchSpace::insertNode over a batch -> (keep uint8[n], dup_of int64[n])."""
+        P = _f64(poses, 7)
+        keep = np.zeros(len(P), dtype=np.uint8)
+        dup = np.zeros(len(P), dtype=np.int64)
+        self.L.orc_dedup_poses(_p(P), len(P), _p(keep), _p(dup))
+        return keep, dup
 
     def connect(self, world, xyz, radius, box=(0.5, 0.5, 0.3), mode=0):
         """Restated O(N^2) connectNodes -> (row_ptr, col_idx, counters[cand, same, steps, rays])."""
