@@ -171,14 +171,39 @@ struct ConnectArgs {
   int use_map;
   int use_pyramid;
   TileShape ts;
+  // Pair storage.  slot > 0: row r owns the fixed slot [r*slot, r*slot + slot) of the pair buffers and
+  // cand_count[r] says how many entries it holds — the counting pass writes the pairs itself, no scan
+  // and no second neighbour pass; a row with more than `slot` pairs raises counters[8] and the host
+  // repeats the pass with scanned offsets (slot == 0: row r owns [cand_off[r], cand_off[r+1])).
+  int slot;
+  const int* cand_count;
 };
+
+// where row r keeps its pairs
+__device__ __forceinline__ void row_span(const ConnectArgs& a, const long long* __restrict__ cand_off, int r, long long& off,
+                                         int& n) {
+  if (a.slot) {
+    off = (long long)r * a.slot;
+    n = a.cand_count[r];
+  } else {
+    off = cand_off[r];
+    n = (int)(cand_off[r + 1] - off);
+  }
+}
+// true when the pair buffers do not hold this pass's pairs (too small / a slot overflowed): every
+// consumer kernel then returns at once and the host repeats the phase
+__device__ __forceinline__ bool pairs_unusable(const ConnectArgs& a, const long long* __restrict__ cand_off,
+                                               const unsigned long long* counters, long long pair_cap) {
+  return a.slot ? (counters[8] != 0) : (cand_off[a.nrows] > pair_cap);
+}
 
 // counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows, [3] voxel steps (instrumented),
 //           [4] next work row (edge kernel's ticket), [5] pairs accepted by their key box,
-//           [6] pairs that ran the ray lattice, [7] number of work rows
+//           [6] pairs that ran the ray lattice, [7] number of work rows, [8] rows that overflowed their slot
 //
 // One thread per source row walks the 27 neighbouring cells (9 contiguous ranges of the cell-sorted
-// arrays).  FILL == false: count the in-radius pairs and test the row's reach against the pyramid.
+// arrays).  FILL == false: count the in-radius pairs and test the row's reach against the pyramid;
+// in slot mode also write the pairs into the row's slot (then no FILL pass runs).
 // FILL == true (after the scan of the counts): write the pairs — (sorted position, list index with
 // bit 31 = same position) — to cand[], in cell order; the edge kernel orders them by list index.
 template <bool FILL>
@@ -198,7 +223,8 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
     int cx = grid_cell_axis(a.g, px, 0), cy = grid_cell_axis(a.g, py, 1), cz = grid_cell_axis(a.g, pz, 2);
     int x0 = max(cx - 1, 0), x1 = min(cx + 1, a.g.n[0] - 1);
     int cnt = 0, tst = 0;
-    long long w = FILL ? cand_off[r] : 0;
+    long long w = FILL ? cand_off[r] : (long long)r * a.slot;
+    const bool slots = !FILL && a.slot > 0;
     for (int zz = max(cz - 1, 0); zz <= min(cz + 1, a.g.n[2] - 1); ++zz)
       for (int yy = max(cy - 1, 0); yy <= min(cy + 1, a.g.n[1] - 1); ++yy) {
         int base = (zz * a.g.n[1] + yy) * a.g.n[0];
@@ -210,6 +236,7 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
           if (FILL) {
             if (pc) cand[w++] = make_int2(j, (int)o.idx | (pc == 2 ? (int)0x80000000 : 0));
           } else {
+            if (slots && pc && cnt < a.slot) cand[w + cnt] = make_int2(j, (int)o.idx | (pc == 2 ? (int)0x80000000 : 0));
             cnt += (pc != 0);
             tst += (pc == 1);
           }
@@ -217,6 +244,7 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
       }
     if (!FILL) {
       cand_count[r] = cnt;
+      if (slots && cnt > a.slot) atomicAdd(counters + 8, 1ull);
       uint8_t fr = 0;
       if (a.use_map && a.use_pyramid && tst > 0) fr = row_reach_is_free(m, px, py, pz, a.ts.reach) ? 1 : 0;
       row_free[r] = fr;
@@ -477,16 +505,18 @@ __device__ __forceinline__ int2 sort_row_pairs(EdgeSmemSort& sb, int warp, int l
 // all: every pair is an edge.  One warp per row: sort by list index, write.
 __global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long long* __restrict__ cand_off,
                                                      const uint8_t* __restrict__ row_free, const int2* __restrict__ candA,
-                                                     int2* candB, int* __restrict__ acc, int* __restrict__ deg, long long pair_cap) {
+                                                     int2* candB, int* __restrict__ acc, int* __restrict__ deg,
+                                                     const unsigned long long* counters, long long pair_cap) {
   __shared__ EdgeSmemSort sb;
-  if (cand_off[a.nrows] > pair_cap) return;
+  if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * EDGE_WARPS + warp;
   if (t >= a.nrows) return;
   const int s = a.rows ? a.rows[t] : t;
   const int r = (int)(a.sn[s].idx - a.lo);
-  const long long off = cand_off[r];
-  const int n = (int)(cand_off[r + 1] - off);
+  long long off;
+  int n;
+  row_span(a, cand_off, r, off, n);
   if (a.use_map && !row_free[r] && n > 0) return;  // a work row: k_edges writes it
   if (n == 0) {
     if (lane == 0) deg[r] = 0;
@@ -510,8 +540,9 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
   const int s = a.rows ? a.rows[t] : t;
   const NodeRec me = load_node(a.sn + s);
   const int r = (int)(me.idx - a.lo);
-  const long long off = cand_off[r];
-  const int n = (int)(cand_off[r + 1] - off);
+  long long off;
+  int n;
+  row_span(a, cand_off, r, off, n);
   const int2 c0 = sort_row_pairs(sm.sort, warp, lane, candA, candB, off, n);
 
   const double px = me.x, py = me.y, pz = me.z;
@@ -673,7 +704,7 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
         const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
         int* __restrict__ deg, unsigned long long* counters, long long pair_cap) {
   __shared__ EdgeSmem sm;
-  if (cand_off[a.nrows] > pair_cap) return;
+  if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
   RayLattice& lat = sm.lat;
   for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
   __syncthreads();
@@ -697,17 +728,19 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   }
 }
 
-// CSR compaction: one warp per row, coalesced copy of the accepted prefix
-__global__ void k_compact(const long long* __restrict__ cand_off, const int* __restrict__ deg,
+// CSR compaction: eight lanes per row (rows hold a dozen or two edges), coalesced copy of the accepted prefix
+constexpr int COMPACT_LANES = 8;
+__global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off, const int* __restrict__ deg,
                           const long long* __restrict__ row_ptr, const int* __restrict__ acc, int* __restrict__ col,
-                          int nrows, long long pair_cap) {
-  if (cand_off[nrows] > pair_cap) return;
-  int r = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-  int lane = threadIdx.x & 31;
-  if (r >= nrows) return;
-  long long src = cand_off[r], dst = row_ptr[r];
-  int d = deg[r];
-  for (int e = lane; e < d; e += 32) col[dst + e] = acc[src + e];
+                          const unsigned long long* counters, long long pair_cap) {
+  if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
+  const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int r = (int)(gt / COMPACT_LANES);
+  const int sub = (int)(gt % COMPACT_LANES);
+  if (r >= a.nrows) return;
+  const long long src = a.slot ? (long long)r * a.slot : cand_off[r], dst = row_ptr[r];
+  const int d = deg[r];
+  for (int e = sub; e < d; e += COMPACT_LANES) col[dst + e] = acc[src + e];
 }
 
 // Multi-GPU CSR assembly: every rank holds the all-gathered, padded blocks of all ranks

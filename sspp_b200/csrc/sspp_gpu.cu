@@ -13,6 +13,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -610,52 +611,69 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->cand_count.reserve((size_t)nrows * 4));
   CK(ctx->row_free.reserve((size_t)nrows));
   CK(ctx->cand_off.reserve((size_t)(nrows + 1) * 8));
-  CK(ctx->counters.reserve(8 * 8));
-  CK(cudaMemsetAsync(ctx->counters.p, 0, 8 * 8, st));
+  CK(ctx->counters.reserve(16 * 8));
+  CK(cudaMemsetAsync(ctx->counters.p, 0, 16 * 8, st));
   CK(ctx->work_rows.reserve((size_t)nrows * 4));
   CK(ctx->deg.reserve((size_t)nrows * 4));
-  k_count<false><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
-                                                      ctx->counters.as<unsigned long long>(), nullptr, nullptr,
-                                                      ctx->work_rows.as<int>(), 0);
-  LAUNCHED(ctx);
-  {
-    int rc = scan_exclusive<long long>(ctx, ctx->cand_count.as<int>(), nrows, ctx->cand_off.as<long long>());
-    if (rc) return rc;
-  }
-  CK(cudaEventRecord(ctx->ev[2], st));
+  a.cand_count = ctx->cand_count.as<int>();
 
-  // --- 4/5. edge test and CSR.  The pair buffers keep their size from call to call; the kernels
-  // refuse to run when the pair count exceeds it, which the host sees at the single synchronisation
-  // at the end (it then grows the buffers and repeats this phase).  Only the first call, with no
-  // buffers yet, has to wait for the count here.
-  auto pair_capacity = [&]() -> long long {
-    return (long long)std::min(std::min(ctx->candA.cap / 8, ctx->candB.cap / 8), std::min(ctx->acc.cap / 4, ctx->col_idx.cap / 4));
-  };
+  // Pair storage: with few pairs per row (the expected count follows from the node density: a ball of
+  // the radius holds 4.19 / 27 of the nodes of its 27 cells) every row gets a fixed slot and the
+  // counting pass writes the pairs itself; otherwise — or when a row overflows its slot — the counts
+  // are scanned and a second neighbour pass fills the pairs.
   auto reserve_pairs = [&](long long c) -> cudaError_t {
-    const size_t want = (size_t)std::max<long long>(c + c / 16 + 1024, 1);
+    const size_t want = (size_t)std::max<long long>(c, 1);
     cudaError_t e;
     if ((e = ctx->candA.reserve(want * 8)) != cudaSuccess) return e;
     if ((e = ctx->candB.reserve(want * 8)) != cudaSuccess) return e;
     if ((e = ctx->acc.reserve(want * 4)) != cudaSuccess) return e;
     return ctx->col_idx.reserve(want * 4);
   };
+  {
+    const double lambda = 4.19 * (sharded ? 1.1 * (double)nrows : (double)n) / (double)ncells;
+    a.slot = lambda <= 10.0 ? 32 : (lambda <= 28.0 ? 64 : 0);
+    if (const char* env = getenv("SSPP_CONNECT_SLOT")) a.slot = std::max(0, atoi(env));
+    if (a.slot && (double)nrows * a.slot > 3.0e9) a.slot = 0;  // slots beyond ~36 GB of pair buffers: scan instead
+    if (a.slot) CK(reserve_pairs((long long)nrows * a.slot));
+  }
+  k_count<false><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
+                                                      ctx->counters.as<unsigned long long>(), nullptr,
+                                                      a.slot ? ctx->candA.as<int2>() : nullptr, ctx->work_rows.as<int>(), 0);
+  LAUNCHED(ctx);
+  if (!a.slot) {
+    int rc = scan_exclusive<long long>(ctx, ctx->cand_count.as<int>(), nrows, ctx->cand_off.as<long long>());
+    if (rc) return rc;
+  }
+  CK(cudaEventRecord(ctx->ev[2], st));
+
+  // --- 4/5. edge test and CSR.  The pair buffers keep their size from call to call; the kernels
+  // refuse to run when the pairs do not fit (a slot overflowed / the scanned total exceeds the
+  // buffers), which the host sees at the single synchronisation at the end; it then switches to
+  // scanned offsets or grows the buffers and repeats this phase.  Only a scanned pass with no buffers
+  // yet has to wait for the count here.
+  auto pair_capacity = [&]() -> long long {
+    return (long long)std::min(std::min(ctx->candA.cap / 8, ctx->candB.cap / 8), std::min(ctx->acc.cap / 4, ctx->col_idx.cap / 4));
+  };
   long long C = -1;
-  if (pair_capacity() == 0) {
+  if (!a.slot && pair_capacity() == 0) {
     CK(cudaMemcpyAsync(&C, ctx->cand_off.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    CK(reserve_pairs(C));
+    CK(reserve_pairs(C + C / 16 + 1024));
   }
-  unsigned long long hc[8];
+  unsigned long long hc[9];
   long long E = 0;
   for (int attempt = 0;; ++attempt) {
     const long long cap = pair_capacity();
-    k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
-                                                       ctx->candA.as<int2>(), nullptr, cap);
-    LAUNCHED(ctx);
+    if (!a.slot) {
+      k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
+                                                         ctx->candA.as<int2>(), nullptr, cap);
+      LAUNCHED(ctx);
+    }
     k_rows_accept<<<ceil_div(nrows, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
                                                                           ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(),
                                                                           ctx->candB.as<int2>(), ctx->acc.as<int>(),
-                                                                          ctx->deg.as<int>(), cap);
+                                                                          ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(),
+                                                                          cap);
     LAUNCHED(ctx);
     CK(cudaEventRecord(ctx->ev[5], st));
     if (use_map) {
@@ -677,18 +695,28 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
       int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
       if (rc) return rc;
     }
-    k_compact<<<ceil_div(nrows * 32, 256), 256, 0, st>>>(ctx->cand_off.as<long long>(), ctx->deg.as<int>(),
-                                                        ctx->row_ptr.as<long long>(), ctx->acc.as<int>(), ctx->col_idx.as<int>(),
-                                                        (int)nrows, cap);
+    k_compact<<<ceil_div(nrows * COMPACT_LANES, 256), 256, 0, st>>>(a, ctx->cand_off.as<long long>(), ctx->deg.as<int>(),
+                                                                   ctx->row_ptr.as<long long>(), ctx->acc.as<int>(),
+                                                                   ctx->col_idx.as<int>(), ctx->counters.as<unsigned long long>(), cap);
     LAUNCHED(ctx);
     CK(cudaEventRecord(ctx->ev[4], st));
     CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(&C, ctx->cand_off.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hc, ctx->counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    C = (long long)hc[0];
+    if (a.slot) {
+      if (hc[8] == 0) break;
+      // some row holds more pairs than a slot: redo the phase with scanned offsets (the counts, the
+      // pyramid flags and the work list of the counting pass stay valid)
+      a.slot = 0;
+      int rc = scan_exclusive<long long>(ctx, ctx->cand_count.as<int>(), nrows, ctx->cand_off.as<long long>());
+      if (rc) return rc;
+      if (C > pair_capacity()) CK(reserve_pairs(C + C / 16 + 1024));
+      continue;
+    }
     if (C <= cap) break;
-    if (attempt > 0) return fail(ctx, SSPP_ERR_CUDA, "connect: pair buffers still too small after growing them");
-    CK(reserve_pairs(C));
+    if (attempt > 1) return fail(ctx, SSPP_ERR_CUDA, "connect: pair buffers still too small after growing them");
+    CK(reserve_pairs(C + C / 16 + 1024));
   }
   if (stats) {
     stats->rows = nrows;

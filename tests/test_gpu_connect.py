@@ -90,6 +90,28 @@ def test_random_nodes_with_map(eng, orc, pyramid):
     w.close()
 
 
+@pytest.mark.parametrize("slot", ["0", "4", "32", "64"])
+def test_pair_storage_modes_give_the_same_graph(eng, orc, slot, monkeypatch):
+    """Fixed slots per row (pairs written by the counting pass), scanned offsets (second neighbour pass),
+    and the switch from one to the other when a row overflows its slot (slot 4: almost every row does;
+    slot 32: the dense clump does) all build the same CSR."""
+    monkeypatch.setenv("SSPP_CONNECT_SLOT", slot)
+    w = make_map(eng, orc, 0.3, True, n_vox=96, seed=9)
+    rng = np.random.RandomState(8)
+    nodes = np.concatenate([scenes.uniform_nodes(2500, extent=22.0, seed=5), rng.uniform(-1.0, 1.0, (60, 3))])
+    st, cnt = assert_same_graph(eng, orc, w, nodes, 1.7)
+    assert st.in_radius_pairs > 10000
+    st2, _ = assert_same_graph(eng, orc, w, nodes, 1.7, rows=None)  # again on warm buffers
+    assert st2.edges == st.edges
+    eng.set_nodes(nodes)
+    full = eng.connect_fetch(eng.connect(radius=1.7, box=BOX))
+    a = eng.connect_fetch(eng.connect(radius=1.7, box=BOX, rows=(0, 1000)))
+    b = eng.connect_fetch(eng.connect(radius=1.7, box=BOX, rows=(1000, len(nodes))))
+    assert np.array_equal(np.concatenate([a[0][:-1], b[0] + a[0][-1]]), full[0])
+    assert np.array_equal(np.concatenate([a[1], b[1]]), full[1])
+    w.close()
+
+
 def test_duplicates_and_position_modes(eng, orc):
     """same-position nodes (other yaw) are connected without a test; mode 1 uses the 1e-12 tolerance"""
     w = make_map(eng, orc, 0.3, True, n_vox=64, seed=4)
