@@ -210,7 +210,7 @@ template <bool FILL>
 __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* __restrict__ cand_count,
                                                uint8_t* __restrict__ row_free, unsigned long long* counters,
                                                const long long* __restrict__ cand_off, int2* __restrict__ cand,
-                                               int* __restrict__ work_rows, long long pair_cap) {
+                                               int* __restrict__ work_rows, int* __restrict__ deg, long long pair_cap) {
   if (FILL && cand_off[a.nrows] > pair_cap) return;  // the pair buffers are too small: the host grows them and reruns
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned long long inr = 0, tested = 0, pyr = 0;
@@ -250,6 +250,8 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
       row_free[r] = fr;
       inr = cnt; tested = tst; pyr = fr;
       is_work = a.use_map && !fr && cnt > 0;
+      // slot mode: a row that needs no ray keeps all its pairs; k_compact orders them on the way out
+      if (slots && !is_work) deg[r] = cnt;
     }
   }
   if (!FILL) {
@@ -728,11 +730,14 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   }
 }
 
-// CSR compaction: eight lanes per row (rows hold a dozen or two edges), coalesced copy of the accepted prefix
+// CSR compaction: eight lanes per row (rows hold a dozen or two edges).  Work rows: coalesced copy of
+// the accepted prefix k_edges left in acc[].  Slot mode, rows that needed no ray: all pairs of the slot
+// are edges — rank-sorted by list index straight from the pair slot (the row never went through acc[]).
 constexpr int COMPACT_LANES = 8;
 __global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off, const int* __restrict__ deg,
-                          const long long* __restrict__ row_ptr, const int* __restrict__ acc, int* __restrict__ col,
-                          const unsigned long long* counters, long long pair_cap) {
+                          const long long* __restrict__ row_ptr, const int* __restrict__ acc, const int2* __restrict__ candA,
+                          const uint8_t* __restrict__ row_free, int* __restrict__ col, const unsigned long long* counters,
+                          long long pair_cap) {
   if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
   const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int r = (int)(gt / COMPACT_LANES);
@@ -740,6 +745,15 @@ __global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off,
   if (r >= a.nrows) return;
   const long long src = a.slot ? (long long)r * a.slot : cand_off[r], dst = row_ptr[r];
   const int d = deg[r];
+  if (a.slot && !(a.use_map && !row_free[r])) {
+    for (int e = sub; e < d; e += COMPACT_LANES) {
+      const int key = candA[src + e].y & 0x7fffffff;
+      int rank = 0;
+      for (int k = 0; k < d; ++k) rank += ((candA[src + k].y & 0x7fffffff) < key);
+      col[dst + rank] = key;
+    }
+    return;
+  }
   for (int e = sub; e < d; e += COMPACT_LANES) col[dst + e] = acc[src + e];
 }
 

@@ -638,7 +638,8 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   }
   k_count<false><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
                                                       ctx->counters.as<unsigned long long>(), nullptr,
-                                                      a.slot ? ctx->candA.as<int2>() : nullptr, ctx->work_rows.as<int>(), 0);
+                                                      a.slot ? ctx->candA.as<int2>() : nullptr, ctx->work_rows.as<int>(),
+                                                      ctx->deg.as<int>(), 0);
   LAUNCHED(ctx);
   if (!a.slot) {
     int rc = scan_exclusive<long long>(ctx, ctx->cand_count.as<int>(), nrows, ctx->cand_off.as<long long>());
@@ -666,15 +667,15 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
     const long long cap = pair_capacity();
     if (!a.slot) {
       k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
-                                                         ctx->candA.as<int2>(), nullptr, cap);
+                                                         ctx->candA.as<int2>(), nullptr, nullptr, cap);
       LAUNCHED(ctx);
-    }
-    k_rows_accept<<<ceil_div(nrows, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
+      k_rows_accept<<<ceil_div(nrows, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
                                                                           ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(),
                                                                           ctx->candB.as<int2>(), ctx->acc.as<int>(),
                                                                           ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(),
                                                                           cap);
-    LAUNCHED(ctx);
+      LAUNCHED(ctx);
+    }
     CK(cudaEventRecord(ctx->ev[5], st));
     if (use_map) {
       const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
@@ -697,6 +698,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
     }
     k_compact<<<ceil_div(nrows * COMPACT_LANES, 256), 256, 0, st>>>(a, ctx->cand_off.as<long long>(), ctx->deg.as<int>(),
                                                                    ctx->row_ptr.as<long long>(), ctx->acc.as<int>(),
+                                                                   ctx->candA.as<int2>(), ctx->row_free.as<uint8_t>(),
                                                                    ctx->col_idx.as<int>(), ctx->counters.as<unsigned long long>(), cap);
     LAUNCHED(ctx);
     CK(cudaEventRecord(ctx->ev[4], st));
