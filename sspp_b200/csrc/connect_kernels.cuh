@@ -310,6 +310,30 @@ __device__ __forceinline__ bool box_maybe_blocked(const DeviceMap& m, int lox, i
   return any != 0;
 }
 
+// The same question asked of the 4x4x4 pyramid first: a box whose coarse cells are all clear holds no
+// blocked voxel (a coarse bit is the OR of its 64 voxels), and that costs a few words instead of a few
+// dozen.  "true" = some coarse cell is set or the box leaves the window: the fine scan decides.
+__device__ __forceinline__ bool box_maybe_blocked_coarse(const DeviceMap& m, int lox, int hix, int loy, int hiy, int loz, int hiz) {
+  const int x0 = lox - m.kmin[0], x1 = hix - m.kmin[0];
+  const int y0 = loy - m.kmin[1], y1 = hiy - m.kmin[1];
+  const int z0 = loz - m.kmin[2], z1 = hiz - m.kmin[2];
+  if (x0 < 0 || y0 < 0 || z0 < 0 || x1 >= m.dims[0] || y1 >= m.dims[1] || z1 >= m.dims[2] || x0 > x1 || y0 > y1 || z0 > z1)
+    return true;
+  const int cx0 = x0 >> 2, cx1 = x1 >> 2, cy0 = y0 >> 2, cy1 = y1 >> 2, cz0 = z0 >> 2, cz1 = z1 >> 2;
+  uint32_t any = 0;
+  for (int w = cx0 >> 5; w <= (cx1 >> 5); ++w) {
+    const int b0 = max(cx0, w * 32) & 31, b1 = min(cx1, w * 32 + 31) & 31;
+    const uint32_t mask = (b1 == 31 ? 0xffffffffu : ((1u << (b1 + 1)) - 1u)) & ~((1u << b0) - 1u);
+    uint32_t acc = 0;
+    for (int z = cz0; z <= cz1; ++z) {
+      const uint32_t* col = m.cblocked + ((size_t)w * m.cdims[2] + z) * m.cdims[1];
+      for (int y = cy0; y <= cy1; ++y) acc |= __ldg(col + y);
+    }
+    any |= acc & mask;
+  }
+  return any != 0;
+}
+
 // the exact walk on the blocked plane, kept out of line: it is the rare path of line_status_fast and
 // inlining it would cost the whole edge kernel its occupancy
 __device__ __noinline__ int line_status_exact(const DeviceMap& m, float ox, float oy, float oz, float ex, float ey, float ez) {
@@ -604,7 +628,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
           pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
           pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
-          !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz))
+          (!box_maybe_blocked_coarse(m, lox, hix, loy, hiy, loz, hiz) || !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)))
         needs = false;
     }
     unsigned need = __ballot_sync(0xffffffffu, needs);
