@@ -159,6 +159,7 @@ __device__ bool row_reach_is_free(const DeviceMap& m, double px, double py, doub
   return true;
 }
 
+constexpr int SSPP_MAX_CHUNKS = 8;
 struct ConnectArgs {
   NodeGrid g;
   const int* cell_start;
@@ -177,6 +178,12 @@ struct ConnectArgs {
   // repeats the pass with scanned offsets (slot == 0: row r owns [cand_off[r], cand_off[r+1])).
   int slot;
   const int* cand_count;
+  // Row chunks (list-index ranges [chunk_lo[c], chunk_lo[c+1]) relative to `lo`): the edge test and the
+  // CSR compaction can run chunk by chunk so that a finished chunk travels to the host while the next
+  // one is computed.  nchunks == 1: one pass.  Chunk c keeps its work list at work_rows + chunk_lo[c]
+  // (a chunk never has more work rows than rows), its length in counters[16 + c], its ticket in [32 + c].
+  int nchunks;
+  int chunk_lo[SSPP_MAX_CHUNKS + 1];
 };
 
 // where row r keeps its pairs
@@ -199,7 +206,8 @@ __device__ __forceinline__ bool pairs_unusable(const ConnectArgs& a, const long 
 
 // counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows, [3] voxel steps (instrumented),
 //           [4] next work row (edge kernel's ticket), [5] pairs accepted by their key box,
-//           [6] pairs that ran the ray lattice, [7] number of work rows, [8] rows that overflowed their slot
+//           [6] pairs that ran the ray lattice, [8] rows that overflowed their slot,
+//           [16 + c] work rows of chunk c, [32 + c] next work row of chunk c (edge kernel's ticket)
 //
 // One thread per source row walks the 27 neighbouring cells (9 contiguous ranges of the cell-sorted
 // arrays).  FILL == false: count the in-radius pairs and test the row's reach against the pyramid;
@@ -215,6 +223,7 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned long long inr = 0, tested = 0, pyr = 0;
   bool is_work = false;
+  int chunk = 0;
   if (t < a.nrows) {
     int s = a.rows ? a.rows[t] : t;
     const NodeRec me = load_node(a.sn + s);
@@ -250,19 +259,22 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
       row_free[r] = fr;
       inr = cnt; tested = tst; pyr = fr;
       is_work = a.use_map && !fr && cnt > 0;
+      while (chunk + 1 < a.nchunks && r >= a.chunk_lo[chunk + 1]) ++chunk;
       // slot mode: a row that needs no ray keeps all its pairs; k_compact orders them on the way out
       if (slots && !is_work) deg[r] = cnt;
     }
   }
   if (!FILL) {
-    // rows that need the edge kernel, appended warp by warp (their order does not matter)
-    const unsigned wb = __ballot_sync(0xffffffffu, is_work);
-    if (wb) {
+    // rows that need the edge kernel, appended to their chunk's list, one atomic per warp and chunk
+    // (the order inside a list does not matter)
+    const unsigned grp = __match_any_sync(0xffffffffu, is_work ? chunk : -1);
+    if (is_work) {
       const int lane = threadIdx.x & 31;
+      const int leader = __ffs(grp) - 1;
       unsigned long long base = 0;
-      if (lane == 0) base = atomicAdd(counters + 7, (unsigned long long)__popc(wb));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (is_work) work_rows[base + __popc(wb & ((1u << lane) - 1u))] = t;
+      if (lane == leader) base = atomicAdd(counters + 16 + chunk, (unsigned long long)__popc(grp));
+      base = __shfl_sync(grp, base, leader);
+      work_rows[a.chunk_lo[chunk] + base + __popc(grp & ((1u << lane) - 1u))] = t;
     }
     for (int o = 16; o; o >>= 1) {
       inr += __shfl_xor_sync(0xffffffffu, inr, o);
@@ -728,7 +740,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
 k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
         const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
-        int* __restrict__ deg, unsigned long long* counters, long long pair_cap) {
+        int* __restrict__ deg, unsigned long long* counters, long long pair_cap, int chunk) {
   __shared__ EdgeSmem sm;
   if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
   RayLattice& lat = sm.lat;
@@ -744,10 +756,11 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const unsigned long long n_work = counters[7];
+  const unsigned long long n_work = counters[16 + chunk];
+  work_rows += a.chunk_lo[chunk];
   for (;;) {
     unsigned long long i = 0;
-    if (lane == 0) i = atomicAdd(counters + 4, 1ull);
+    if (lane == 0) i = atomicAdd(counters + 32 + chunk, 1ull);
     i = __shfl_sync(0xffffffffu, i, 0);
     if (i >= n_work) break;
     edge_row<COUNT>(a, m, sm, warp, lane, work_rows[i], cand_off, candA, candB, acc, deg, counters);
@@ -761,12 +774,12 @@ constexpr int COMPACT_LANES = 8;
 __global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off, const int* __restrict__ deg,
                           const long long* __restrict__ row_ptr, const int* __restrict__ acc, const int2* __restrict__ candA,
                           const uint8_t* __restrict__ row_free, int* __restrict__ col, const unsigned long long* counters,
-                          long long pair_cap) {
+                          long long pair_cap, int r_begin, int r_end) {
   if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
   const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int r = (int)(gt / COMPACT_LANES);
+  const int r = r_begin + (int)(gt / COMPACT_LANES);
   const int sub = (int)(gt % COMPACT_LANES);
-  if (r >= a.nrows) return;
+  if (r >= r_end) return;
   const long long src = a.slot ? (long long)r * a.slot : cand_off[r], dst = row_ptr[r];
   const int d = deg[r];
   if (a.slot && !(a.use_map && !row_free[r])) {
@@ -779,6 +792,20 @@ __global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off,
     return;
   }
   for (int e = sub; e < d; e += COMPACT_LANES) col[dst + e] = acc[src + e];
+}
+
+// Chunked CSR: the exclusive scan of one chunk's degrees (tmp, n + 1 entries) becomes the chunk's piece
+// of row_ptr by adding the edges of the chunks before it; base[c + 1] passes the running total on.
+__global__ void k_chunk_rebase(const long long* __restrict__ tmp, int n, long long* base, int c, int last,
+                               long long* __restrict__ row_ptr, int r0, int nrows) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const long long b = base[c];
+  if (i < n) row_ptr[r0 + i] = tmp[i] + b;
+  if (i == 0) {
+    const long long nb = b + tmp[n];
+    base[c + 1] = nb;
+    if (last) row_ptr[nrows] = nb;
+  }
 }
 
 // Multi-GPU CSR assembly: every rank holds the all-gathered, padded blocks of all ranks

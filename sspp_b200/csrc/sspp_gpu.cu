@@ -124,6 +124,11 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
                     &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
                     &ctx->dd_pend, &ctx->dd_dup, &ctx->dd_keep, &ctx->dd_misc};
   for (DevBuf* b : bufs) b->release();
+  ctx->chunk_tmp.release();
+  ctx->chunk_base.release();
+  for (int c = 0; c < 8; ++c) if (ctx->chunk_ev[c]) cudaEventDestroy(ctx->chunk_ev[c]);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
   for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
   for (void* q : ctx->peer_created) cudaFree(q);
   for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -439,7 +444,25 @@ int sspp_gpu_set_nodes_device(sspp_gpu_ctx* ctx, const double* xyz_device, int64
 }
 
 // ---- connect ---------------------------------------------------------------------------------
+namespace {
+// Host buffers of sspp_gpu_connect_nodes_host: the connection pass then runs the edge test and the
+// compaction in row chunks and sends every finished chunk home on a second stream while the next
+// one is computed.
+struct HostSink {
+  int64_t* row_ptr;
+  int32_t* col_idx;
+  int64_t col_capacity;
+  bool delivered;  // out: the CSR is already in the host buffers
+};
+int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect_stats* stats, HostSink* sink);
+}  // namespace
+
 int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect_stats* stats) {
+  return connect_impl(ctx, prm, stats, nullptr);
+}
+
+namespace {
+int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect_stats* stats, HostSink* sink) {
   if (!ctx || !prm) return fail(ctx, SSPP_ERR_INVALID, "connect: null argument");
   if (!std::isfinite(prm->radius)) return fail(ctx, SSPP_ERR_INVALID, "connect: radius must be finite");
   if (prm->position_mode != 0 && prm->position_mode != 1) return fail(ctx, SSPP_ERR_INVALID, "connect: position_mode must be 0 or 1");
@@ -611,8 +634,26 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   CK(ctx->cand_count.reserve((size_t)nrows * 4));
   CK(ctx->row_free.reserve((size_t)nrows));
   CK(ctx->cand_off.reserve((size_t)(nrows + 1) * 8));
-  CK(ctx->counters.reserve(16 * 8));
-  CK(cudaMemsetAsync(ctx->counters.p, 0, 16 * 8, st));
+  CK(ctx->counters.reserve(48 * 8));
+  CK(cudaMemsetAsync(ctx->counters.p, 0, 48 * 8, st));
+  // row chunks: only when the CSR goes straight to host buffers and the pass is large enough to pipeline
+  int K = 1;
+  if (sink && nrows >= (1 << 16)) {
+    K = 4;
+    if (const char* env = getenv("SSPP_HOST_CHUNKS")) K = std::min(std::max(atoi(env), 1), (int)SSPP_MAX_CHUNKS);
+  }
+  a.nchunks = K;
+  for (int c = 0; c <= SSPP_MAX_CHUNKS; ++c) a.chunk_lo[c] = (int)(c >= K ? nrows : (nrows * c) / K);
+  if (K > 1) {
+    if (!ctx->copy_stream) CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (int c = 0; c < K; ++c)
+      if (!ctx->chunk_ev[c]) CK(cudaEventCreateWithFlags(&ctx->chunk_ev[c], cudaEventDisableTiming));
+    if (!ctx->pinned) CK(cudaMallocHost((void**)&ctx->pinned, 32 * 8));
+    CK(ctx->chunk_tmp.reserve((size_t)(nrows / K + 2) * 8));
+    CK(ctx->chunk_base.reserve((SSPP_MAX_CHUNKS + 1) * 8));
+    CK(cudaMemsetAsync(ctx->chunk_base.p, 0, (SSPP_MAX_CHUNKS + 1) * 8, st));
+  }
+  if (sink) sink->delivered = false;
   CK(ctx->work_rows.reserve((size_t)nrows * 4));
   CK(ctx->deg.reserve((size_t)nrows * 4));
   a.cand_count = ctx->cand_count.as<int>();
@@ -677,34 +718,89 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
       LAUNCHED(ctx);
     }
     CK(cudaEventRecord(ctx->ev[5], st));
-    if (use_map) {
-      const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
-      if (count_steps)
-        k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
-                                                          ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
-                                                          ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
-                                                          ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap);
-      else
-        k_edges<false><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
-                                                           ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
-                                                           ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
-                                                           ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap);
-      LAUNCHED(ctx);
+    bool copies_off = false;    // chunked: this attempt's pairs turned out unusable, nothing is sent home
+    bool range_fail = false;    // chunked: the host column buffer is too small
+    volatile long long* pin = (volatile long long*)ctx->pinned;  // [0..K] edge prefix per chunk, [16..24] counters
+    // what chunk c needs once its kernels are done: its piece of the CSR goes to the host buffers
+    auto drain = [&](int c) -> int {
+      CK(cudaEventSynchronize(ctx->chunk_ev[c]));
+      if (c == 0) copies_off = a.slot ? (pin[16 + 8] != 0) : (pin[16 + 0] > cap);
+      if (copies_off || range_fail) return SSPP_OK;
+      const long long e0 = pin[c], e1 = pin[c + 1];
+      if (e1 > sink->col_capacity) { range_fail = true; return SSPP_OK; }
+      const int r0 = a.chunk_lo[c], r1 = a.chunk_lo[c + 1];
+      if (e1 > e0)
+        CK(cudaMemcpyAsync(sink->col_idx + e0, ctx->col_idx.as<int>() + e0, (size_t)(e1 - e0) * 4, cudaMemcpyDeviceToHost,
+                           ctx->copy_stream));
+      CK(cudaMemcpyAsync(sink->row_ptr + r0, ctx->row_ptr.as<long long>() + r0, (size_t)(r1 - r0) * 8, cudaMemcpyDeviceToHost,
+                         ctx->copy_stream));
+      return SSPP_OK;
+    };
+    for (int c = 0; c < K; ++c) {
+      if (use_map) {
+        const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
+        if (count_steps)
+          k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
+                                                            ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
+                                                            ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
+                                                            ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c);
+        else
+          k_edges<false><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
+                                                             ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
+                                                             ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
+                                                             ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c);
+        LAUNCHED(ctx);
+      }
+      if (c == K - 1) CK(cudaEventRecord(ctx->ev[3], st));
+      const int r0 = a.chunk_lo[c], r1 = a.chunk_lo[c + 1];
+      if (K == 1) {
+        int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
+        if (rc) return rc;
+      } else {
+        int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>() + r0, r1 - r0, ctx->chunk_tmp.as<long long>());
+        if (rc) return rc;
+        k_chunk_rebase<<<ceil_div(std::max(r1 - r0, 1), 256), 256, 0, st>>>(ctx->chunk_tmp.as<long long>(), r1 - r0,
+                                                                           ctx->chunk_base.as<long long>(), c, c == K - 1,
+                                                                           ctx->row_ptr.as<long long>(), r0, (int)nrows);
+        LAUNCHED(ctx);
+      }
+      if (r1 > r0) {
+        k_compact<<<ceil_div((int64_t)(r1 - r0) * COMPACT_LANES, 256), 256, 0, st>>>(
+            a, ctx->cand_off.as<long long>(), ctx->deg.as<int>(), ctx->row_ptr.as<long long>(), ctx->acc.as<int>(),
+            ctx->candA.as<int2>(), ctx->row_free.as<uint8_t>(), ctx->col_idx.as<int>(), ctx->counters.as<unsigned long long>(),
+            cap, r0, r1);
+        LAUNCHED(ctx);
+      }
+      if (K > 1) {
+        CK(cudaMemcpyAsync((void*)(pin + c + 1), ctx->chunk_base.as<long long>() + c + 1, 8, cudaMemcpyDeviceToHost, st));
+        if (c == 0) CK(cudaMemcpyAsync((void*)(pin + 16), ctx->counters.p, 9 * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(ctx->chunk_ev[c], st));
+        if (c >= 1) {
+          int rc = drain(c - 1);  // chunk c is queued: now wait for chunk c-1 and send it home
+          if (rc) return rc;
+        }
+      }
     }
-    CK(cudaEventRecord(ctx->ev[3], st));
-    {
-      int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
+    CK(cudaEventRecord(ctx->ev[4], st));
+    if (K > 1) {
+      pin[0] = 0;
+      int rc = drain(K - 1);
       if (rc) return rc;
     }
-    k_compact<<<ceil_div(nrows * COMPACT_LANES, 256), 256, 0, st>>>(a, ctx->cand_off.as<long long>(), ctx->deg.as<int>(),
-                                                                   ctx->row_ptr.as<long long>(), ctx->acc.as<int>(),
-                                                                   ctx->candA.as<int2>(), ctx->row_free.as<uint8_t>(),
-                                                                   ctx->col_idx.as<int>(), ctx->counters.as<unsigned long long>(), cap);
-    LAUNCHED(ctx);
-    CK(cudaEventRecord(ctx->ev[4], st));
     CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hc, ctx->counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    if (K > 1) {
+      CK(cudaStreamSynchronize(ctx->copy_stream));
+      if (range_fail) {
+        if (stats) stats->edges = E;
+        return fail(ctx, SSPP_ERR_RANGE, "connect_nodes_host: col_idx capacity too small");
+      }
+      if (!copies_off) {
+        sink->row_ptr[nrows] = E;
+        sink->delivered = true;
+      }
+    }
     C = (long long)hc[0];
     if (a.slot) {
       if (hc[8] == 0) break;
@@ -742,6 +838,7 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_con
   ctx->res_edges = E;
   return SSPP_OK;
 }
+}  // namespace
 
 int sspp_gpu_connect_fetch(sspp_gpu_ctx* ctx, int64_t* row_ptr, int32_t* col_idx) {
   if (!ctx) return SSPP_ERR_INVALID;
@@ -877,10 +974,14 @@ int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n,
                                 int64_t* row_ptr, int32_t* col_idx, int64_t col_capacity, sspp_connect_stats* stats) {
   sspp_connect_stats local;
   if (!stats) stats = &local;
+  if (!row_ptr || (col_capacity > 0 && !col_idx) || col_capacity < 0)
+    return fail(ctx, SSPP_ERR_INVALID, "connect_nodes_host: null argument");
   int rc = set_nodes_impl(ctx, xyz, n, cudaMemcpyHostToDevice);
   if (rc) return rc;
-  rc = sspp_gpu_connect(ctx, params, stats);
+  HostSink sink = {row_ptr, col_idx, col_capacity, false};
+  rc = connect_impl(ctx, params, stats, &sink);
   if (rc) return rc;
+  if (sink.delivered) return SSPP_OK;  // the chunks were sent home while the pass was still running
   if (stats->edges > col_capacity) return fail(ctx, SSPP_ERR_RANGE, "connect_nodes_host: col_idx capacity too small");
   return sspp_gpu_connect_fetch(ctx, row_ptr, col_idx);
 }

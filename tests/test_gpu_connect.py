@@ -207,6 +207,42 @@ def test_connect_nodes_host_and_determinism(eng, orc):
     w.close()
 
 
+@pytest.mark.parametrize("chunks,slot", [(None, None), ("3", None), ("8", None), ("4", "0"), ("4", "4")])
+def test_connect_nodes_host_chunked_delivery(eng, chunks, slot, monkeypatch):
+    """Above 65 536 rows the host-buffer call runs the edge test in row chunks and sends each finished
+    chunk home while the next one is computed: same CSR as connect + fetch, whatever the chunking and
+    the pair storage (slot 4: the slots overflow and the chunked phase is repeated with scanned offsets)."""
+    if chunks:
+        monkeypatch.setenv("SSPP_HOST_CHUNKS", chunks)
+    if slot:
+        monkeypatch.setenv("SSPP_CONNECT_SLOT", slot)
+    km, dm, occ, known = scenes.synthetic_map(n_vox=160, res=0.3, seed=12, n_boxes=30, n_spheres=20, region=40.0)
+    eng.map_create(0.3, km, dm, True)
+    eng.map_upload_dense(occ, known)
+    nodes = scenes.lattice_nodes(44, 1.0)  # 85 184 rows
+    eng.set_nodes(nodes)
+    st0 = eng.connect(radius=1.5, box=BOX)
+    rp0, col0 = eng.connect_fetch(st0)
+    assert st0.pyramid_rows > 0 and st0.lattice_pairs > 0 and st0.edges < st0.in_radius_pairs
+    rp = np.full(len(nodes) + 1, -7, dtype=np.int64)
+    col = np.full(st0.edges + 5, -7, dtype=np.int32)
+    for _ in range(2):
+        st = eng.connect_nodes_host(nodes, rp, col, radius=1.5, box=BOX)
+        assert st.edges == st0.edges and st.tested_pairs == st0.tested_pairs
+        assert np.array_equal(rp, rp0) and np.array_equal(col[: st.edges], col0)
+        assert (col[st.edges:] == -7).all()
+    # without a map every in-radius pair is an edge; the chunks still line up
+    st1 = eng.connect(radius=1.5, use_map=False)
+    rp1, col1 = eng.connect_fetch(st1)
+    colb = np.zeros(st1.edges, dtype=np.int32)
+    st2 = eng.connect_nodes_host(nodes, rp, colb, radius=1.5, use_map=False)
+    assert st2.edges == st1.edges and np.array_equal(rp, rp1) and np.array_equal(colb, col1)
+    # a column buffer that is too small is refused with the size needed
+    with pytest.raises(SsppError) as e:
+        eng.connect_nodes_host(nodes, rp, np.zeros(st0.edges // 2, dtype=np.int32), radius=1.5, box=BOX)
+    assert e.value.code == 4
+
+
 def test_full_size_properties(eng):
     """BASELINE config 4 shape (512^3 voxels, 10^6 lattice nodes): size-independent properties.
     (a) with an empty (all-free) map the graph equals the map-free graph; (b) the pyramid skip does
