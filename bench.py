@@ -260,8 +260,11 @@ def main():
     ap.add_argument("--no-visibility", action="store_true")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = one S4a region per GPU in one map / one search space (default); strong = S4a split over the GPUs")
-    ap.add_argument("--assembler", default="peer", choices=["peer", "nccl"],
-                    help="N>1: CSR assembly by the fused push kernel over NVLink peer memory (default) or by NCCL all-gather + packing")
+    ap.add_argument("--assembler", default="auto", choices=["auto", "streamed", "peer", "nccl"],
+                    help="N>1: CSR assembly overlapped with the edge test (chunks copied to all ranks over NVLink while the next "
+                         "chunk is computed), by one push kernel over NVLink peer memory after the pass, or by NCCL all-gather "
+                         "+ packing.  auto = streamed above 4 GPUs (where the exchange is long enough to pay for the chunking), "
+                         "peer otherwise")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
@@ -335,11 +338,18 @@ def main():
     steps_total = st_cnt.voxel_steps
 
     # ---- device-resident timing: `value`
-    assembler = None
+    assembler, streamed = None, None
     if distributed:
         from sspp_b200 import sharded
-        cls = sharded.PeerCsrAssembler if args.assembler == "peer" else sharded.GpuCsrAssembler
-        assembler = cls(eng, n, torch.device("cuda", local_rank))
+        dev = torch.device("cuda", local_rank)
+        if args.assembler == "auto":
+            args.assembler = "streamed" if world > 4 else "peer"
+        if args.assembler == "streamed":
+            streamed = sharded.StreamedPeerAssembler(eng, n, dev)
+            assembler = sharded.PeerCsrAssembler(eng, n, dev)  # the e2e leg (host buffers in) assembles after its pass
+        else:
+            cls = sharded.PeerCsrAssembler if args.assembler == "peer" else sharded.GpuCsrAssembler
+            assembler = cls(eng, n, dev)
 
     def assemble_csr(st):
         """N>1: every rank ends the step holding the whole graph's CSR (peer-memory push, or NCCL all-gather + packing)."""
@@ -350,6 +360,10 @@ def main():
 
     def step_resident():
         t0 = time.perf_counter()
+        if streamed is not None:  # connect and exchange in one call
+            st, _, _ = streamed.connect(radius=RADIUS, box=BOX)
+            split.append((time.perf_counter() - t0, 0.0))
+            return st
         st = eng.connect(radius=RADIUS, box=BOX, rows=rows)
         t1 = time.perf_counter()
         assemble_csr(st)

@@ -178,6 +178,23 @@ int sspp_gpu_peer_buffer_release(sspp_gpu_ctx* ctx, void* device_ptr);
 int sspp_gpu_connect_push_csr(sspp_gpu_ctx* ctx, int world, int rank, const int64_t* edge_counts_device,
                               const int64_t* row_base_device, int64_t* const* row_ptr_peers, int32_t* const* col_idx_peers,
                               int64_t col_capacity, int64_t* overflow_device);
+/* Multi-GPU, transfer overlapped with the edge test: sspp_gpu_connect, with the edge test and the
+ * compaction run in row chunks and every finished chunk copied over NVLink (copy engines, peer
+ * pointers from sspp_gpu_peer_buffer_open) into slot [rank] of EVERY rank's block buffers while the
+ * next chunk is computed.  Block buffers as sspp_gpu_assemble_csr_blocks reads them: row_ptr blocks of
+ * row_stride int64 per rank (relative to the block, entry [rows] = the block's edge count), column
+ * blocks of col_stride int32 per rank.  Returns when this rank's copies have landed; after a barrier
+ * over the ranks, sspp_gpu_assemble_csr_blocks on the local buffers yields the whole-graph CSR.
+ * SSPP_ERR_RANGE (nothing sent) when the block's edges exceed col_stride; stats->edges = size needed.
+ * No counterpart in the reference (one process). */
+typedef struct sspp_peer_blocks {
+  int32_t world, rank;
+  int64_t* const* row_ptr_blocks; /* host array of `world` device addresses: rank p's row_ptr block buffer */
+  int32_t* const* col_blocks;     /* likewise, column block buffer */
+  int64_t row_stride, col_stride;
+} sspp_peer_blocks;
+int sspp_gpu_connect_to_peers(sspp_gpu_ctx* ctx, const sspp_connect_params* params, const sspp_peer_blocks* peers,
+                              sspp_connect_stats* stats);
 /* Device addresses of the last CSR (valid until the next connect on this context). */
 int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_device, const int32_t** col_idx_device);
 

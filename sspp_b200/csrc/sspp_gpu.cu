@@ -452,7 +452,10 @@ struct HostSink {
   int64_t* row_ptr;
   int32_t* col_idx;
   int64_t col_capacity;
-  bool delivered;  // out: the CSR is already in the host buffers
+  bool delivered;  // out: the CSR is already in the host buffers / in the peers' block slots
+  // multi-GPU variant (sspp_gpu_connect_to_peers): the chunks go to slot [rank] of every rank's block
+  // buffers over NVLink (copy engines) instead of to the host; col_capacity = the slot size then
+  const sspp_peer_blocks* peers;
 };
 int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect_stats* stats, HostSink* sink);
 }  // namespace
@@ -642,14 +645,20 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     K = 4;
     if (const char* env = getenv("SSPP_HOST_CHUNKS")) K = std::min(std::max(atoi(env), 1), (int)SSPP_MAX_CHUNKS);
   }
+  const bool chunked = K > 1 || (sink && sink->peers);  // the peer variant always delivers through the chunk path
   a.nchunks = K;
-  for (int c = 0; c <= SSPP_MAX_CHUNKS; ++c) a.chunk_lo[c] = (int)(c >= K ? nrows : (nrows * c) / K);
-  if (K > 1) {
+  // chunk sizes fall off linearly (4:3:2:1 for four chunks): the copy of the last chunk is the only one
+  // nothing overlaps, so it is the smallest; the earlier copies have the later chunks' kernels to hide behind
+  for (int c = 0; c <= SSPP_MAX_CHUNKS; ++c) {
+    const int64_t done = (int64_t)c * (2 * K - c + 1) / 2, all = (int64_t)K * (K + 1) / 2;  // sum of (K - j), j < c
+    a.chunk_lo[c] = (int)(c >= K ? nrows : (nrows * done) / all);
+  }
+  if (chunked) {
     if (!ctx->copy_stream) CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     for (int c = 0; c < K; ++c)
       if (!ctx->chunk_ev[c]) CK(cudaEventCreateWithFlags(&ctx->chunk_ev[c], cudaEventDisableTiming));
     if (!ctx->pinned) CK(cudaMallocHost((void**)&ctx->pinned, 32 * 8));
-    CK(ctx->chunk_tmp.reserve((size_t)(nrows / K + 2) * 8));
+    CK(ctx->chunk_tmp.reserve((size_t)(a.chunk_lo[1] + 2) * 8));
     CK(ctx->chunk_base.reserve((SSPP_MAX_CHUNKS + 1) * 8));
     CK(cudaMemsetAsync(ctx->chunk_base.p, 0, (SSPP_MAX_CHUNKS + 1) * 8, st));
   }
@@ -729,6 +738,19 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       const long long e0 = pin[c], e1 = pin[c + 1];
       if (e1 > sink->col_capacity) { range_fail = true; return SSPP_OK; }
       const int r0 = a.chunk_lo[c], r1 = a.chunk_lo[c + 1];
+      if (sink->peers) {
+        const sspp_peer_blocks* pb = sink->peers;
+        const bool last = (c == K - 1);  // the last chunk also carries row_ptr[rows] = the block's edge count
+        for (int j = 0; j < pb->world; ++j) {
+          const int p = (pb->rank + 1 + j) % pb->world;  // start with the right-hand neighbour, finish with the own slot
+          if (e1 > e0)
+            CK(cudaMemcpyAsync(pb->col_blocks[p] + (size_t)pb->rank * pb->col_stride + e0, ctx->col_idx.as<int>() + e0,
+                               (size_t)(e1 - e0) * 4, cudaMemcpyDefault, ctx->copy_stream));
+          CK(cudaMemcpyAsync(pb->row_ptr_blocks[p] + (size_t)pb->rank * pb->row_stride + r0, ctx->row_ptr.as<long long>() + r0,
+                             (size_t)(r1 - r0 + (last ? 1 : 0)) * 8, cudaMemcpyDefault, ctx->copy_stream));
+        }
+        return SSPP_OK;
+      }
       if (e1 > e0)
         CK(cudaMemcpyAsync(sink->col_idx + e0, ctx->col_idx.as<int>() + e0, (size_t)(e1 - e0) * 4, cudaMemcpyDeviceToHost,
                            ctx->copy_stream));
@@ -736,6 +758,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
                          ctx->copy_stream));
       return SSPP_OK;
     };
+    if (chunked) pin[0] = 0;
     for (int c = 0; c < K; ++c) {
       if (use_map) {
         const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
@@ -753,7 +776,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       }
       if (c == K - 1) CK(cudaEventRecord(ctx->ev[3], st));
       const int r0 = a.chunk_lo[c], r1 = a.chunk_lo[c + 1];
-      if (K == 1) {
+      if (!chunked) {
         int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
         if (rc) return rc;
       } else {
@@ -771,7 +794,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
             cap, r0, r1);
         LAUNCHED(ctx);
       }
-      if (K > 1) {
+      if (chunked) {
         CK(cudaMemcpyAsync((void*)(pin + c + 1), ctx->chunk_base.as<long long>() + c + 1, 8, cudaMemcpyDeviceToHost, st));
         if (c == 0) CK(cudaMemcpyAsync((void*)(pin + 16), ctx->counters.p, 9 * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(ctx->chunk_ev[c], st));
@@ -782,7 +805,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       }
     }
     CK(cudaEventRecord(ctx->ev[4], st));
-    if (K > 1) {
+    if (chunked) {
       pin[0] = 0;
       int rc = drain(K - 1);
       if (rc) return rc;
@@ -790,14 +813,15 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hc, ctx->counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if (K > 1) {
+    if (chunked) {
       CK(cudaStreamSynchronize(ctx->copy_stream));
       if (range_fail) {
         if (stats) stats->edges = E;
-        return fail(ctx, SSPP_ERR_RANGE, "connect_nodes_host: col_idx capacity too small");
+        return fail(ctx, SSPP_ERR_RANGE, sink->peers ? "connect_to_peers: the block does not fit its column slot"
+                                                     : "connect_nodes_host: col_idx capacity too small");
       }
       if (!copies_off) {
-        sink->row_ptr[nrows] = E;
+        if (!sink->peers) sink->row_ptr[nrows] = E;
         sink->delivered = true;
       }
     }
@@ -978,12 +1002,44 @@ int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n,
     return fail(ctx, SSPP_ERR_INVALID, "connect_nodes_host: null argument");
   int rc = set_nodes_impl(ctx, xyz, n, cudaMemcpyHostToDevice);
   if (rc) return rc;
-  HostSink sink = {row_ptr, col_idx, col_capacity, false};
+  HostSink sink = {row_ptr, col_idx, col_capacity, false, nullptr};
   rc = connect_impl(ctx, params, stats, &sink);
   if (rc) return rc;
   if (sink.delivered) return SSPP_OK;  // the chunks were sent home while the pass was still running
   if (stats->edges > col_capacity) return fail(ctx, SSPP_ERR_RANGE, "connect_nodes_host: col_idx capacity too small");
   return sspp_gpu_connect_fetch(ctx, row_ptr, col_idx);
+}
+
+int sspp_gpu_connect_to_peers(sspp_gpu_ctx* ctx, const sspp_connect_params* params, const sspp_peer_blocks* peers,
+                              sspp_connect_stats* stats) {
+  sspp_connect_stats local;
+  if (!stats) stats = &local;
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!peers || !peers->row_ptr_blocks || !peers->col_blocks) return fail(ctx, SSPP_ERR_INVALID, "connect_to_peers: null argument");
+  if (peers->world < 1 || peers->world > SSPP_MAX_PEERS || peers->rank < 0 || peers->rank >= peers->world)
+    return fail(ctx, SSPP_ERR_INVALID, "connect_to_peers: world must be 1..SSPP_MAX_PEERS and rank inside it");
+  for (int p = 0; p < peers->world; ++p)
+    if (!peers->row_ptr_blocks[p] || !peers->col_blocks[p]) return fail(ctx, SSPP_ERR_INVALID, "connect_to_peers: null peer buffer");
+  int64_t lo = params ? params->row_begin : 0, hi = params ? params->row_end : 0;
+  if (lo == 0 && hi == 0) hi = ctx->n_nodes;
+  if (peers->row_stride < hi - lo + 1 || peers->col_stride < 0)
+    return fail(ctx, SSPP_ERR_INVALID, "connect_to_peers: row_stride must hold rows + 1 entries");
+  HostSink sink = {nullptr, nullptr, peers->col_stride, false, peers};
+  int rc = connect_impl(ctx, params, stats, &sink);
+  if (rc) return rc;
+  if (sink.delivered) return SSPP_OK;
+  // nothing went through the chunk path (an empty row range): deliver the block in one piece
+  if (stats->edges > peers->col_stride) return fail(ctx, SSPP_ERR_RANGE, "connect_to_peers: the block does not fit its column slot");
+  CK(cudaSetDevice(ctx->device));
+  for (int p = 0; p < peers->world; ++p) {
+    if (stats->edges)
+      CK(cudaMemcpyAsync(peers->col_blocks[p] + (size_t)peers->rank * peers->col_stride, ctx->col_idx.p, (size_t)stats->edges * 4,
+                         cudaMemcpyDefault, ctx->stream));
+    CK(cudaMemcpyAsync(peers->row_ptr_blocks[p] + (size_t)peers->rank * peers->row_stride, ctx->row_ptr.p,
+                       (size_t)(stats->rows + 1) * 8, cudaMemcpyDefault, ctx->stream));
+  }
+  CK(cudaStreamSynchronize(ctx->stream));
+  return SSPP_OK;
 }
 
 int sspp_gpu_connect_timings(sspp_gpu_ctx* ctx, float ms[8]) {

@@ -32,6 +32,11 @@ class ConnectStats(ctypes.Structure):
                 ("lattice_pairs", c_i64), ("voxel_steps", c_i64)]
 
 
+class PeerBlocks(ctypes.Structure):
+    _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("row_ptr_blocks", c_vp), ("col_blocks", c_vp),
+                ("row_stride", c_i64), ("col_stride", c_i64)]
+
+
 class Frustum(ctypes.Structure):
     _fields_ = [("hfov_deg", ctypes.c_double), ("vfov_deg", ctypes.c_double), ("near_dist", ctypes.c_double),
                 ("far_dist", ctypes.c_double)]
@@ -83,6 +88,8 @@ def load_library():
         "sspp_gpu_peer_buffer_open": (ctypes.c_int, [c_vp, c_vp, ctypes.POINTER(c_vp)]),
         "sspp_gpu_peer_buffer_release": (ctypes.c_int, [c_vp, c_vp]),
         "sspp_gpu_connect_push_csr": (ctypes.c_int, [c_vp, ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
+        "sspp_gpu_connect_to_peers": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), ctypes.POINTER(PeerBlocks),
+                                                     ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_result_device": (ctypes.c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
         "sspp_gpu_connect_nodes_host": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(ConnectParams), c_vp, c_vp,
                                                        c_i64, ctypes.POINTER(ConnectStats)]),
@@ -254,6 +261,22 @@ class Engine:
         b = (c_vp * world)(*[c_vp(int(x)) for x in col_peers])
         self._ck(self.L.sspp_gpu_connect_push_csr(self.h, world, rank, c_vp(edge_counts), c_vp(row_base), a, b,
                                                   int(col_capacity), c_vp(overflow)))
+
+    def connect_to_peers(self, world, rank, rp_blocks, col_blocks, row_stride, col_stride, **kw):
+        """connect + chunked delivery of this rank's block into slot [rank] of every rank's block buffers
+        (lists of `world` device addresses).  Returns the stats; raises SsppError (code 4) when the block does
+        not fit col_stride — `needed_edges` on the exception says how many it has."""
+        p = self.params(**kw)
+        s = ConnectStats()
+        a = (c_vp * world)(*[c_vp(int(x)) for x in rp_blocks])
+        b = (c_vp * world)(*[c_vp(int(x)) for x in col_blocks])
+        pb = PeerBlocks(world, rank, ctypes.cast(a, c_vp), ctypes.cast(b, c_vp), int(row_stride), int(col_stride))
+        rc = self.L.sspp_gpu_connect_to_peers(self.h, ctypes.byref(p), ctypes.byref(pb), ctypes.byref(s))
+        if rc:
+            e = SsppError(rc, self.L.sspp_gpu_last_error(self.h).decode())
+            e.needed_edges = int(s.edges)
+            raise e
+        return s
 
     def connect_result_device(self):
         a, b = c_vp(), c_vp()

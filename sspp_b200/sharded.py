@@ -11,6 +11,12 @@ their whole-graph CSR buffers once, and from then on every connect ends with ONE
 (sspp_gpu_connect_push_csr) that writes the rank's block, rebased, into all ranks' CSRs through
 NVLink peer memory; NCCL only carries the 8-byte edge counts and the closing barrier.
 GpuCsrAssembler (NCCL all-gather of padded slots + a packing kernel) stays as the comparison.
+
+StreamedPeerAssembler goes one step further and overlaps the exchange with the edge test:
+sspp_gpu_connect_to_peers runs the test in row chunks and copies every finished chunk into slot
+[rank] of all ranks' block buffers over NVLink (copy engines) while the next chunk is computed; what
+is left after the pass is one MAX all-reduce (barrier + "does every block fit") and the local packing
+kernel.
 """
 import torch
 import torch.distributed as dist
@@ -202,3 +208,100 @@ class PeerCsrAssembler:
         if self.rp_ptr is not None:
             self._release(self.rp_ptr, self.rp_peers)
             self.rp_ptr = None
+
+
+class StreamedPeerAssembler:
+    """connect + whole-graph CSR on every rank, the exchange overlapped with the edge test.
+
+    Every rank owns two sets of block buffers (row_ptr blocks of stride_r int64 per rank, column blocks
+    of stride_e int32 per rank) that its peers can address; the sets alternate from call to call, so a
+    rank may already be writing the next graph's chunks into its peers while they still pack the last
+    one (the barrier of the call in between orders the reuse of a set)."""
+
+    def __init__(self, eng, n_nodes, device):
+        self.eng = eng
+        self.world = dist.get_world_size()
+        self.rank = dist.get_rank()
+        self.device = device
+        self.n = n_nodes
+        base = [row_range(n_nodes, g, self.world)[0] for g in range(self.world)] + [n_nodes]
+        self.rows = (base[self.rank], base[self.rank + 1])
+        self.row_base = torch.tensor(base, dtype=torch.int64, device=device)
+        self.stride_r = max(base[g + 1] - base[g] for g in range(self.world)) + 1
+        self.ext_stream = torch.cuda.ExternalStream(eng.stream(), device=device)
+        self.out_rp = torch.empty(n_nodes + 1, dtype=torch.int64, device=device)
+        self.out_col = None
+        self.overflow = torch.zeros(1, dtype=torch.int64, device=device)
+        self.need = torch.zeros(1, dtype=torch.int64, device=device)
+        self.stride_e = 0
+        self.sets = []  # [(rp_ptr, rp_peers, col_ptr, col_peers)] x 2
+        self.turn = 0
+
+    def _exchange(self, nbytes):
+        ptr, handle = self.eng.peer_buffer_create(nbytes)
+        mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(self.device)
+        allh = torch.empty(self.world * 64, dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(allh, mine)
+        raw = allh.cpu().numpy().tobytes()
+        peers = [ptr if g == self.rank else self.eng.peer_buffer_open(raw[g * 64:(g + 1) * 64]) for g in range(self.world)]
+        return ptr, peers
+
+    def _release_sets(self):
+        torch.cuda.synchronize()
+        for rp_ptr, rp_peers, col_ptr, col_peers in self.sets:
+            for g in range(self.world):
+                if g != self.rank:
+                    self.eng.peer_buffer_release(rp_peers[g])
+                    self.eng.peer_buffer_release(col_peers[g])
+        dist.barrier()  # every importer has closed its mappings before the owners free the memory
+        for rp_ptr, rp_peers, col_ptr, col_peers in self.sets:
+            self.eng.peer_buffer_release(rp_ptr)
+            self.eng.peer_buffer_release(col_ptr)
+        self.sets = []
+
+    def _size(self, edges_max):
+        self._release_sets()
+        self.stride_e = ((int(edges_max * 1.1) + 1024 + 3) // 4) * 4
+        for _ in range(2):
+            rp_ptr, rp_peers = self._exchange(self.world * self.stride_r * 8)
+            col_ptr, col_peers = self._exchange(self.world * self.stride_e * 4)
+            self.sets.append((rp_ptr, rp_peers, col_ptr, col_peers))
+        self.out_col = torch.empty(self.world * self.stride_e, dtype=torch.int32, device=self.device)
+        dist.barrier()
+
+    def connect(self, **kw):
+        """This rank's rows of sspp_gpu_connect + the exchange.  Returns (stats, row_ptr, col_idx): the
+        stats of this rank's block and device tensors of the whole graph."""
+        from .engine import SsppError
+        if self.stride_e == 0:  # first call: learn the block sizes from a plain pass
+            st = self.eng.connect(rows=self.rows, **kw)
+            self.need.fill_(int(st.edges))
+            dist.all_reduce(self.need, op=dist.ReduceOp.MAX)
+            self._size(int(self.need.item()))
+        for attempt in range(3):
+            rp_ptr, rp_peers, col_ptr, col_peers = self.sets[self.turn % 2]
+            self.turn += 1
+            try:
+                st = self.eng.connect_to_peers(self.world, self.rank, rp_peers, col_peers, self.stride_r, self.stride_e,
+                                               rows=self.rows, **kw)
+                edges = int(st.edges)
+            except SsppError as e:
+                if e.code != 4:
+                    raise
+                st, edges = None, e.needed_edges
+            # barrier: every rank's copies have landed (connect_to_peers returns after its own have);
+            # the same message tells all ranks whether some block did not fit its slot
+            self.need.fill_(edges)
+            dist.all_reduce(self.need, op=dist.ReduceOp.MAX)
+            need = int(self.need.item())
+            if need > self.stride_e:
+                self._size(need)
+                continue
+            self.eng.assemble_csr_blocks(rp_ptr, col_ptr, self.world, self.stride_r, self.stride_e, self.row_base.data_ptr(),
+                                         self.out_rp.data_ptr(), self.out_col.data_ptr(), self.overflow.data_ptr())
+            self.eng.synchronize()
+            return st, self.out_rp, self.out_col
+        raise RuntimeError("CSR assembly: block slots still too small after resizing")
+
+    def close(self):
+        self._release_sets()

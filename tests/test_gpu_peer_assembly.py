@@ -99,6 +99,62 @@ def test_push_argument_errors(eng):
     eng.peer_buffer_release(ptr)
 
 
+@pytest.mark.parametrize("lattice,world", [(12, 2), (12, 3), (56, 2)])
+def test_connect_to_peers_blocks_pack_to_one_gpu_csr(eng, lattice, world):
+    """sspp_gpu_connect_to_peers: every rank's block lands in slot [rank] of all ranks' block buffers
+    (chunk by chunk above 65 536 rows per rank: lattice 56 -> 87 808 rows each), and packing the blocks
+    gives the CSR of one connect over all rows."""
+    import torch
+    dev = torch.device("cuda", 0)
+    km, dm, occ, known = scenes.synthetic_map(n_vox=224, res=0.3, seed=12, n_boxes=60, n_spheres=40, region=56.0)
+    nodes = scenes.lattice_nodes(lattice, 1.0)
+    if world * len(nodes) > 200000:
+        nodes = np.concatenate([nodes, nodes + np.array([0.0, 0.0, 0.37])])  # two rows per position column, still one space
+    n = len(nodes)
+    eng.map_create(0.3, km, dm, True)
+    eng.map_upload_dense(occ, known)
+    eng.set_nodes(nodes)
+    st = eng.connect(radius=1.5, box=BOX)
+    rp_full, col_full = eng.connect_fetch(st)
+    bounds = [(n * g) // world for g in range(world + 1)]
+    stride_r = max(bounds[g + 1] - bounds[g] for g in range(world)) + 1
+    ranks = [Engine(0) for _ in range(world)]
+    try:
+        for e in ranks:
+            e.map_create(0.3, km, dm, True)
+            e.map_upload_dense(occ, known)
+            e.set_nodes(nodes)
+        stride_e = st.edges  # generous: any block fits
+        rp_blk = [torch.full((world * stride_r,), -1, dtype=torch.int64, device=dev) for _ in range(world)]
+        col_blk = [torch.full((world * stride_e,), -1, dtype=torch.int32, device=dev) for _ in range(world)]
+        torch.cuda.synchronize()
+        edges = []
+        for g, e in enumerate(ranks):
+            s = e.connect_to_peers(world, g, [t.data_ptr() for t in rp_blk], [t.data_ptr() for t in col_blk], stride_r, stride_e,
+                                   radius=1.5, box=BOX, rows=(bounds[g], bounds[g + 1]))
+            edges.append(s.edges)
+        assert sum(edges) == st.edges
+        row_base = torch.tensor(bounds, dtype=torch.int64, device=dev)
+        for k in range(world):
+            out_rp = torch.empty(n + 1, dtype=torch.int64, device=dev)
+            out_col = torch.empty(world * stride_e, dtype=torch.int32, device=dev)
+            over = torch.zeros(1, dtype=torch.int64, device=dev)
+            ranks[k].assemble_csr_blocks(rp_blk[k].data_ptr(), col_blk[k].data_ptr(), world, stride_r, stride_e, row_base.data_ptr(),
+                                         out_rp.data_ptr(), out_col.data_ptr(), over.data_ptr())
+            ranks[k].synchronize()
+            assert int(over.item()) == 0
+            assert np.array_equal(out_rp.cpu().numpy(), rp_full), "row_ptr on rank %d differs" % k
+            assert np.array_equal(out_col.cpu().numpy()[: st.edges], col_full), "col_idx on rank %d differs" % k
+        # a slot that is too small: nothing is sent, the error carries the size needed
+        with pytest.raises(SsppError) as ei:
+            ranks[0].connect_to_peers(world, 0, [t.data_ptr() for t in rp_blk], [t.data_ptr() for t in col_blk], stride_r,
+                                      edges[0] // 2, radius=1.5, box=BOX, rows=(bounds[0], bounds[1]))
+        assert ei.value.code == 4 and ei.value.needed_edges == edges[0]
+    finally:
+        for e in ranks:
+            e.close()
+
+
 def _ipc_rank(rank, world, port, q):
     import torch
     import torch.distributed as dist
@@ -126,6 +182,15 @@ def _ipc_rank(rank, world, port, q):
             ok = ok and np.array_equal(rp, rpf) and np.array_equal(col[: sf.edges], colf)
             dist.barrier()
         asm.close()
+        sasm = sharded.StreamedPeerAssembler(e, n, dev)
+        for radius in (1.0, 1.5, 1.0, 1.0):  # sizing pass, a graph that outgrows the slots, both buffer sets
+            st, rp, col = sasm.connect(radius=radius, box=BOX)
+            rp, col = rp.cpu().numpy(), col.cpu().numpy()
+            sf = e.connect(radius=radius, box=BOX)
+            rpf, colf = e.connect_fetch(sf)
+            ok = ok and np.array_equal(rp, rpf) and np.array_equal(col[: sf.edges], colf)
+            dist.barrier()
+        sasm.close()
         q.put((rank, bool(ok)))
     finally:
         e.close()
