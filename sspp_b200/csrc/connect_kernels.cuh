@@ -794,20 +794,6 @@ __global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off,
   for (int e = sub; e < d; e += COMPACT_LANES) col[dst + e] = acc[src + e];
 }
 
-// Chunked CSR: the exclusive scan of one chunk's degrees (tmp, n + 1 entries) becomes the chunk's piece
-// of row_ptr by adding the edges of the chunks before it; base[c + 1] passes the running total on.
-__global__ void k_chunk_rebase(const long long* __restrict__ tmp, int n, long long* base, int c, int last,
-                               long long* __restrict__ row_ptr, int r0, int nrows) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  const long long b = base[c];
-  if (i < n) row_ptr[r0 + i] = tmp[i] + b;
-  if (i == 0) {
-    const long long nb = b + tmp[n];
-    base[c + 1] = nb;
-    if (last) row_ptr[nrows] = nb;
-  }
-}
-
 // Multi-GPU CSR assembly: every rank holds the all-gathered, padded blocks of all ranks
 // (row_ptr blocks of stride_r entries whose entry [rows_g] is the block's edge count; column blocks
 // of stride_e entries).  One CTA per block rebases and copies: the whole-graph CSR without a host

@@ -73,7 +73,7 @@ struct sspp_gpu_ctx {
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t chunk_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   long long* pinned = nullptr;  // small pinned host block the chunk totals land in
-  DevBuf chunk_tmp, chunk_base;
+  DevBuf chunk_base;
 
   // peer-addressable buffers (multi-GPU CSR assembly): created here / opened from a peer's IPC handle
   std::vector<void*> peer_created, peer_opened;

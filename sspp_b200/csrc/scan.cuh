@@ -54,15 +54,17 @@ __global__ void k_scan_sums(long long* sums, int nb) {
   }
 }
 
+// base (may be NULL): a device scalar added to every output; total_out (may be NULL) receives out[n]
 template <class T>
-__global__ void k_scan_apply(const int* __restrict__ in, int64_t n, const long long* __restrict__ sums, T* __restrict__ out) {
+__global__ void k_scan_apply(const int* __restrict__ in, int64_t n, const long long* __restrict__ sums, T* __restrict__ out,
+                             const long long* __restrict__ base, long long* total_out) {
   // items are laid out thread-major inside the tile so the local scan is a plain running sum
   __shared__ long long sh[SCAN_THREADS];
-  int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+  int64_t first = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
   int v[SCAN_ITEMS];
   long long t = 0;
   for (int k = 0; k < SCAN_ITEMS; ++k) {
-    int64_t i = base + k;
+    int64_t i = first + k;
     v[k] = (i < n) ? in[i] : 0;
     t += v[k];
   }
@@ -74,23 +76,32 @@ __global__ void k_scan_apply(const int* __restrict__ in, int64_t n, const long l
     sh[threadIdx.x] += u;
     __syncthreads();
   }
-  long long run = sums[blockIdx.x] + sh[threadIdx.x] - t;
+  long long run = sums[blockIdx.x] + sh[threadIdx.x] - t + (base ? *base : 0);
   for (int k = 0; k < SCAN_ITEMS; ++k) {
-    int64_t i = base + k;
+    int64_t i = first + k;
     if (i < n) out[i] = (T)run;
     run += v[k];
-    if (i == n - 1) out[n] = (T)run;
+    if (i == n - 1) {
+      out[n] = (T)run;
+      if (total_out) *total_out = run;
+    }
   }
 }
 
 template <class T>
-__global__ void k_scan_empty(T* out) { out[0] = 0; }
+__global__ void k_scan_empty(T* out, const long long* base, long long* total_out) {
+  const long long b = base ? *base : 0;
+  out[0] = (T)b;
+  if (total_out) *total_out = b;
+}
 
-// out must hold n+1 entries; out[n] = total
+// out must hold n+1 entries; out[n] = total.  With `base` (a device scalar) the scan starts there
+// instead of at 0, and total_out receives out[n]: a chain of scans over consecutive pieces of one array.
 template <class T>
-int scan_exclusive(sspp_gpu_ctx* ctx, const int* in, int64_t n, T* out) {
+int scan_exclusive(sspp_gpu_ctx* ctx, const int* in, int64_t n, T* out, const long long* base = nullptr,
+                   long long* total_out = nullptr) {
   if (n == 0) {
-    k_scan_empty<T><<<1, 1, 0, ctx->stream>>>(out);
+    k_scan_empty<T><<<1, 1, 0, ctx->stream>>>(out, base, total_out);
     LAUNCHED(ctx);
     return SSPP_OK;
   }
@@ -101,7 +112,7 @@ int scan_exclusive(sspp_gpu_ctx* ctx, const int* in, int64_t n, T* out) {
   LAUNCHED(ctx);
   k_scan_sums<<<1, 1024, 0, ctx->stream>>>(sums, nb);
   LAUNCHED(ctx);
-  k_scan_apply<T><<<nb, SCAN_THREADS, 0, ctx->stream>>>(in, n, sums, out);
+  k_scan_apply<T><<<nb, SCAN_THREADS, 0, ctx->stream>>>(in, n, sums, out, base, total_out);
   LAUNCHED(ctx);
   return SSPP_OK;
 }

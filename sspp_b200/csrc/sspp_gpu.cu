@@ -124,7 +124,6 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
                     &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
                     &ctx->dd_pend, &ctx->dd_dup, &ctx->dd_keep, &ctx->dd_misc};
   for (DevBuf* b : bufs) b->release();
-  ctx->chunk_tmp.release();
   ctx->chunk_base.release();
   for (int c = 0; c < 8; ++c) if (ctx->chunk_ev[c]) cudaEventDestroy(ctx->chunk_ev[c]);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -658,7 +657,6 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     for (int c = 0; c < K; ++c)
       if (!ctx->chunk_ev[c]) CK(cudaEventCreateWithFlags(&ctx->chunk_ev[c], cudaEventDisableTiming));
     if (!ctx->pinned) CK(cudaMallocHost((void**)&ctx->pinned, 32 * 8));
-    CK(ctx->chunk_tmp.reserve((size_t)(a.chunk_lo[1] + 2) * 8));
     CK(ctx->chunk_base.reserve((SSPP_MAX_CHUNKS + 1) * 8));
     CK(cudaMemsetAsync(ctx->chunk_base.p, 0, (SSPP_MAX_CHUNKS + 1) * 8, st));
   }
@@ -780,12 +778,10 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
         int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
         if (rc) return rc;
       } else {
-        int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>() + r0, r1 - r0, ctx->chunk_tmp.as<long long>());
+        // the chunk's piece of row_ptr, continued from the chunks before it (chunk_base[c] -> [c + 1])
+        int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>() + r0, r1 - r0, ctx->row_ptr.as<long long>() + r0,
+                                           ctx->chunk_base.as<long long>() + c, ctx->chunk_base.as<long long>() + c + 1);
         if (rc) return rc;
-        k_chunk_rebase<<<ceil_div(std::max(r1 - r0, 1), 256), 256, 0, st>>>(ctx->chunk_tmp.as<long long>(), r1 - r0,
-                                                                           ctx->chunk_base.as<long long>(), c, c == K - 1,
-                                                                           ctx->row_ptr.as<long long>(), r0, (int)nrows);
-        LAUNCHED(ctx);
       }
       if (r1 > r0) {
         k_compact<<<ceil_div((int64_t)(r1 - r0) * COMPACT_LANES, 256), 256, 0, st>>>(
