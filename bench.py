@@ -260,11 +260,10 @@ def main():
     ap.add_argument("--no-visibility", action="store_true")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = one S4a region per GPU in one map / one search space (default); strong = S4a split over the GPUs")
-    ap.add_argument("--assembler", default="auto", choices=["auto", "streamed", "peer", "nccl"],
+    ap.add_argument("--assembler", default="peer", choices=["streamed", "peer", "nccl"],
                     help="N>1: CSR assembly overlapped with the edge test (chunks copied to all ranks over NVLink while the next "
-                         "chunk is computed), by one push kernel over NVLink peer memory after the pass, or by NCCL all-gather "
-                         "+ packing.  auto = streamed above 4 GPUs (where the exchange is long enough to pay for the chunking), "
-                         "peer otherwise")
+                         "chunk is computed), by one push kernel over NVLink peer memory after the pass (default: the fastest "
+                         "at 2, 4 and 8 GPUs), or by NCCL all-gather + packing")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)
@@ -342,8 +341,6 @@ def main():
     if distributed:
         from sspp_b200 import sharded
         dev = torch.device("cuda", local_rank)
-        if args.assembler == "auto":
-            args.assembler = "streamed" if world > 4 else "peer"
         if args.assembler == "streamed":
             streamed = sharded.StreamedPeerAssembler(eng, n, dev)
             assembler = sharded.PeerCsrAssembler(eng, n, dev)  # the e2e leg (host buffers in) assembles after its pass
@@ -438,10 +435,23 @@ def main():
     col_host = torch.empty(int(st.in_radius_pairs) + 64, dtype=torch.int32).pin_memory()
     rp_np, col_np, nodes_np = rp_host.numpy(), col_host.numpy(), pin_nodes.numpy()
 
+    if distributed:
+        assert n % world == 0
+        nodes_dev = torch.empty((n, 3), dtype=torch.float64, device="cuda")
+
     def step_e2e():
-        s = eng.connect_nodes_host(nodes_np, rp_np[: (hi - lo) + 1] if distributed else rp_np, col_np, radius=RADIUS, box=BOX,
-                                   rows=rows)
-        assemble_csr(s)
+        if not distributed:
+            return eng.connect_nodes_host(nodes_np, rp_np, col_np, radius=RADIUS, box=BOX)
+        # N > 1: every rank uploads ITS slice of the host node array over its own PCIe link, the slices are
+        # all-gathered over NVLink into the replicated node set, the rank connects its rows while its block
+        # travels to pinned host memory chunk by chunk, and the whole CSR is assembled on every GPU
+        mine = nodes_dev[lo:hi]
+        mine.copy_(pin_nodes[lo:hi], non_blocking=True)
+        dist.all_gather_into_tensor(nodes_dev, mine)
+        ext_stream.wait_event(torch.cuda.current_stream().record_event())
+        eng.set_nodes_device(nodes_dev.data_ptr(), n)
+        s = eng.connect_to_host(rp_np[: (hi - lo) + 1], col_np, radius=RADIUS, box=BOX, rows=rows)  # block home, chunk by chunk
+        assembler.assemble(s)
         return s
 
     for _ in range(2):
@@ -461,8 +471,8 @@ def main():
     if distributed:
         dist.all_reduce(e2e_tot, op=dist.ReduceOp.MAX)
     e2e_value = tested_all * K / float(e2e_tot[0])
-    h2d = n * 24
-    d2h = ((hi - lo) + 1) * 8 + int(s2.edges) * 4
+    h2d = n * 24  # whole job: every node crosses PCIe once (N > 1: one slice per rank)
+    d2h = n * 8 + 8 * n_gpus + int(edges_all) * 4  # whole job: every rank reads its own block
     clk = clocks.stop() if rank == 0 else None
 
     # ---- correctness guard on the timed configuration: the pyramid skip must not change the CSR

@@ -127,6 +127,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
   ctx->chunk_base.release();
   for (int c = 0; c < 8; ++c) if (ctx->chunk_ev[c]) cudaEventDestroy(ctx->chunk_ev[c]);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  for (int p = 0; p < SSPP_MAX_PEERS; ++p) if (ctx->peer_stream[p]) cudaStreamDestroy(ctx->peer_stream[p]);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
   for (void* q : ctx->peer_created) cudaFree(q);
@@ -740,12 +741,15 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
         const sspp_peer_blocks* pb = sink->peers;
         const bool last = (c == K - 1);  // the last chunk also carries row_ptr[rows] = the block's edge count
         for (int j = 0; j < pb->world; ++j) {
-          const int p = (pb->rank + 1 + j) % pb->world;  // start with the right-hand neighbour, finish with the own slot
+          // one stream per destination, so that the copies to different GPUs run on different copy engines
+          // side by side; start with the right-hand neighbour, finish with the own slot
+          const int p = (pb->rank + 1 + j) % pb->world;
+          if (!ctx->peer_stream[p]) CK(cudaStreamCreateWithFlags(&ctx->peer_stream[p], cudaStreamNonBlocking));
           if (e1 > e0)
             CK(cudaMemcpyAsync(pb->col_blocks[p] + (size_t)pb->rank * pb->col_stride + e0, ctx->col_idx.as<int>() + e0,
-                               (size_t)(e1 - e0) * 4, cudaMemcpyDefault, ctx->copy_stream));
+                               (size_t)(e1 - e0) * 4, cudaMemcpyDefault, ctx->peer_stream[p]));
           CK(cudaMemcpyAsync(pb->row_ptr_blocks[p] + (size_t)pb->rank * pb->row_stride + r0, ctx->row_ptr.as<long long>() + r0,
-                             (size_t)(r1 - r0 + (last ? 1 : 0)) * 8, cudaMemcpyDefault, ctx->copy_stream));
+                             (size_t)(r1 - r0 + (last ? 1 : 0)) * 8, cudaMemcpyDefault, ctx->peer_stream[p]));
         }
         return SSPP_OK;
       }
@@ -811,6 +815,9 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     CK(cudaStreamSynchronize(st));
     if (chunked) {
       CK(cudaStreamSynchronize(ctx->copy_stream));
+      if (sink->peers)
+        for (int p = 0; p < sink->peers->world; ++p)
+          if (ctx->peer_stream[p]) CK(cudaStreamSynchronize(ctx->peer_stream[p]));
       if (range_fail) {
         if (stats) stats->edges = E;
         return fail(ctx, SSPP_ERR_RANGE, sink->peers ? "connect_to_peers: the block does not fit its column slot"
@@ -990,20 +997,29 @@ int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_de
   return SSPP_OK;
 }
 
-int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n, const sspp_connect_params* params,
-                                int64_t* row_ptr, int32_t* col_idx, int64_t col_capacity, sspp_connect_stats* stats) {
+int sspp_gpu_connect_to_host(sspp_gpu_ctx* ctx, const sspp_connect_params* params, int64_t* row_ptr, int32_t* col_idx,
+                             int64_t col_capacity, sspp_connect_stats* stats) {
   sspp_connect_stats local;
   if (!stats) stats = &local;
+  if (!ctx) return SSPP_ERR_INVALID;
   if (!row_ptr || (col_capacity > 0 && !col_idx) || col_capacity < 0)
-    return fail(ctx, SSPP_ERR_INVALID, "connect_nodes_host: null argument");
-  int rc = set_nodes_impl(ctx, xyz, n, cudaMemcpyHostToDevice);
-  if (rc) return rc;
+    return fail(ctx, SSPP_ERR_INVALID, "connect_to_host: null argument");
   HostSink sink = {row_ptr, col_idx, col_capacity, false, nullptr};
-  rc = connect_impl(ctx, params, stats, &sink);
+  int rc = connect_impl(ctx, params, stats, &sink);
   if (rc) return rc;
   if (sink.delivered) return SSPP_OK;  // the chunks were sent home while the pass was still running
   if (stats->edges > col_capacity) return fail(ctx, SSPP_ERR_RANGE, "connect_nodes_host: col_idx capacity too small");
   return sspp_gpu_connect_fetch(ctx, row_ptr, col_idx);
+}
+
+int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n, const sspp_connect_params* params,
+                                int64_t* row_ptr, int32_t* col_idx, int64_t col_capacity, sspp_connect_stats* stats) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!row_ptr || (col_capacity > 0 && !col_idx) || col_capacity < 0)
+    return fail(ctx, SSPP_ERR_INVALID, "connect_nodes_host: null argument");
+  int rc = set_nodes_impl(ctx, xyz, n, cudaMemcpyHostToDevice);
+  if (rc) return rc;
+  return sspp_gpu_connect_to_host(ctx, params, row_ptr, col_idx, col_capacity, stats);
 }
 
 int sspp_gpu_connect_to_peers(sspp_gpu_ctx* ctx, const sspp_connect_params* params, const sspp_peer_blocks* peers,

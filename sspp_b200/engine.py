@@ -93,6 +93,8 @@ def load_library():
         "sspp_gpu_connect_result_device": (ctypes.c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
         "sspp_gpu_connect_nodes_host": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(ConnectParams), c_vp, c_vp,
                                                        c_i64, ctypes.POINTER(ConnectStats)]),
+        "sspp_gpu_connect_to_host": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), c_vp, c_vp, c_i64,
+                                                    ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_timings": (ctypes.c_int, [c_vp, c_vp]),
         "sspp_gpu_dedup_poses": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.c_double, c_vp, c_vp, ctypes.POINTER(c_i64)]),
         "sspp_gpu_check_segments": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp]),
@@ -225,11 +227,13 @@ class Engine:
         self._ck(self.L.sspp_gpu_connect(self.h, ctypes.byref(p), ctypes.byref(s)))
         return s
 
-    def connect_fetch(self, stats):
-        rp = np.zeros(stats.rows + 1, dtype=np.int64)
-        col = np.zeros(max(stats.edges, 1), dtype=np.int32)
+    def connect_fetch(self, stats, rp_out=None, col_out=None):
+        """Last CSR to host; rp_out / col_out: caller's (e.g. pinned) arrays of at least rows+1 / edges entries."""
+        rp = np.zeros(stats.rows + 1, dtype=np.int64) if rp_out is None else rp_out
+        col = np.zeros(max(stats.edges, 1), dtype=np.int32) if col_out is None else col_out
+        assert len(rp) >= stats.rows + 1 and len(col) >= stats.edges
         self._ck(self.L.sspp_gpu_connect_fetch(self.h, _p(rp), _p(col)))
-        return rp, col[:stats.edges]
+        return rp[:stats.rows + 1], col[:stats.edges]
 
     def connect_fetch_device(self, row_ptr_dev, col_idx_dev):
         """D2D copy of the last CSR into caller-owned device buffers (raw addresses)."""
@@ -289,6 +293,13 @@ class Engine:
         s = ConnectStats()
         self._ck(self.L.sspp_gpu_connect_nodes_host(self.h, _p(xyz), len(xyz), ctypes.byref(p), _p(row_ptr), _p(col_idx),
                                                    len(col_idx), ctypes.byref(s)))
+        return s
+
+    def connect_to_host(self, row_ptr, col_idx, **kw):
+        """connect on the nodes already set, CSR into preallocated host arrays; returns stats."""
+        p = self.params(**kw)
+        s = ConnectStats()
+        self._ck(self.L.sspp_gpu_connect_to_host(self.h, ctypes.byref(p), _p(row_ptr), _p(col_idx), len(col_idx), ctypes.byref(s)))
         return s
 
     def connect_timings(self):
