@@ -200,33 +200,46 @@ SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float di
   const double maxrange_sq = d_mul(max_range, max_range);
   // squared distance of the current voxel centre from the origin, one term per axis: upstream rebuilds
   // all three every step; only the axis that moved changes, so the other two terms are kept
-  // (each term is the float product (c - o)^2 widened to double; the sum keeps upstream's order)
-  double qx = 0.0, qy = 0.0, qz = 0.0;
+  // (each term is the float product (c - o)^2 widened to double; the sum keeps upstream's order).
+  // The test cannot fire during the first steps: the origin lies in the start voxel (its centre is
+  // within res/2 per axis) and every step moves the centre by res along one axis, so after n steps
+  // the centre is within (n + 1.5) res of the origin; while that stays half a voxel below max_range
+  // the bookkeeping is skipped, and the three terms are rebuilt from the current keys when it starts
+  // (each term depends on the current key of its axis only, so nothing is lost).
+  int safe = 0;  // steps during which the range test is known not to fire
   if (max_range_set) {
-    float ddx = f_sub(d2f(key_to_coord(ks, kx)), ox), ddy = f_sub(d2f(key_to_coord(ks, ky)), oy),
-          ddz = f_sub(d2f(key_to_coord(ks, kz)), oz);
-    qx = (double)f_mul(ddx, ddx);
-    qy = (double)f_mul(ddy, ddy);
-    qz = (double)f_mul(ddz, ddz);
+    const double v = floor(d_sub(d_div(max_range, ks.res), 2.0));
+    safe = v > 0.0 ? (v < 262144.0 ? (int)v : 262144) : 0;
   }
+  bool ranged = false;  // qx, qy, qz hold the terms of the current voxel
+  double qx = 0.0, qy = 0.0, qz = 0.0;
   for (int it = 0; it < 262144; ++it) {
+    const bool check = max_range_set && it >= safe;
+    if (check && !ranged) {
+      float ddx = f_sub(d2f(key_to_coord(ks, kx)), ox), ddy = f_sub(d2f(key_to_coord(ks, ky)), oy),
+            ddz = f_sub(d2f(key_to_coord(ks, kz)), oz);
+      qx = (double)f_mul(ddx, ddx);
+      qy = (double)f_mul(ddy, ddy);
+      qz = (double)f_mul(ddz, ddz);
+      ranged = true;
+    }
     int dim;
     if (tx < ty) dim = (tx < tz) ? 0 : 2;
     else dim = (ty < tz) ? 1 : 2;
     if (dim == 0) {
       if ((sx < 0 && kx == 0) || (sx > 0 && kx == 65535)) return false;
       kx += sx; tx = d_add(tx, dtx);
-      if (max_range_set) { float dd = f_sub(d2f(key_to_coord(ks, kx)), ox); qx = (double)f_mul(dd, dd); }
+      if (check) { float dd = f_sub(d2f(key_to_coord(ks, kx)), ox); qx = (double)f_mul(dd, dd); }
     } else if (dim == 1) {
       if ((sy < 0 && ky == 0) || (sy > 0 && ky == 65535)) return false;
       ky += sy; ty = d_add(ty, dty);
-      if (max_range_set) { float dd = f_sub(d2f(key_to_coord(ks, ky)), oy); qy = (double)f_mul(dd, dd); }
+      if (check) { float dd = f_sub(d2f(key_to_coord(ks, ky)), oy); qy = (double)f_mul(dd, dd); }
     } else {
       if ((sz < 0 && kz == 0) || (sz > 0 && kz == 65535)) return false;
       kz += sz; tz = d_add(tz, dtz);
-      if (max_range_set) { float dd = f_sub(d2f(key_to_coord(ks, kz)), oz); qz = (double)f_mul(dd, dd); }
+      if (check) { float dd = f_sub(d2f(key_to_coord(ks, kz)), oz); qz = (double)f_mul(dd, dd); }
     }
-    if (max_range_set) {
+    if (check) {
       double d2 = 0.0;
       d2 = d_add(d2, qx);
       d2 = d_add(d2, qy);

@@ -54,6 +54,36 @@ def test_probe_lattice_equals_oracle(orc, probe):
             assert n == len(b) and np.array_equal(a, b)
 
 
+def test_probe_cast_ray_range_boundary(orc, probe):
+    """max_range set right at the distance of the voxel a ray would hit (a hair below, exactly, a hair
+    above, and a voxel either side): the range test decides, and the engine's version of it — which
+    skips the bookkeeping while the range provably cannot be exceeded — must decide as the oracle does."""
+    res = 0.25
+    km, dm, occ, known = scenes.synthetic_map(n_vox=64, res=res, seed=2, n_boxes=8, n_spheres=6, region=12.0)
+    w = orc.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    rng = np.random.RandomState(5)
+    n = 6000
+    O = rng.uniform(-6, 6, (n, 3)).astype(np.float32)
+    D = rng.normal(size=(n, 3)).astype(np.float32)
+    hit, key = w.cast_rays(O, D, True, np.full(n, -1.0))
+    sel = hit.astype(bool)
+    assert sel.sum() > 1000
+    O, D, key = O[sel], D[sel], key[sel]
+    centre = ((key.astype(np.float64) - 32768 + 0.5) * res).astype(np.float32)
+    dist = np.linalg.norm(centre.astype(np.float64) - O.astype(np.float64), axis=1)
+    total = 0
+    for f in (1 - 1e-6, 1.0, 1 + 1e-6, 0.93, 1.07):
+        mr = dist * f
+        mr[mr <= 0] = 1e-3
+        ho, ko = w.cast_rays(O, D, True, mr)
+        hp, kp = probe.cast_rays(res, km, dm, occ, known, O, D, True, mr)
+        assert np.array_equal(ho, hp) and np.array_equal(ko, kp)
+        total += int(ho.sum())
+    assert 0 < total < 5 * len(O)
+    w.close()
+
+
 @pytest.mark.parametrize("ignore_unknown", [True, False])
 def test_probe_cast_ray_equals_oracle(orc, probe, ignore_unknown):
     res = 0.25
