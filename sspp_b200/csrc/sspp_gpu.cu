@@ -712,6 +712,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   }
   unsigned long long hc[9];
   long long E = 0;
+  bool range_error = false;
   for (int attempt = 0;; ++attempt) {
     const long long cap = pair_capacity();
     if (!a.slot) {
@@ -818,12 +819,8 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       if (sink->peers)
         for (int p = 0; p < sink->peers->world; ++p)
           if (ctx->peer_stream[p]) CK(cudaStreamSynchronize(ctx->peer_stream[p]));
-      if (range_fail) {
-        if (stats) stats->edges = E;
-        return fail(ctx, SSPP_ERR_RANGE, sink->peers ? "connect_to_peers: the block does not fit its column slot"
-                                                     : "connect_nodes_host: col_idx capacity too small");
-      }
-      if (!copies_off) {
+      if (range_fail) range_error = true;  // reported below, once the resident result is registered (connect_fetch still works)
+      if (!copies_off && !range_fail) {
         if (!sink->peers) sink->row_ptr[nrows] = E;
         sink->delivered = true;
       }
@@ -863,6 +860,9 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   ctx->has_result = true;
   ctx->res_rows = nrows;
   ctx->res_edges = E;
+  if (range_error)
+    return fail(ctx, SSPP_ERR_RANGE, sink->peers ? "connect_to_peers: the block does not fit its column slot"
+                                                 : "connect_nodes_host: col_idx capacity too small");
   return SSPP_OK;
 }
 }  // namespace

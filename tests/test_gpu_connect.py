@@ -241,6 +241,8 @@ def test_connect_nodes_host_chunked_delivery(eng, chunks, slot, monkeypatch):
     with pytest.raises(SsppError) as e:
         eng.connect_nodes_host(nodes, rp, np.zeros(st0.edges // 2, dtype=np.int32), radius=1.5, box=BOX)
     assert e.value.code == 4
+    rp3, col3 = eng.connect_fetch(st0)  # the result stays resident: a caller can size its buffer and fetch
+    assert np.array_equal(rp3, rp0) and np.array_equal(col3, col0)
 
 
 def test_full_size_properties(eng):
