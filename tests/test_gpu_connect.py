@@ -220,6 +220,9 @@ def test_connect_nodes_host_chunked_delivery(eng, chunks, slot, monkeypatch):
     eng.map_create(0.3, km, dm, True)
     eng.map_upload_dense(occ, known)
     nodes = scenes.lattice_nodes(44, 1.0)  # 85 184 rows
+    if chunks == "3":  # an unordered node set: rows of a chunk are scattered over the cells
+        nodes = np.ascontiguousarray(nodes[np.random.RandomState(3).permutation(len(nodes))] +
+                                     np.random.RandomState(4).uniform(-0.2, 0.2, nodes.shape))
     eng.set_nodes(nodes)
     st0 = eng.connect(radius=1.5, box=BOX)
     rp0, col0 = eng.connect_fetch(st0)
