@@ -171,7 +171,7 @@ struct ConnectArgs {
   int mode;
   int use_map;
   int use_pyramid;
-  TileShape ts;
+  RowReach ts;
   // Pair storage.  slot > 0: row r owns the fixed slot [r*slot, r*slot + slot) of the pair buffers and
   // cand_count[r] says how many entries it holds — the counting pass writes the pairs itself, no scan
   // and no second neighbour pass; a row with more than `slot` pairs raises counters[8] and the host

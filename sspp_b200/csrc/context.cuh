@@ -25,10 +25,8 @@ struct DevBuf {
   template <class T> T* as() const { return (T*)p; }
 };
 
-struct TileShape {
-  int XW, SY, SZ;     // 0 = no staging
-  double reach[3];    // radius + box/2 per axis
-  double half[3];     // box/2 per axis (largest ray offset)
+struct RowReach {
+  double reach[3];    // radius + box/2 per axis: how far from a row's node any of its rays can get
 };
 
 }  // namespace

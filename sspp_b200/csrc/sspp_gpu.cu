@@ -3,11 +3,14 @@
 // Hot path (reference file:line in include/sspp_gpu.h):
 //   map ingest      k_upload_boxes / k_set_box / k_dense_in  -> bit planes, k_blocked, k_pyramid
 //   neighbour search k_bbox, k_cell_hist, scan, k_cell_scatter  (uniform grid, cell edge >= radius)
-//                    k_count                                    (in-radius pairs per source row)
+//                    k_count                                    (in-radius pairs per source row, written
+//                                                                straight into fixed per-row slots)
 //   edge test        k_edges   persistent, one work row per warp: pairs ordered by list index, exact
 //                              key-box shortcuts per row / pair / ray, queued exact DDA walks
-//   CSR              scan + k_compact
-//   queries          k_check_segments, k_validity, k_cast_rays
+//   CSR              scan + k_compact; in row chunks with the copies to host / peers overlapped
+//                    (sspp_gpu_connect_to_host / _to_peers); k_push_csr = compaction result + all-gather
+//   node store       k_dedup_*  batched SearchSpace::insertNode
+//   queries          k_check_segments, k_validity, k_cast_rays; visibility (k_view_*)
 // There is no CPU fallback: every entry point runs these kernels or fails with a status.
 #include <cuda_runtime.h>
 #include <math.h>
@@ -482,10 +485,8 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   RayLattice lat;
   memset(&lat, 0, sizeof(lat));
   lat.rays = 1;
-  TileShape ts;
-  ts.XW = ts.SY = ts.SZ = 0;
+  RowReach ts;
   ts.reach[0] = ts.reach[1] = ts.reach[2] = 0;
-  ts.half[0] = ts.half[1] = ts.half[2] = 0;
   const int use_map = prm->use_map ? 1 : 0;
   if (use_map) {
     int rc = ensure_planes(ctx);
@@ -497,7 +498,6 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     const double rad = std::max(prm->radius, 0.0);
     for (int a = 0; a < 3; ++a) {
       ts.reach[a] = rad + prm->box[a] * 0.5;
-      ts.half[a] = prm->box[a] * 0.5;
     }
   }
   if (stats) stats->rays_per_pair = use_map ? lat.rays : 0;
