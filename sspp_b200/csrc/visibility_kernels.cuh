@@ -247,29 +247,48 @@ __global__ void __launch_bounds__(256) k_segment_sort(int nv, const long long* _
   extern __shared__ int sh[];
   const int SM_CAP = 8192;
   for (int w = blockIdx.x; w < nv; w += gridDim.x) {
-    long long b = ptr[w], len = ptr[w + 1] - b;
+    const long long b = ptr[w], len = ptr[w + 1] - b;
     if (len < 2) continue;
+    if (len <= 2 * 256) {
+      // short segments (the usual case: a viewpoint sees a hundred points or so): rank sort, two barriers.
+      // The indices of one viewpoint are distinct, so the rank of a value is the number of smaller ones;
+      // every thread reads the same shared word at the same time (a broadcast).
+      const int n = (int)len;
+      int* g = data + b;
+      for (int i = threadIdx.x; i < n; i += blockDim.x) sh[i] = g[i];
+      __syncthreads();
+      for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int v = sh[i];
+        int rank = 0;
+        for (int k = 0; k < n; ++k) rank += (sh[k] < v);
+        g[rank] = v;
+      }
+      __syncthreads();
+      continue;
+    }
     int* a = data + b;
-    bool in_smem = len <= SM_CAP;
+    const bool in_smem = len <= SM_CAP;
     if (in_smem) {
       for (int i = threadIdx.x; i < len; i += blockDim.x) sh[i] = a[i];
       a = sh;
     }
     __syncthreads();
-    long long P = 1;
-    while (P < len) P <<= 1;
-    for (long long k = 2; k <= P; k <<= 1) {
-      // flip: i in the lower half of its k-block is compared with its mirror
-      for (long long t = threadIdx.x; t < P / 2; t += blockDim.x) {
-        long long blk = t / (k / 2), o = t % (k / 2);
-        long long i = blk * k + o, j = blk * k + (k - 1 - o);
+    // bitonic network on the next power of two; blocks are powers of two, so the index arithmetic is shifts
+    int lp = 1;
+    while ((1ll << lp) < len) ++lp;
+    const long long half = 1ll << (lp - 1);
+    for (int lk = 1; lk <= lp; ++lk) {
+      // flip: i in the lower half of its 2^lk block is compared with its mirror
+      for (long long t = threadIdx.x; t < half; t += blockDim.x) {
+        const long long blk = t >> (lk - 1), o = t & ((1ll << (lk - 1)) - 1);
+        const long long i = (blk << lk) + o, j = (blk << lk) + ((1ll << lk) - 1 - o);
         if (i < len) cmpswap(a, i, j, len);
       }
       __syncthreads();
-      for (long long h = k / 4; h >= 1; h >>= 1) {
-        for (long long t = threadIdx.x; t < P / 2; t += blockDim.x) {
-          long long blk = t / h, o = t % h;
-          long long i = blk * 2 * h + o, j = i + h;
+      for (int lh = lk - 2; lh >= 0; --lh) {
+        for (long long t = threadIdx.x; t < half; t += blockDim.x) {
+          const long long blk = t >> lh, o = t & ((1ll << lh) - 1);
+          const long long i = (blk << (lh + 1)) + o, j = i + (1ll << lh);
           if (i < len) cmpswap(a, i, j, len);
         }
         __syncthreads();

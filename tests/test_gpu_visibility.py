@@ -50,8 +50,10 @@ def test_visibility_degenerate_inputs(eng, orc):
     w.close()
 
 
-def test_visibility_large_segments_sorted(eng, orc):
-    """more than 8192 visible points for one viewpoint exercises the global-memory sort path"""
+@pytest.mark.parametrize("n_pts,at_least,at_most", [(40000, 8193, 10**9), (6000, 513, 8192), (500, 2, 512)])
+def test_visibility_large_segments_sorted(eng, orc, n_pts, at_least, at_most):
+    """the three paths of the per-viewpoint sort: more than 8192 visible points for one viewpoint (bitonic
+    network in global memory), 513..8192 (in shared memory), up to 512 (rank sort)"""
     res = 0.25
     km, dm = [32768 - 48] * 3, [96] * 3
     occ = np.zeros((96, 96, 96), dtype=bool)
@@ -63,12 +65,12 @@ def test_visibility_large_segments_sorted(eng, orc):
     w = orc.world(res, True)
     w.build_dense(km, dm, ob, kb)
     rng = np.random.RandomState(0)
-    pts = np.stack([np.full(40000, 5.6), rng.uniform(-3, 3, 40000), rng.uniform(-3, 3, 40000)], axis=1).astype(np.float32)
+    pts = np.stack([np.full(n_pts, 5.6), rng.uniform(-3, 3, n_pts), rng.uniform(-3, 3, n_pts)], axis=1).astype(np.float32)
     pose = np.array([[0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 1.0]])  # looking along +x
     eng.set_model_points(pts)
     st, vp, idx = eng.visibility(pose, 90.0, 90.0, 0.5, 9.0)
     vp_o, idx_o, rays_o, _ = w.visibility(pose, 90.0, 90.0, 0.5, 9.0, pts)
-    assert st.visible_pairs > 8192
+    assert at_least <= st.visible_pairs <= at_most
     assert np.array_equal(vp, vp_o) and np.array_equal(idx, idx_o)
     w.close()
 
