@@ -281,6 +281,43 @@ def test_full_size_properties(eng):
     assert np.isin(key0, rows0.astype(np.int64) * len(nodes) + col0, assume_unique=True).all()
 
 
+def test_full_size_random_nodes_all_paths_agree(eng, monkeypatch):
+    """S4b shape (10^6 nodes uniform in the 100 m cube of the 512^3 map): every way the engine can run the
+    pass gives the same graph — fixed pair slots, scanned offsets, row shards put back together, the
+    chunked delivery to host buffers — and graph symmetry holds where the test is symmetric: without
+    a map, (i, j) is an edge iff (j, i) is."""
+    res = 0.3
+    km, dm, occ, known = scenes.synthetic_map(n_vox=512, res=res, seed=42)
+    nodes = scenes.uniform_nodes(1_000_000, extent=100.0, seed=43)
+    n = len(nodes)
+    eng.map_create(res, km, dm, True)
+    eng.map_upload_dense(occ, known)
+    eng.set_nodes(nodes)
+    s_slot = eng.connect(radius=1.5, box=BOX)
+    rp, col = eng.connect_fetch(s_slot)
+    assert 0 < s_slot.edges < s_slot.in_radius_pairs and s_slot.pyramid_rows > 0 and s_slot.lattice_pairs > 0
+    monkeypatch.setenv("SSPP_CONNECT_SLOT", "0")
+    s_scan = eng.connect(radius=1.5, box=BOX)
+    rp2, col2 = eng.connect_fetch(s_scan)
+    assert np.array_equal(rp, rp2) and np.array_equal(col, col2)
+    monkeypatch.delenv("SSPP_CONNECT_SLOT")
+    cuts = [0, 123_457, 600_000, n]
+    parts = [eng.connect_fetch(eng.connect(radius=1.5, box=BOX, rows=(cuts[g], cuts[g + 1]))) for g in range(3)]
+    assert np.array_equal(np.concatenate([p[1] for p in parts]), col)
+    base = np.cumsum([0] + [len(p[1]) for p in parts])
+    assert np.array_equal(np.concatenate([parts[g][0][:-1] + base[g] for g in range(3)] + [[base[3]]]), rp)
+    rph = np.zeros(n + 1, dtype=np.int64)
+    colh = np.zeros(s_slot.edges, dtype=np.int32)
+    s_host = eng.connect_nodes_host(nodes, rph, colh, radius=1.5, box=BOX)
+    assert s_host.edges == s_slot.edges and np.array_equal(rph, rp) and np.array_equal(colh, col)
+    s_free = eng.connect(radius=1.5, use_map=False)
+    rpf, colf = eng.connect_fetch(s_free)
+    rows = np.repeat(np.arange(n, dtype=np.int64), np.diff(rpf))
+    fwd = np.sort(rows * n + colf)
+    bwd = np.sort(colf.astype(np.int64) * n + rows)
+    assert np.array_equal(fwd, bwd)
+
+
 @pytest.mark.parametrize("res,box", [(0.3, BOX), (0.15, BOX), (1.0, BOX), (0.1, (0.5, 0.5, 0.3))])
 def test_voxel_step_count_matches_reference_semantics(eng, orc, res, box):
     """the instrumented run counts exactly the lookups getLineStatusBoundingBox performs (rays in
