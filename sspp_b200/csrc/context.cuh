@@ -85,7 +85,7 @@ struct sspp_gpu_ctx {
 
   // model points / visibility
   int64_t n_points = 0;
-  DevBuf pts, vis_cnt, vis_ptr, vis_idx, vis_poses, vis_counters, vis_bbox;
+  DevBuf pts, vis_cnt, vis_ptr, vis_idx, vis_poses, vis_counters, vis_bbox, vis_words, vis_mask;
   bool has_vis = false;
   int64_t vis_nv = 0, vis_total = 0;
 };

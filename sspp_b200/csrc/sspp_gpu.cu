@@ -124,7 +124,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
                     &ctx->rows, &ctx->row_flag, &ctx->row_free, &ctx->cand_count, &ctx->cand_off, &ctx->candA, &ctx->candB,
                     &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice, &ctx->work_rows,
                     &ctx->q0, &ctx->q1, &ctx->q2, &ctx->q3, &ctx->q4, &ctx->pts, &ctx->vis_cnt, &ctx->vis_ptr,
-                    &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
+                    &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->vis_words, &ctx->vis_mask, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
                     &ctx->dd_pend, &ctx->dd_dup, &ctx->dd_keep, &ctx->dd_misc};
   for (DevBuf* b : bufs) b->release();
   ctx->chunk_base.release();
@@ -1420,8 +1420,20 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
   int* vis_count = ray_count + nv;
   CK(ctx->q2.reserve((size_t)(nv + 1) * 8));
   long long* ray_off = ctx->q2.as<long long>();
+  // ballot words per viewpoint (the count pass keeps its frustum verdicts for the fill pass)
+  CK(ctx->vis_words.reserve((((size_t)nv * 4 + 7) & ~(size_t)7) + (size_t)(nv + 1) * 8));
+  int* words = ctx->vis_words.as<int>();
+  long long* word_off = (long long*)(ctx->vis_words.as<char>() + (((size_t)nv * 4 + 7) & ~(size_t)7));
+  k_view_bound<<<ceil_div(nv, 128), 128, 0, st>>>(views, (int)nv, g, ctx->cell_start.as<int>(), words);
+  LAUNCHED(ctx);
+  { int rc = scan_exclusive<long long>(ctx, words, nv, word_off); if (rc) return rc; }
+  long long nwords = 0;
+  CK(cudaMemcpyAsync(&nwords, word_off + nv, 8, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  CK(ctx->vis_mask.reserve((size_t)std::max<long long>(nwords, 1) * 4));
+  uint32_t* vmask = ctx->vis_mask.as<uint32_t>();
   k_view_gather<false><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, ctx->cell_start.as<int>(), sp, ray_count,
-                                                              nullptr, nullptr, nullptr);
+                                                              nullptr, nullptr, nullptr, word_off, vmask);
   LAUNCHED(ctx);
   { int rc = scan_exclusive<long long>(ctx, ray_count, nv, ray_off); if (rc) return rc; }
   long long nrays = 0;
@@ -1434,7 +1446,7 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
   int* ray_pt = ctx->q4.as<int>();
   uint8_t* vis = ctx->row_free.as<uint8_t>();
   k_view_gather<true><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, ctx->cell_start.as<int>(), sp, nullptr,
-                                                             ray_off, ray_view, ray_pt);
+                                                             ray_off, ray_view, ray_pt, word_off, vmask);
   LAUNCHED(ctx);
 
   // --- occlusion rays

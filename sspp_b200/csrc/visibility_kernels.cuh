@@ -145,35 +145,61 @@ __global__ void k_pts_scatter(const float* __restrict__ xyz, int64_t n, const in
   sp[pos] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], __int_as_float((int)i));
 }
 
+// Ballot words a viewpoint's gather loop produces: one per 32 candidate points of every (z, y) run of
+// its cell box.  The count pass stores its ballots there and the fill pass reads them back instead
+// of loading the points and running the six-plane test a second time.
+__global__ void k_view_bound(const ViewRec* __restrict__ views, int nv, PointGrid g, const int* __restrict__ cell_start,
+                             int* __restrict__ words) {
+  int w = blockIdx.x * blockDim.x + threadIdx.x;
+  if (w >= nv) return;
+  const ViewRec& R = views[w];
+  int n = 0;
+  for (int cz = R.c0[2]; cz <= R.c1[2]; ++cz)
+    for (int cy = R.c0[1]; cy <= R.c1[1]; ++cy) {
+      const int cb = (cz * g.n[1] + cy) * g.n[0];
+      n += (cell_start[cb + R.c1[0] + 1] - cell_start[cb + R.c0[0]] + 31) >> 5;
+    }
+  words[w] = n;
+}
+
 // one warp per viewpoint: in-frustum points of the cells its bounding box touches.
-// FILL == false: count only.  FILL == true: write (viewpoint, binned position) per ray.
+// FILL == false: run the frustum test, keep the ballots, count.  FILL == true (after the scan of the
+// counts): write (viewpoint, binned position) per ray from the stored ballots.
 template <bool FILL>
 __global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__ views, int64_t v0, int nv, PointGrid g,
                                                      const int* __restrict__ cell_start, const float4* __restrict__ sp,
                                                      int* __restrict__ ray_count, const long long* __restrict__ ray_off,
-                                                     int* __restrict__ ray_view, int* __restrict__ ray_pt) {
+                                                     int* __restrict__ ray_view, int* __restrict__ ray_pt,
+                                                     const long long* __restrict__ word_off, uint32_t* __restrict__ mask) {
   int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   int lane = threadIdx.x & 31;
   if (w >= nv) return;
   const ViewRec R = views[v0 + w];
   long long base = FILL ? ray_off[w] : 0;
-  int filled = 0;
+  uint32_t* mw = mask + word_off[w];
+  int filled = 0, it = 0;
   for (int cz = R.c0[2]; cz <= R.c1[2]; ++cz)
     for (int cy = R.c0[1]; cy <= R.c1[1]; ++cy) {
       int cb = (cz * g.n[1] + cy) * g.n[0];
       int b = cell_start[cb + R.c0[0]], e = cell_start[cb + R.c1[0] + 1];
-      for (int j0 = b; j0 < e; j0 += 32) {
+      for (int j0 = b; j0 < e; j0 += 32, ++it) {
         int j = j0 + lane;
-        bool in = false;
-        if (j < e) {
-          float4 p = sp[j];
-          in = in_frustum_dev(R, p.x, p.y, p.z);
-        }
-        unsigned bal = __ballot_sync(0xffffffffu, in);
-        if (FILL && in) {
-          long long o = base + filled + __popc(bal & ((1u << lane) - 1u));
-          ray_view[o] = w;
-          ray_pt[o] = j;
+        unsigned bal;
+        if (FILL) {
+          bal = mw[it];
+          if ((bal >> lane) & 1u) {
+            long long o = base + filled + __popc(bal & ((1u << lane) - 1u));
+            ray_view[o] = w;
+            ray_pt[o] = j;
+          }
+        } else {
+          bool in = false;
+          if (j < e) {
+            float4 p = sp[j];
+            in = in_frustum_dev(R, p.x, p.y, p.z);
+          }
+          bal = __ballot_sync(0xffffffffu, in);
+          if (lane == 0) mw[it] = bal;
         }
         filled += __popc(bal);
       }
