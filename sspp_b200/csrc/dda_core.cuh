@@ -223,28 +223,34 @@ SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float di
       qz = (double)f_mul(ddz, ddz);
       ranged = true;
     }
-    int dim;
-    if (tx < ty) dim = (tx < tz) ? 0 : 2;
-    else dim = (ty < tz) ? 1 : 2;
-    if (dim == 0) {
-      if ((sx < 0 && kx == 0) || (sx > 0 && kx == 65535)) return false;
-      kx += sx; tx = d_add(tx, dtx);
-      if (check) { float dd = f_sub(d2f(key_to_coord(ks, kx)), ox); qx = (double)f_mul(dd, dd); }
-    } else if (dim == 1) {
-      if ((sy < 0 && ky == 0) || (sy > 0 && ky == 65535)) return false;
-      ky += sy; ty = d_add(ty, dty);
-      if (check) { float dd = f_sub(d2f(key_to_coord(ks, ky)), oy); qy = (double)f_mul(dd, dd); }
-    } else {
-      if ((sz < 0 && kz == 0) || (sz > 0 && kz == 65535)) return false;
-      kz += sz; tz = d_add(tz, dtz);
-      if (check) { float dd = f_sub(d2f(key_to_coord(ks, kz)), oz); qz = (double)f_mul(dd, dd); }
-    }
+    // upstream's tie rule: x only if strictly below both, y only if strictly below z, else z.  The
+    // three per-axis branches are written as selects: the lanes of a warp step along different axes,
+    // and three divergent branches would each run at a third of the warp.
+    const bool d0 = (tx < ty) && (tx < tz);
+    const bool d1 = !(tx < ty) && (ty < tz);
+    const bool d2 = !d0 && !d1;
+    const int ksel = d0 ? kx : (d1 ? ky : kz);
+    const int ssel = d0 ? sx : (d1 ? sy : sz);
+    if ((ssel < 0 && ksel == 0) || (ssel > 0 && ksel == 65535)) return false;  // leaving the key space
+    const int kn = ksel + ssel;
+    const double tn = d_add(d0 ? tx : (d1 ? ty : tz), d0 ? dtx : (d1 ? dty : dtz));
+    kx = d0 ? kn : kx;
+    ky = d1 ? kn : ky;
+    kz = d2 ? kn : kz;
+    tx = d0 ? tn : tx;
+    ty = d1 ? tn : ty;
+    tz = d2 ? tn : tz;
     if (check) {
-      double d2 = 0.0;
-      d2 = d_add(d2, qx);
-      d2 = d_add(d2, qy);
-      d2 = d_add(d2, qz);
-      if (d2 > maxrange_sq) return false;
+      const float dd = f_sub(d2f(key_to_coord(ks, kn)), d0 ? ox : (d1 ? oy : oz));
+      const double qn = (double)f_mul(dd, dd);
+      qx = d0 ? qn : qx;
+      qy = d1 ? qn : qy;
+      qz = d2 ? qn : qz;
+      double dsq = 0.0;
+      dsq = d_add(dsq, qx);
+      dsq = d_add(dsq, qy);
+      dsq = d_add(dsq, qz);
+      if (dsq > maxrange_sq) return false;
     }
     if (steps) ++*steps;
     st = cell(kx, ky, kz);
