@@ -40,6 +40,25 @@ METRIC = "collision-checked edges/s (connectNodes graph build, 1M nodes / 512^3 
 UNIT = "edges/s"
 
 
+# stdout must carry exactly ONE line, the JSON result: file descriptor 1 is pointed at stderr for the
+# whole run (NCCL prints its version banner to stdout from C, whatever NCCL_DEBUG_FILE says; so may other
+# libraries) and the result line is written to the saved descriptor at the end.
+_RESULT_FD = None
+
+
+def claim_stdout():
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.write(_RESULT_FD if _RESULT_FD is not None else 1, (json.dumps(line) + "\n").encode())
+
+
 def workload_config(n_gpus, regions=1, assembler=None):
     w = ("S4a: 512^3 voxels @0.3 m (seed 42, 400 boxes + 200 spheres), 10^6 nodes on a 100^3 lattice @1.0 m, "
          "R=1.5, box (0.5,0.5,0.3) -> 27 rays/pair, treat_unknown_as_occupied")
@@ -244,7 +263,7 @@ def run_reference_arm(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -265,6 +284,7 @@ def main():
                          "chunk is computed), by one push kernel over NVLink peer memory after the pass (default: the fastest "
                          "at 2, 4 and 8 GPUs), or by NCCL all-gather + packing")
     args = ap.parse_args()
+    claim_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
         return
@@ -585,7 +605,7 @@ def main():
                     "ms_per_step": float(e2e_tot[0]) * 1e3 / K},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "visibility": vis,
             "tested_pairs_per_step": tested_all, "edges_per_step": edges_all, "multi_gpu": multi}
-    print(json.dumps(line))
+    emit(line)
     if distributed:
         dist.barrier()
         dist.destroy_process_group()
