@@ -364,9 +364,14 @@ def main():
         if args.assembler == "streamed":
             streamed = sharded.StreamedPeerAssembler(eng, n, dev)
             assembler = sharded.PeerCsrAssembler(eng, n, dev)  # the e2e leg (host buffers in) assembles after its pass
+        elif args.assembler == "peer":
+            try:
+                assembler = sharded.PeerCsrAssembler(eng, n, dev)
+            except sharded.PeerMemoryUnavailable as e:  # raised on every rank together
+                args.assembler = "nccl (peer memory unavailable: %s)" % e
+                assembler = sharded.GpuCsrAssembler(eng, n, dev)
         else:
-            cls = sharded.PeerCsrAssembler if args.assembler == "peer" else sharded.GpuCsrAssembler
-            assembler = cls(eng, n, dev)
+            assembler = sharded.GpuCsrAssembler(eng, n, dev)
 
     def assemble_csr(st):
         """N>1: every rank ends the step holding the whole graph's CSR (peer-memory push, or NCCL all-gather + packing)."""

@@ -116,6 +116,44 @@ class GpuCsrAssembler:
         raise RuntimeError("CSR assembly: column slots still too small after resizing")
 
 
+class PeerMemoryUnavailable(RuntimeError):
+    """Some rank could not create or map a peer buffer (CUDA IPC not permitted, no P2P path).  Raised on
+    EVERY rank together, so the callers can fall back to the NCCL assembler without a collective mismatch."""
+
+
+def exchange_peer_buffer(eng, nbytes, device):
+    """Create this rank's buffer and open every peer's: -> (own address, [address of rank g's buffer here]).
+    Collective.  The success of every rank is agreed on before anyone returns."""
+    from .engine import SsppError
+    world, rank = dist.get_world_size(), dist.get_rank()
+    err, ptr, handle, peers = None, 0, bytes(64), []
+    try:
+        ptr, handle = eng.peer_buffer_create(nbytes)
+    except SsppError as e:
+        err = e
+    mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(device)
+    allh = torch.empty(world * 64, dtype=torch.uint8, device=device)
+    dist.all_gather_into_tensor(allh, mine)
+    raw = allh.cpu().numpy().tobytes()
+    if err is None:
+        try:
+            for g in range(world):
+                peers.append(ptr if g == rank else eng.peer_buffer_open(raw[g * 64:(g + 1) * 64]))
+        except SsppError as e:
+            err = e
+    bad = torch.tensor([0 if err is None else 1], dtype=torch.int32, device=device)
+    dist.all_reduce(bad, op=dist.ReduceOp.MAX)
+    if int(bad.item()):
+        for g, q in enumerate(peers):
+            if g != rank:
+                eng.peer_buffer_release(q)
+        dist.barrier()
+        if ptr:
+            eng.peer_buffer_release(ptr)
+        raise PeerMemoryUnavailable(str(err) if err is not None else "another rank could not map the peer buffers")
+    return ptr, peers
+
+
 class _DeviceArray:
     """A raw device address as a torch tensor (no copy) via __cuda_array_interface__."""
 
@@ -156,14 +194,7 @@ class PeerCsrAssembler:
         self.col_ptr, self.col_peers, self.out_col = None, None, None
 
     def _exchange(self, nbytes):
-        """Create this rank's buffer and open every peer's: -> (own address, [address on rank g])."""
-        ptr, handle = self.eng.peer_buffer_create(nbytes)
-        mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(self.device)
-        allh = torch.empty(self.world * 64, dtype=torch.uint8, device=self.device)
-        dist.all_gather_into_tensor(allh, mine)
-        raw = allh.cpu().numpy().tobytes()
-        peers = [ptr if g == self.rank else self.eng.peer_buffer_open(raw[g * 64:(g + 1) * 64]) for g in range(self.world)]
-        return ptr, peers
+        return exchange_peer_buffer(self.eng, nbytes, self.device)
 
     def _release(self, ptr, peers):
         torch.cuda.synchronize()
@@ -238,13 +269,7 @@ class StreamedPeerAssembler:
         self.turn = 0
 
     def _exchange(self, nbytes):
-        ptr, handle = self.eng.peer_buffer_create(nbytes)
-        mine = torch.frombuffer(bytearray(handle), dtype=torch.uint8).to(self.device)
-        allh = torch.empty(self.world * 64, dtype=torch.uint8, device=self.device)
-        dist.all_gather_into_tensor(allh, mine)
-        raw = allh.cpu().numpy().tobytes()
-        peers = [ptr if g == self.rank else self.eng.peer_buffer_open(raw[g * 64:(g + 1) * 64]) for g in range(self.world)]
-        return ptr, peers
+        return exchange_peer_buffer(self.eng, nbytes, self.device)
 
     def _release_sets(self):
         torch.cuda.synchronize()
