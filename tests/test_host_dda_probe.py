@@ -46,6 +46,41 @@ def test_probe_line_status_bbox_equals_oracle(orc, probe, res, treat):
     w.close()
 
 
+@pytest.mark.parametrize("res", [0.3, 0.25, 0.1])
+def test_probe_tie_rule_on_exact_diagonals(orc, probe, res):
+    """Segments from voxel centres (and from points a few float ulps off them) along exact diagonals: tMax
+    ties at every step, so the walk is decided by the tie rule alone; and segments ending exactly on
+    voxel faces.  Status and lookup count must match the oracle ray by ray."""
+    nv = 64
+    km, dm, occ, known = scenes.synthetic_map(n_vox=nv, res=res, seed=21, n_boxes=10, n_spheres=8,
+                                              region=nv * res * 0.8, unknown_shell=0.15)
+    w = orc.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    rng = np.random.RandomState(7)
+    n = 3000
+    k0 = rng.randint(-20, 20, (n, 3))
+    S = (k0 + 0.5) * res
+    dirs = np.array([[1, 1, 0], [1, 0, 1], [0, 1, 1], [1, 1, 1], [-1, 1, 0], [1, -1, 1], [-1, -1, -1], [1, -1, 0], [2, 1, 0], [1, 2, 2]])
+    d = dirs[rng.randint(len(dirs), size=n)]
+    steps = rng.randint(1, 14, (n, 1))
+    E = S + d * steps * res
+    third = n // 3
+    # second third: nudge the start by a few float32 ulps; last third: end exactly on a voxel face
+    S32 = S.astype(np.float32)
+    S[third:2 * third] = np.nextafter(S32[third:2 * third], np.float32(1e9) * np.sign(rng.normal(size=(third, 3))).astype(np.float32)).astype(np.float64)
+    E[2 * third:] = np.round(E[2 * third:] / res) * res
+    zero = (0.0, 0.0, 0.0)  # a box of size 0: the lattice is the single centre ray
+    so, st_o, rays_o = w.line_status_bbox(S, E, zero, True)
+    sp, st_p = probe.line_status_bbox(res, km, dm, occ, known, True, S, E, zero)
+    assert rays_o == n or rays_o <= n
+    assert np.array_equal(so, sp) and st_o == st_p
+    assert len(np.unique(so)) >= 2
+    so2, st2, _ = w.line_status_bbox(S, E, BOX, True)
+    sp2, st2p = probe.line_status_bbox(res, km, dm, occ, known, True, S, E, BOX)
+    assert np.array_equal(so2, sp2) and st2 == st2p
+    w.close()
+
+
 def test_probe_lattice_equals_oracle(orc, probe):
     for res in (0.3, 0.25, 0.2, 0.15, 0.1, 0.05, 0.5, 1.0, 0.07):
         for size in BOX + (0.0, 1.0):
