@@ -52,3 +52,26 @@ def test_gpu_arm_prints_one_json_line_with_the_contract_keys(built):
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
     assert set(("sm_mhz", "sm_max_mhz", "reasons")) <= set(d["clocks"])
+
+
+def test_weak_scaling_regions_line_up_with_the_map_slabs():
+    """bench.py --gpus N stacks N S4a regions along z: region g's lattice must sit centred in slab g of the
+    tall map (keys [32768 - 256 N + 512 g, +512)), with room for the reach of its rays."""
+    import importlib.util
+    import numpy as np
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(REPO, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    from sspp_b200 import scenes
+    for regions in (1, 2, 4, 8):
+        kmin_z = 32768 - (b.N_VOX // 2) * regions
+        for g in range(regions):
+            zc = b.region_centre_z(g, regions)
+            nodes = scenes.lattice_nodes(4, (b.LATTICE - 1) / 3.0, centre=(0.0, 0.0, zc))  # the lattice's corners and thirds
+            keys = np.floor(nodes[:, 2] / b.RES).astype(np.int64) + 32768
+            lo, hi = kmin_z + b.N_VOX * g, kmin_z + b.N_VOX * (g + 1)
+            reach = int(np.ceil((b.RADIUS + max(b.BOX) / 2) / b.RES)) + 2
+            assert keys.min() - reach >= lo and keys.max() + reach < hi
+            assert abs((keys.min() - lo) - (hi - 1 - keys.max())) <= 1  # centred in its slab
+        cfg = b.workload_config(regions, regions, "peer" if regions > 1 else None)
+        assert cfg["nodes"] == regions * 10 ** 6 and cfg["voxels"] == regions * 512 ** 3
