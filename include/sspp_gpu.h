@@ -238,8 +238,11 @@ int sspp_gpu_check_segments(sspp_gpu_ctx* ctx, const double* starts_xyz, const d
  * so the call performs no cudaMalloc, cudaFree or other allocating call.
  *   - n may not exceed SSPP_NOALLOC_MAX_SEGMENTS; a larger batch is refused with SSPP_ERR_RANGE
  *     (split it, or use sspp_gpu_check_segments).
- *   - The first call on each device looks up the array's device address; make that first call
- *     before starting any stream capture on that device.
+ *   - The first call on each device looks up the array's device address, and — the CUDA runtime
+ *     loads kernels lazily — is also the call that loads the query kernel onto the device, which
+ *     the driver may back with memory of its own.  Make one warm-up call per device at start-up,
+ *     before starting any stream capture on that device and before the phase in which the device
+ *     must not be asked for memory; from the second call on nothing is loaded or allocated.
  *   - The array is shared by every context on the device and keeps the previous call's contents.
  *     Each call overwrites everything it later reads, so nothing needs clearing between calls, but
  *     two calls whose GPU work overlaps (different contexts or threads) would race on it: serialise them. */

@@ -31,9 +31,9 @@ def _nvcc():
 
 
 def build_gpu(force=False, verbose=False):
-    srcs = [os.path.join(CSRC, f) for f in ("sspp_gpu.cu", "engine.cuh", "dda_core.cuh", "context.cuh", "scan.cuh",
-                                            "map_kernels.cuh", "connect_kernels.cuh", "query_kernels.cuh",
-                                            "visibility_kernels.cuh")]
+    # every header of the one translation unit triggers a rebuild (a hand-kept list once missed dedup_kernels.cuh)
+    srcs = [os.path.join(CSRC, "sspp_gpu.cu")] + sorted(
+        os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h")))
     srcs.append(os.path.join(REPO, "include", "sspp_gpu.h"))
     if not force and _newer(LIB_GPU, srcs):
         return LIB_GPU

@@ -1231,11 +1231,13 @@ unsigned char* g_noalloc_addr[NA_MAX_DEVICES] = {nullptr};
 
 int noalloc_scratch_address(sspp_gpu_ctx* ctx, unsigned char** out) {
   if (ctx->device < 0 || ctx->device >= NA_MAX_DEVICES) return fail(ctx, SSPP_ERR_RANGE, "check_segments_noalloc: device index too large");
-  if (!g_noalloc_addr[ctx->device]) {
+  if (!__atomic_load_n(&g_noalloc_addr[ctx->device], __ATOMIC_ACQUIRE)) {
     unsigned char* ptr = nullptr;
     cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
-    if (e != cudaSuccess || !ptr) return cuda_fail(ctx, e, "cudaGetSymbolAddress(g_noalloc_scratch)");
-    g_noalloc_addr[ctx->device] = ptr;
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+    if (!ptr) return fail(ctx, SSPP_ERR_CUDA, "check_segments_noalloc: the runtime returned a null address for the scratch array");
+    // every caller on this device computes the same value, so a racing first call stores it twice at worst
+    __atomic_store_n(&g_noalloc_addr[ctx->device], ptr, __ATOMIC_RELEASE);
   }
   *out = g_noalloc_addr[ctx->device];
   return SSPP_OK;

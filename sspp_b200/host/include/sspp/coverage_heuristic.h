@@ -10,8 +10,8 @@
 //     of the original planner rewards a step (coverage gained alone when the step has zero length);
 //   * the search ends when coverage is within `tolerance` of the target;
 //   * edges are the swept-robot-box test of DistanceHeuristic against the same occupancy map.
-// Visible sets depend on the way-point only, so they are computed once per way-point, for all
-// children of an expansion in one batched call.
+// Visible sets depend on the way-point and the map only, so they are computed once per way-point and
+// map generation (GpuWorld::mapGeneration), for all children of an expansion in one batched call.
 #pragma once
 #include <unordered_map>
 #include "distance_heuristic.h"
@@ -61,7 +61,11 @@ class CoverageHeuristic : public DistanceHeuristic {
   int64_t modelSize = 0;
   double hfov = 58.0, vfov = 45.0, nearD = 0.7, farD = 6.0;
   double coverageTarget = 100.0, coverageTolerance = 0.0;
-  std::unordered_map<const SearchSpaceNode*, std::vector<int32_t> > seen_;  // way-point -> sorted visible indices
+  // way-point (by its never-reused uid, not its address) -> sorted visible indices; valid for the map
+  // generation seenGen_ only: any change of the occupancy map drops the cache and the running coverage
+  std::unordered_map<uint64_t, std::vector<int32_t> > seen_;
+  uint64_t seenGen_ = 0;
+  void dropStale();
   std::vector<float> model_;        // host copy of the model points (pointCloudDiff hands the uncovered ones back)
   std::vector<uint8_t> covered_;    // per model point: seen by a kept sample
   double clusterTolerance = 0.6, standoff = 3.0;

@@ -33,6 +33,9 @@ class GpuWorld {
   void insertPointcloud(const float* points_world_xyz, int64_t n, const double sensor_origin[3], double sensor_max_range);
   double getResolution() const { return resolution_; }
   bool hasMap() const { return has_map_; }
+  // bumped by every call that can change an occupancy answer: results cached from queries (the coverage
+  // heuristic's visible sets) are only valid for the generation they were computed in
+  uint64_t mapGeneration() const { return map_generation_; }
 
   // queries
   CellStatus getLineStatusBoundingBox(const double start[3], const double end[3], const double box[3]);
@@ -56,6 +59,7 @@ class GpuWorld {
   sspp_gpu_ctx* ctx_ = nullptr;
   double resolution_ = 0;
   bool has_map_ = false;
+  uint64_t map_generation_ = 0;
   void check(int rc, const char* where);
 };
 }  // namespace SSPP

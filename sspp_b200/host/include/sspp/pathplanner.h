@@ -15,6 +15,7 @@ class PathPlanner : public Astar {
   PathPlanner(Robot* rob, double regGridConRadius, int progressDisplayFrequency);
   PathPlanner(Robot* rob, double regGridConRadius, int progressDisplayFrequency, std::vector<Sensors>& rSensors);
   ~PathPlanner();
+  unsigned int getPlanningSteps();
   void setConRad(double r) { regGridConRadius = r; }
   void setMultiAgentSupport(bool on) { multiAgentSupport = on; }
   void freeResources();
@@ -22,8 +23,9 @@ class PathPlanner : public Astar {
   void generateRegularGrid(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize);
   void generateRegularGrid(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize, float gridRes);
   void generateRegularGrid(geometry_msgs::Pose gridStartPose, geometry_msgs::Vector3 gridSize, float gridRes,
-                           bool sampleOrientations, float orientationRes = 360, bool samplesFiltering = false,
-                           bool insertSearchSpace = true);
+                           bool sampleOrientations = false, float orientationRes = 360, bool samplesFiltering = false,
+                           bool insertSearchSpace = true);  // defaults as include/sspp/pathplanner.h:73 (a three-argument
+                                                            // call is ambiguous with the overload above, there as here)
   void connectNodes();
   void connectClustersInternalNodes(SearchSpaceNode* space, double connRadius);
   // links every point of cloudHull2 to its nearest point of cloudHull1, in all yaw combinations
@@ -39,6 +41,7 @@ class PathPlanner : public Astar {
   std::vector<geometry_msgs::Point> getConnections();
   std::vector<geometry_msgs::Point> getSearchSpace();
   void getRobotSensorPoses(geometry_msgs::PoseArray& robotPoses, std::vector<geometry_msgs::PoseArray>& sensorsPoses);
+  void getRobotSensorPoses(geometry_msgs::PoseArray& robotPoses, geometry_msgs::PoseArray& sensorPoses);
   void loadRegularGrid(const char* robotFile, const char* sensor1File, const char* sensor2File);
   void saveSearchSpace(const char* filename);
   bool loadSearchSpace(const char* filename);

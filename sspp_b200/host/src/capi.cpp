@@ -172,7 +172,13 @@ int sspph_generate_grid(void* p, const double start[3], const double size[3], fl
 }
 void sspph_insert_nodes(void* p, const double* poses, int64_t n) {
   Handle* h = (Handle*)p;
-  for (int64_t i = 0; i < n; ++i) h->planner->insertNode(mkpose(poses + 7 * i));
+  for (int64_t i = 0; i < n; ++i) {
+    const geometry_msgs::Pose q = mkpose(poses + 7 * i);
+    if (h->sensors.empty()) { h->planner->insertNode(q); continue; }
+    geometry_msgs::PoseArray sp;  // a planner with sensors stores every way-point with its viewpoints
+    for (Sensors& s : h->sensors) sp.poses.push_back(s.robot2sensorTransformation(q));
+    h->planner->insertNode(q, sp);
+  }
 }
 int sspph_load_regular_grid(void* p, const char* f1, const char* f2, const char* f3) {
   Handle* h = (Handle*)p;

@@ -12,6 +12,7 @@ void CoverageHeuristic::setModelPoints(const float* xyz, int64_t n) {
   world_->setModelPoints(xyz, n);
   modelSize = n;
   seen_.clear();
+  seenGen_ = world_->mapGeneration();
   model_.assign(xyz, xyz + 3 * n);
   covered_.assign((size_t)n, 0);
   coveredCount = 0;
@@ -22,11 +23,22 @@ void CoverageHeuristic::setFrustum(double h, double v, double n, double f) {
   seen_.clear();
 }
 
+// occlusion answers belong to one state of the map: after setFree / insertPointcloud / a new upload
+// the cached visible sets and the coverage accumulated from them are stale
+void CoverageHeuristic::dropStale() {
+  const uint64_t g = world_->mapGeneration();
+  if (g == seenGen_) return;
+  seenGen_ = g;
+  seen_.clear();
+  resetCoverage();
+}
+
 // visible sets of the way-points not seen yet: all their sensor poses in ONE engine call
 void CoverageHeuristic::ensureVisible(const std::vector<const SearchSpaceNode*>& wps) {
+  dropStale();
   std::vector<const SearchSpaceNode*> todo;
   for (const SearchSpaceNode* w : wps)
-    if (w && !seen_.count(w) && std::find(todo.begin(), todo.end(), w) == todo.end()) todo.push_back(w);
+    if (w && !seen_.count(w->uid) && std::find(todo.begin(), todo.end(), w) == todo.end()) todo.push_back(w);
   if (todo.empty()) return;
   std::vector<double> poses;
   std::vector<size_t> first(todo.size() + 1, 0);
@@ -50,17 +62,17 @@ void CoverageHeuristic::ensureVisible(const std::vector<const SearchSpaceNode*>&
       std::set_union(u.begin(), u.end(), idx.begin() + view_ptr[s], idx.begin() + view_ptr[s + 1], std::back_inserter(m));
       u.swap(m);
     }
-    seen_[todo[i]].swap(u);
+    seen_[todo[i]->uid].swap(u);
   }
 }
 
 const std::vector<int32_t>& CoverageHeuristic::visibleFrom(const SearchSpaceNode* wp) {
   ensureVisible(std::vector<const SearchSpaceNode*>(1, wp));
-  return seen_[wp];
+  return seen_[wp->uid];
 }
 
 void CoverageHeuristic::score(Node* n) {
-  const std::vector<int32_t>& mine = seen_[n->ssnode];
+  const std::vector<int32_t>& mine = seen_[n->ssnode->uid];
   n->coveredPoints.clear();
   if (n->parent)
     std::set_union(n->parent->coveredPoints.begin(), n->parent->coveredPoints.end(), mine.begin(), mine.end(),
@@ -124,7 +136,7 @@ double CoverageHeuristic::uncoveredShare(const std::vector<const SearchSpaceNode
   std::vector<int32_t> u;
   for (const SearchSpaceNode* w : waypoints) {
     std::vector<int32_t> m;
-    const std::vector<int32_t>& s = seen_[w];
+    const std::vector<int32_t>& s = seen_[w->uid];
     std::set_union(u.begin(), u.end(), s.begin(), s.end(), std::back_inserter(m));
     u.swap(m);
   }
@@ -135,6 +147,7 @@ bool CoverageHeuristic::filterAllPoses(const std::vector<geometry_msgs::Pose>& p
   const size_t n = poses.size();
   valid.assign(n, 0);
   if (n == 0) return true;
+  dropStale();
   std::vector<uint8_t> st(n, GpuWorld::kFree);
   if (world_->hasMap()) {
     std::vector<double> xyz(n * 3);
@@ -170,6 +183,7 @@ bool CoverageHeuristic::filterAllPoses(const std::vector<geometry_msgs::Pose>& p
 
 double CoverageHeuristic::pointCloudDiff(pcl::PointCloud<pcl::PointXYZ>::Ptr, pcl::PointCloud<pcl::PointXYZ>::Ptr& diff) {
   if (!diff) diff.reset(new pcl::PointCloud<pcl::PointXYZ>);
+  dropStale();
   diff->points.clear();
   for (int64_t i = 0; i < modelSize; ++i)
     if (!covered_[(size_t)i]) diff->points.push_back(pcl::PointXYZ(model_[3 * i], model_[3 * i + 1], model_[3 * i + 2]));

@@ -20,10 +20,20 @@ void GpuWorld::createMap(double resolution, const int32_t key_min[3], const int3
   check(sspp_gpu_map_create(ctx_, resolution, key_min, dims, treat_unknown ? 1 : 0), "map_create");
   resolution_ = resolution;
   has_map_ = true;
+  ++map_generation_;
 }
-void GpuWorld::setTreatUnknownAsOccupied(bool flag) { check(sspp_gpu_map_set_treat_unknown(ctx_, flag ? 1 : 0), "map_set_treat_unknown"); }
-void GpuWorld::setFree(const double position[3], const double box[3]) { check(sspp_gpu_map_set_box(ctx_, position, box, 0), "setFree"); }
-void GpuWorld::setOccupied(const double position[3], const double box[3]) { check(sspp_gpu_map_set_box(ctx_, position, box, 1), "setOccupied"); }
+void GpuWorld::setTreatUnknownAsOccupied(bool flag) {
+  ++map_generation_;
+  check(sspp_gpu_map_set_treat_unknown(ctx_, flag ? 1 : 0), "map_set_treat_unknown");
+}
+void GpuWorld::setFree(const double position[3], const double box[3]) {
+  ++map_generation_;
+  check(sspp_gpu_map_set_box(ctx_, position, box, 0), "setFree");
+}
+void GpuWorld::setOccupied(const double position[3], const double box[3]) {
+  ++map_generation_;
+  check(sspp_gpu_map_set_box(ctx_, position, box, 1), "setOccupied");
+}
 
 void GpuWorld::insertBoxes(const std::vector<std::pair<std::vector<double>, double> >& boxes, bool occupied) {
   std::vector<double> c, s;
@@ -37,13 +47,16 @@ void GpuWorld::insertBoxes(const std::vector<std::pair<std::vector<double>, doub
   insertBoxes(c.data(), s.data(), o.data(), (int64_t)s.size());
 }
 void GpuWorld::insertBoxes(const double* centres, const double* sizes, const uint8_t* occupied, int64_t n) {
+  ++map_generation_;
   check(sspp_gpu_map_upload_boxes(ctx_, centres, sizes, occupied, n), "map_upload_boxes");
 }
 void GpuWorld::uploadDense(const uint32_t* occ_bits, const uint32_t* known_bits) {
+  ++map_generation_;
   check(sspp_gpu_map_upload_dense(ctx_, occ_bits, known_bits), "map_upload_dense");
 }
 
 void GpuWorld::insertPointcloud(const float* pts, int64_t n, const double origin[3], double max_range) {
+  ++map_generation_;
   check(sspp_gpu_map_insert_pointcloud(ctx_, pts, n, origin, max_range), "map_insert_pointcloud");
 }
 

@@ -331,13 +331,33 @@ std::vector<geometry_msgs::Point> PathPlanner::getConnections() {
   return seg;
 }
 
+// way-points and sensor viewpoints, one PoseArray per sensor (:378-404).  As in the reference the number of
+// sensor arrays follows the head node's sensor poses; an empty search space (which the reference
+// dereferences) yields nothing.
 void PathPlanner::getRobotSensorPoses(geometry_msgs::PoseArray& robotPoses, std::vector<geometry_msgs::PoseArray>& sensorsPoses) {
-  for (size_t i = 0; i < robotSensors.size(); ++i) sensorsPoses.push_back(geometry_msgs::PoseArray());
+  if (!searchspace) return;
+  for (size_t i = 0; i < searchspace->sensorLocation.poses.size(); ++i) sensorsPoses.push_back(geometry_msgs::PoseArray());
   for (SearchSpaceNode* t = searchspace; t; t = t->next) {
     robotPoses.poses.push_back(t->location);
     for (size_t i = 0; i < sensorsPoses.size() && i < t->sensorLocation.poses.size(); ++i)
       sensorsPoses[i].poses.push_back(t->sensorLocation.poses[i]);
   }
+}
+
+// way-points and ALL sensor viewpoints in one array, node by node (:407-427)
+void PathPlanner::getRobotSensorPoses(geometry_msgs::PoseArray& robotPoses, geometry_msgs::PoseArray& sensorPoses) {
+  for (SearchSpaceNode* t = searchspace; t; t = t->next) {
+    robotPoses.poses.push_back(t->location);
+    for (const geometry_msgs::Pose& sp : t->sensorLocation.poses) sensorPoses.poses.push_back(sp);
+  }
+}
+
+// declared at include/sspp/pathplanner.h:63 of the reference and defined nowhere in it; here: the number of
+// way-points of the path the last startSearch returned (0 when it found none)
+unsigned int PathPlanner::getPlanningSteps() {
+  unsigned int steps = 0;
+  for (Node* q = paths.empty() ? nullptr : paths.back(); q; q = q->next) ++steps;
+  return steps;
 }
 
 // three pose files read in lock-step: robot pose + two sensor poses per way-point (:204-269)

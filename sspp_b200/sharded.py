@@ -66,8 +66,8 @@ def assemble_csr(row_ptr_local, col_local, counts=None, buffers=None):
 class GpuCsrAssembler:
     """Steady-state assembly for CUDA ranks: fixed-size slots all-gathered over NCCL, then packed on the
     device by the engine (sspp_gpu_assemble_csr_blocks) — no host round trip on the data path.  The
-    column slot size is learned on the first call (one count all-gather) and re-learned if a block
-    ever outgrows it."""
+    column slot size follows a MAX all-reduce of the ranks' block sizes (8 bytes, every call), so all
+    ranks grow their slots in the same call."""
 
     def __init__(self, eng, n_nodes, device):
         self.eng = eng
@@ -84,20 +84,28 @@ class GpuCsrAssembler:
         self.all_rp = torch.empty(self.world * self.stride_r, dtype=torch.int64, device=device)
         self.out_rp = torch.empty(n_nodes + 1, dtype=torch.int64, device=device)
         self.overflow = torch.zeros(1, dtype=torch.int64, device=device)
+        self.need = torch.zeros(1, dtype=torch.int64, device=device)
         self.send_col = self.all_col = self.out_col = None
 
-    def _size_columns(self, edges):
-        counts = gather_counts(0, edges, self.device)
-        self.stride_e = max(int(int(counts[:, 1].max()) * 1.1) + 1024, 1)
+    def _size_columns(self, edges_max):
+        """Local (no collective): every rank calls it with the same all-reduced figure."""
+        self.stride_e = max(int(edges_max * 1.1) + 1024, 1)
         self.send_col = torch.empty(self.stride_e, dtype=torch.int32, device=self.device)
         self.all_col = torch.empty(self.world * self.stride_e, dtype=torch.int32, device=self.device)
         self.out_col = torch.empty(self.world * self.stride_e, dtype=torch.int32, device=self.device)
 
     def assemble(self, stats):
         """stats: the ConnectStats of this rank's sspp_gpu_connect.  Returns (row_ptr, col_idx) device
-        tensors of the whole graph (col_idx is a view of the first E entries' buffer)."""
-        if self.stride_e == 0 or stats.edges > self.stride_e:
-            self._size_columns(int(stats.edges))
+        tensors of the whole graph (col_idx is a view of the first E entries' buffer).
+
+        Whether the column slots have to grow is decided by ALL ranks from the same number — a MAX
+        all-reduce of the block sizes, every call — never from a rank's own edge count: a rank that
+        resized alone would enter a different collective than its peers."""
+        self.need.fill_(int(stats.edges))
+        dist.all_reduce(self.need, op=dist.ReduceOp.MAX)
+        need = int(self.need.item())
+        if need > self.stride_e:
+            self._size_columns(need)
         for attempt in range(2):
             self.eng.connect_fetch_device(self.send_rp.data_ptr(), self.send_col.data_ptr())
             dist.all_gather_into_tensor(self.all_rp, self.send_rp)
@@ -110,9 +118,10 @@ class GpuCsrAssembler:
             over = int(self.overflow.item())
             if over == 0:
                 return self.out_rp, self.out_col
-            # some rank's block outgrew its slot (all ranks see the same flag): re-learn the slot size
+            # cannot happen after the all-reduce above; kept as a guard.  Every rank packs the same gathered
+            # blocks, so all of them see the same flag and resize together.
             self.overflow.zero_()
-            self._size_columns(int(stats.edges))
+            self._size_columns(over)
         raise RuntimeError("CSR assembly: column slots still too small after resizing")
 
 

@@ -119,6 +119,55 @@ def test_coverage_heuristic_plans_a_view_path(eng, orc):
     w.close()
 
 
+def test_coverage_cache_follows_map_and_node_changes(eng, orc):
+    """The coverage heuristic caches a way-point's visible set.  The cache has to follow the world: after the
+    map changes between two queries (the reactive path: setOccupied / setFree / a new cloud) the answer is the
+    oracle's for the NEW map, and a way-point created after another was removed (its memory may be reused)
+    gets its own visible set, not the removed one's."""
+    from sspp_b200 import scenes
+    res = 0.25
+    km, dm, occ, known = scenes.synthetic_map(n_vox=96, res=res, seed=4, n_boxes=10, n_spheres=8, region=16.0)
+    pts = scenes.surface_points(occ, known, km, dm, res, 30000, seed=45)
+    cam = dict(mount_xyz=[0.1, 0.0, -0.05], mount_rpy=[0.0, 0.3, 0.0], hfov=58.0, vfov=45.0, near=0.7, far=6.0)
+    p = host_lib.HostPlanner(1.6, device=0, coverage=cam)
+    p.map_create(res, km, dm, True)
+    p.map_upload_dense(occ, known)
+    p.set_model_points(pts)
+    p.generate_grid([0, 0, 0], [14, 14, 4], 1.5, True, 90.0)
+    poses, _ = p.nodes()
+    sens = p.sensor_poses()
+    w = orc.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    # a way-point that sees something
+    seen = [(i, p.visible_from(i)) for i in range(0, len(poses), 7)]
+    i, before = max(seen, key=lambda t: len(t[1]))
+    assert len(before) > 20
+    _, want, _, _ = w.visibility(sens[i:i + 1], 58.0, 45.0, 0.7, 6.0, pts)
+    assert np.array_equal(before, want)
+    # a wall right in front of that sensor, on the engine and on the oracle alike
+    q = sens[i, 3:7]
+    fwd = np.array([1 - 2 * (q[1] ** 2 + q[2] ** 2), 2 * (q[0] * q[1] + q[3] * q[2]), 2 * (q[0] * q[2] - q[3] * q[1])])
+    wall = sens[i, :3] + 0.9 * fwd
+    p.map_set_box(wall, [1.6, 1.6, 1.6], True)
+    w.set_box(wall, [1.6, 1.6, 1.6], True)
+    after = p.visible_from(i)
+    _, want2, _, _ = w.visibility(sens[i:i + 1], 58.0, 45.0, 0.7, 6.0, pts)
+    assert np.array_equal(after, want2)
+    assert len(after) < len(before)  # the stale answer would have been `before`
+    # remove that way-point and insert a new one elsewhere: whatever address it gets, it is a new way-point
+    assert p.remove_node(poses[i])
+    far = poses[i].copy()
+    far[:3] += [0.37, -0.21, 0.11]
+    p.insert_nodes(far[None, :])
+    poses2, _ = p.nodes()
+    j = int(np.nonzero(np.all(np.abs(poses2 - far) < 1e-12, axis=1))[0][0])
+    sens2 = p.sensor_poses()
+    _, want3, _, _ = w.visibility(sens2[j:j + 1], 58.0, 45.0, 0.7, 6.0, pts)
+    assert np.array_equal(p.visible_from(j), want3)
+    p.close()
+    w.close()
+
+
 def test_casarea_scenario_through_the_mirror(eng):
     """config 1 on the casarea map: grid -> connectNodes (GPU, 847 rays per pair) -> A*, against the path the
     reference's compiled sources found on the same map"""
