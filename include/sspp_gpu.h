@@ -142,6 +142,12 @@ typedef struct sspp_connect_stats {
 int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* params, sspp_connect_stats* stats);
 /* Copies the last CSR to host: row_ptr has rows+1 entries (relative to row_begin), col_idx has `edges`. */
 int sspp_gpu_connect_fetch(sspp_gpu_ctx* ctx, int64_t* row_ptr, int32_t* col_idx);
+/* Diagnostics for the parity tests (no counterpart in the reference): how each row of the last connect
+ * was answered, one byte per row — 0 the row has no in-radius pair; 1 every pair accepted because the
+ * row's whole reach is free in the coarse pyramid (or no map is used); 2 every pair accepted because the
+ * key box spanned by all of the row's rays holds no blocked voxel; 3 the row was decided pair by pair
+ * (start voxels, pair key boxes, ray lattice).  The tests use it to draw oracle checks from every class. */
+int sspp_gpu_connect_row_classes(sspp_gpu_ctx* ctx, uint8_t* row_class);
 /* Same, into DEVICE buffers of the caller (e.g. the send buffers of an NCCL all-gather). */
 int sspp_gpu_connect_fetch_device(sspp_gpu_ctx* ctx, int64_t* row_ptr_device, int32_t* col_idx_device);
 /* Multi-GPU assembly (SURVEY.md §8 e): after an all-gather of every rank's padded blocks —
@@ -270,11 +276,14 @@ int sspp_gpu_cast_rays(sspp_gpu_ctx* ctx, const float* origins_xyz, const float*
  * ("visibility spec v1"): six-plane frustum test in float, then one castRay per in-frustum point. */
 typedef struct sspp_frustum {
   double hfov_deg, vfov_deg, near_dist, far_dist; /* Sensors::hFOV, vFOV, near, far (include/sspp/sensors.h:61) */
+  int32_t count_steps; /* 1: instrumented run, also counts the voxel lookups castRay performs (stats->voxel_steps) */
+  int32_t reserved;    /* 0 */
 } sspp_frustum;
 
 typedef struct sspp_visibility_stats {
   int64_t visible_pairs; /* total (viewpoint, point) pairs visible */
   int64_t rays;          /* occlusion rays cast = in-frustum pairs */
+  int64_t voxel_steps;   /* with count_steps: cells castRay looked up over all rays (the k of SURVEY.md §8 d's byte model) */
 } sspp_visibility_stats;
 
 /* Model points (float xyz), kept resident and binned for frustum queries. */
@@ -285,6 +294,10 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* sensor_poses, int64_t n
                         sspp_visibility_stats* stats);
 /* view_ptr: nv+1 entries; point_idx: visible_pairs entries, ascending within a viewpoint. */
 int sspp_gpu_visibility_fetch(sspp_gpu_ctx* ctx, int64_t* view_ptr, int32_t* point_idx);
+/* Milliseconds the kernels of the last sspp_gpu_visibility spent on the stream (CUDA events):
+ * [0] total, [1] point binning (0 when the cached binning was reused), [2] viewpoint set-up + frustum
+ * gather (count and fill), [3] the occlusion rays (k_view_rays), [4] compaction + per-viewpoint sort. */
+int sspp_gpu_visibility_timings(sspp_gpu_ctx* ctx, float ms[8]);
 
 /* ---- measurement helpers ------------------------------------------------------------------ */
 /* Reads `bytes` of an L2-resident buffer `iters` times and returns the achieved GB/s — the

@@ -184,6 +184,9 @@ struct ConnectArgs {
   // (a chunk never has more work rows than rows), its length in counters[16 + c], its ticket in [32 + c].
   int nchunks;
   int chunk_lo[SSPP_MAX_CHUNKS + 1];
+  // Diagnostics (sspp_gpu_connect_row_classes): how every row was answered — 0 no pair, 1 reach free in the
+  // coarse pyramid (k_count), 2 the key box of all its pairs holds no blocked voxel (k_edges), 3 pair by pair
+  uint8_t* row_class;
 };
 
 // where row r keeps its pairs
@@ -259,6 +262,7 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
       row_free[r] = fr;
       inr = cnt; tested = tst; pyr = fr;
       is_work = a.use_map && !fr && cnt > 0;
+      a.row_class[r] = cnt == 0 ? 0 : (fr || !a.use_map ? 1 : 3);
       while (chunk + 1 < a.nchunks && r >= a.chunk_lo[chunk + 1]) ++chunk;
       // slot mode: a row that needs no ray keeps all its pairs; k_compact orders them on the way out
       if (slots && !is_work) deg[r] = cnt;

@@ -59,7 +59,7 @@ struct sspp_gpu_ctx {
   unsigned long long shard_bbox_host[7] = {0, 0, 0, 0, 0, 0, 0};
 
   // connect scratch + result
-  DevBuf bbox, cell_of, cell_start, cell_cursor, sorted_idx, sx, sy, sz, rows, row_flag, row_free;
+  DevBuf bbox, cell_of, cell_start, cell_cursor, sorted_idx, sx, sy, sz, rows, row_flag, row_free, row_class;
   DevBuf cand_count, cand_off, candA, candB, acc, deg, row_ptr, col_idx, counters, scan_tmp, lattice, work_rows;
   int sm_count = 148;
   bool has_result = false;
@@ -88,6 +88,14 @@ struct sspp_gpu_ctx {
   DevBuf pts, vis_cnt, vis_ptr, vis_idx, vis_poses, vis_counters, vis_bbox, vis_words, vis_mask;
   bool has_vis = false;
   int64_t vis_nv = 0, vis_total = 0;
+  // binning of the model points, kept while the points and the cell size do not change
+  DevBuf pts_cell_start, pts_sorted, vis_views, vis_rayoff, vis_rayview, vis_raypt, vis_flag;
+  bool pts_binned = false;
+  double pts_cell = 0;
+  unsigned long long pts_bbox_host[7] = {0, 0, 0, 0, 0, 0, 0};
+  bool pts_bbox_valid = false;
+  cudaEvent_t vev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  float vis_timings[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 namespace {

@@ -121,10 +121,11 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
   DevBuf* bufs[] = {&ctx->occ, &ctx->known, &ctx->blocked, &ctx->cblocked, &ctx->map_stage, &ctx->logodds, &ctx->scan_free,
                     &ctx->scan_occ, &ctx->pc_pts, &ctx->pc_keys, &ctx->pc_vals, &ctx->xyz, &ctx->bbox, &ctx->vis_bbox,
                     &ctx->cell_of, &ctx->cell_start, &ctx->cell_cursor, &ctx->sorted_idx, &ctx->sx, &ctx->sy, &ctx->sz,
-                    &ctx->rows, &ctx->row_flag, &ctx->row_free, &ctx->cand_count, &ctx->cand_off, &ctx->candA, &ctx->candB,
+                    &ctx->rows, &ctx->row_flag, &ctx->row_free, &ctx->row_class, &ctx->cand_count, &ctx->cand_off, &ctx->candA, &ctx->candB,
                     &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice, &ctx->work_rows,
                     &ctx->q0, &ctx->q1, &ctx->q2, &ctx->q3, &ctx->q4, &ctx->pts, &ctx->vis_cnt, &ctx->vis_ptr,
-                    &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->vis_words, &ctx->vis_mask, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
+                    &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->vis_words, &ctx->vis_mask, &ctx->pts_cell_start, &ctx->pts_sorted,
+                    &ctx->vis_views, &ctx->vis_rayoff, &ctx->vis_rayview, &ctx->vis_raypt, &ctx->vis_flag, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
                     &ctx->dd_pend, &ctx->dd_dup, &ctx->dd_keep, &ctx->dd_misc};
   for (DevBuf* b : bufs) b->release();
   ctx->chunk_base.release();
@@ -135,6 +136,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
   for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
   for (void* q : ctx->peer_created) cudaFree(q);
   for (int i = 0; i < 8; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  for (int i = 0; i < 6; ++i) if (ctx->vev[i]) cudaEventDestroy(ctx->vev[i]);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -636,6 +638,8 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   a.ts = ts;
   CK(ctx->cand_count.reserve((size_t)nrows * 4));
   CK(ctx->row_free.reserve((size_t)nrows));
+  CK(ctx->row_class.reserve((size_t)nrows));
+  a.row_class = ctx->row_class.as<uint8_t>();
   CK(ctx->cand_off.reserve((size_t)(nrows + 1) * 8));
   CK(ctx->counters.reserve(48 * 8));
   CK(cudaMemsetAsync(ctx->counters.p, 0, 48 * 8, st));
@@ -875,6 +879,17 @@ int sspp_gpu_connect_fetch(sspp_gpu_ctx* ctx, int64_t* row_ptr, int32_t* col_idx
   CK(cudaMemcpyAsync(row_ptr, ctx->row_ptr.p, (size_t)(ctx->res_rows + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
   if (ctx->res_edges)
     CK(cudaMemcpyAsync(col_idx, ctx->col_idx.p, (size_t)ctx->res_edges * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return SSPP_OK;
+}
+
+int sspp_gpu_connect_row_classes(sspp_gpu_ctx* ctx, uint8_t* row_class) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!ctx->has_result) return fail(ctx, SSPP_ERR_STATE, "connect_row_classes: no connect result");
+  if (!row_class) return fail(ctx, SSPP_ERR_INVALID, "connect_row_classes: null argument");
+  if (ctx->res_rows == 0) return SSPP_OK;
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaMemcpyAsync(row_class, ctx->row_class.p, (size_t)ctx->res_rows, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   return SSPP_OK;
 }
@@ -1330,11 +1345,25 @@ int sspp_gpu_set_model_points(sspp_gpu_ctx* ctx, const float* xyz, int64_t n) {
   if (n < 0 || (n > 0 && !xyz)) return fail(ctx, SSPP_ERR_INVALID, "set_model_points: null argument");
   if (n >= (int64_t)0x7fffffff) return fail(ctx, SSPP_ERR_RANGE, "set_model_points: point indices must fit in int32");
   CK(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
   CK(ctx->pts.reserve((size_t)std::max<int64_t>(n, 1) * 12));
-  if (n) CK(cudaMemcpyAsync(ctx->pts.p, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->stream));
-  CK(cudaStreamSynchronize(ctx->stream));
+  if (n) CK(cudaMemcpyAsync(ctx->pts.p, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, st));
   ctx->n_points = n;
   ctx->has_vis = false;
+  ctx->pts_binned = false;
+  ctx->pts_bbox_valid = false;
+  // the bounding box (and the finiteness check) belongs to the model: computed here, once, so that
+  // a visibility pass over resident points never waits for the host before its last kernel
+  if (n) {
+    CK(ctx->vis_bbox.reserve(7 * 8));
+    static const unsigned long long init[7] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
+    CK(cudaMemcpyAsync(ctx->vis_bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    k_pts_bbox<<<std::min(ceil_div(n, 256), 148 * 8), 256, 0, st>>>(ctx->pts.as<float>(), n, ctx->vis_bbox.as<unsigned long long>());
+    LAUNCHED(ctx);
+    CK(cudaMemcpyAsync(ctx->pts_bbox_host, ctx->vis_bbox.p, sizeof(ctx->pts_bbox_host), cudaMemcpyDeviceToHost, st));
+  }
+  CK(cudaStreamSynchronize(st));  // the host array may be reused on return
+  ctx->pts_bbox_valid = n > 0;
   return SSPP_OK;
 }
 
@@ -1351,6 +1380,7 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
   cudaStream_t st = ctx->stream;
   ctx->has_vis = false;
   if (stats) memset(stats, 0, sizeof(*stats));
+  for (int i = 0; i < 8; ++i) ctx->vis_timings[i] = 0;
   const int64_t np = ctx->n_points;
   CK(ctx->vis_ptr.reserve((size_t)(nv + 1) * 8));
   if (nv == 0 || np == 0) {
@@ -1360,23 +1390,19 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
     ctx->has_vis = true; ctx->vis_nv = nv; ctx->vis_total = 0;
     return SSPP_OK;
   }
+  for (int i = 0; i < 6; ++i)
+    if (!ctx->vev[i]) CK(cudaEventCreate(&ctx->vev[i]));
   // host half of the spec: tan() of the half angles, narrowed exactly as the oracle states
   float vfov_rad = float(fr->vfov_deg * M_PI / 180);
   float hfov_rad = float(fr->hfov_deg * M_PI / 180);
   float vh = float(2 * tan(vfov_rad / 2));
   float hw = float(2 * tan(hfov_rad / 2));
   float np_dist = (float)fr->near_dist, fp_dist = (float)fr->far_dist;
+  const bool count_steps = fr->count_steps != 0;
 
-  // --- bin the model points (cell edge = far/4)
-  // (its own buffer: ctx->bbox may hold the queued, not yet read bounding box of the node set)
-  CK(ctx->vis_bbox.reserve(7 * 8));
-  unsigned long long init[7] = {~0ull, ~0ull, ~0ull, 0, 0, 0, 0};
-  CK(cudaMemcpyAsync(ctx->vis_bbox.p, init, sizeof(init), cudaMemcpyHostToDevice, st));
-  k_pts_bbox<<<std::min(ceil_div(np, 256), 148 * 8), 256, 0, st>>>(ctx->pts.as<float>(), np, ctx->vis_bbox.as<unsigned long long>());
-  LAUNCHED(ctx);
-  unsigned long long hb[7];
-  CK(cudaMemcpyAsync(hb, ctx->vis_bbox.p, sizeof(hb), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
+  // --- the model points binned into cells of edge far/4: kept while the points and the cell size stay
+  if (!ctx->pts_bbox_valid) return fail(ctx, SSPP_ERR_STATE, "visibility: no model points");
+  const unsigned long long* hb = ctx->pts_bbox_host;
   if (hb[6]) return fail(ctx, SSPP_ERR_INVALID, "visibility: model points must be finite");
   PointGrid g;
   double ext[3];
@@ -1393,85 +1419,125 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
   g.inv_cell = 1.0 / cell;
   int64_t ncells = 1;
   for (int a = 0; a < 3; ++a) { g.n[a] = (int)floor(ext[a] * g.inv_cell) + 1; ncells *= g.n[a]; }
-  CK(ctx->cell_of.reserve((size_t)np * 4));
-  CK(ctx->cell_start.reserve((size_t)(ncells + 1) * 4));
-  CK(ctx->cell_cursor.reserve((size_t)(ncells + 1) * 4));
-  CK(ctx->sorted_idx.reserve((size_t)np * 4));
-  CK(ctx->q0.reserve((size_t)np * 16));
-  float4* sp = ctx->q0.as<float4>();
-  CK(cudaMemsetAsync(ctx->cell_cursor.p, 0, (size_t)(ncells + 1) * 4, st));
-  k_pts_hist<<<ceil_div(np, 256), 256, 0, st>>>(ctx->pts.as<float>(), np, g, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>());
-  LAUNCHED(ctx);
-  { int rc = scan_exclusive<int>(ctx, ctx->cell_cursor.as<int>(), ncells, ctx->cell_start.as<int>()); if (rc) return rc; }
-  CK(cudaMemcpyAsync(ctx->cell_cursor.p, ctx->cell_start.p, (size_t)ncells * 4, cudaMemcpyDeviceToDevice, st));
-  k_pts_scatter<<<ceil_div(np, 256), 256, 0, st>>>(ctx->pts.as<float>(), np, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>(),
-                                                  ctx->sorted_idx.as<int>(), sp);
-  LAUNCHED(ctx);
+  CK(cudaEventRecord(ctx->vev[0], st));
+  if (!ctx->pts_binned || ctx->pts_cell != cell) {
+    CK(ctx->cell_of.reserve((size_t)np * 4));
+    CK(ctx->pts_cell_start.reserve((size_t)(ncells + 1) * 4));
+    CK(ctx->cell_cursor.reserve((size_t)(ncells + 1) * 4));
+    CK(ctx->sorted_idx.reserve((size_t)np * 4));
+    CK(ctx->pts_sorted.reserve((size_t)np * 16));
+    CK(cudaMemsetAsync(ctx->cell_cursor.p, 0, (size_t)(ncells + 1) * 4, st));
+    k_pts_hist<<<ceil_div(np, 256), 256, 0, st>>>(ctx->pts.as<float>(), np, g, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>());
+    LAUNCHED(ctx);
+    { int rc = scan_exclusive<int>(ctx, ctx->cell_cursor.as<int>(), ncells, ctx->pts_cell_start.as<int>()); if (rc) return rc; }
+    CK(cudaMemcpyAsync(ctx->cell_cursor.p, ctx->pts_cell_start.p, (size_t)ncells * 4, cudaMemcpyDeviceToDevice, st));
+    k_pts_scatter<<<ceil_div(np, 256), 256, 0, st>>>(ctx->pts.as<float>(), np, ctx->cell_of.as<int>(), ctx->cell_cursor.as<int>(),
+                                                    ctx->sorted_idx.as<int>(), ctx->pts_sorted.as<float4>());
+    LAUNCHED(ctx);
+    ctx->pts_binned = true;
+    ctx->pts_cell = cell;
+  }
+  const float4* sp = ctx->pts_sorted.as<float4>();
+  const int* pcs = ctx->pts_cell_start.as<int>();
+  CK(cudaEventRecord(ctx->vev[1], st));
 
   // --- viewpoint records
   CK(ctx->vis_poses.reserve((size_t)nv * 56));
-  CK(ctx->q1.reserve((size_t)nv * sizeof(ViewRec)));
+  CK(ctx->vis_views.reserve((size_t)nv * sizeof(ViewRec)));
   CK(cudaMemcpyAsync(ctx->vis_poses.p, poses, (size_t)nv * 56, cudaMemcpyHostToDevice, st));
-  ViewRec* views = ctx->q1.as<ViewRec>();
-  k_view_setup<<<ceil_div(nv, 128), 128, 0, st>>>(ctx->vis_poses.as<double>(), nv, vh, hw, np_dist, fp_dist, g, views);
-  LAUNCHED(ctx);
-
-  // --- in-frustum pairs per viewpoint
+  ViewRec* views = ctx->vis_views.as<ViewRec>();
   CK(ctx->vis_cnt.reserve((size_t)nv * 4 * 2));
   int* ray_count = ctx->vis_cnt.as<int>();
   int* vis_count = ray_count + nv;
-  CK(ctx->q2.reserve((size_t)(nv + 1) * 8));
-  long long* ray_off = ctx->q2.as<long long>();
+  CK(ctx->vis_rayoff.reserve((size_t)(nv + 1) * 8));
+  long long* ray_off = ctx->vis_rayoff.as<long long>();
   // ballot words per viewpoint (the count pass keeps its frustum verdicts for the fill pass)
   CK(ctx->vis_words.reserve((((size_t)nv * 4 + 7) & ~(size_t)7) + (size_t)(nv + 1) * 8));
   int* words = ctx->vis_words.as<int>();
   long long* word_off = (long long*)(ctx->vis_words.as<char>() + (((size_t)nv * 4 + 7) & ~(size_t)7));
-  k_view_bound<<<ceil_div(nv, 128), 128, 0, st>>>(views, (int)nv, g, ctx->cell_start.as<int>(), words);
-  LAUNCHED(ctx);
-  { int rc = scan_exclusive<long long>(ctx, words, nv, word_off); if (rc) return rc; }
-  long long nwords = 0;
-  CK(cudaMemcpyAsync(&nwords, word_off + nv, 8, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  CK(ctx->vis_mask.reserve((size_t)std::max<long long>(nwords, 1) * 4));
-  uint32_t* vmask = ctx->vis_mask.as<uint32_t>();
-  k_view_gather<false><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, ctx->cell_start.as<int>(), sp, ray_count,
-                                                              nullptr, nullptr, nullptr, word_off, vmask);
-  LAUNCHED(ctx);
-  { int rc = scan_exclusive<long long>(ctx, ray_count, nv, ray_off); if (rc) return rc; }
-  long long nrays = 0;
-  CK(cudaMemcpyAsync(&nrays, ray_off + nv, 8, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  CK(ctx->q3.reserve((size_t)std::max<long long>(nrays, 1) * 4));
-  CK(ctx->q4.reserve((size_t)std::max<long long>(nrays, 1) * 4));
-  CK(ctx->row_free.reserve((size_t)std::max<long long>(nrays, 1)));
-  int* ray_view = ctx->q3.as<int>();
-  int* ray_pt = ctx->q4.as<int>();
-  uint8_t* vis = ctx->row_free.as<uint8_t>();
-  k_view_gather<true><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, ctx->cell_start.as<int>(), sp, nullptr,
-                                                             ray_off, ray_view, ray_pt, word_off, vmask);
-  LAUNCHED(ctx);
-
-  // --- occlusion rays
-  CK(cudaMemsetAsync(vis_count, 0, (size_t)nv * 4, st));
-  if (nrays) {
-    k_view_rays<<<(unsigned)((nrays + 255) / 256), 256, 0, st>>>(ctx->map, views, 0, sp, ray_view, ray_pt, nrays, vis, vis_count);
-    LAUNCHED(ctx);
-  }
+  CK(ctx->vis_counters.reserve(8 * 8));
   long long* vis_ptr = ctx->vis_ptr.as<long long>();
-  { int rc = scan_exclusive<long long>(ctx, vis_count, nv, vis_ptr); if (rc) return rc; }
-  long long total = 0;
-  CK(cudaMemcpyAsync(&total, vis_ptr + nv, 8, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  CK(ctx->vis_idx.reserve((size_t)std::max<long long>(total, 1) * 4));
-  k_view_compact<<<ceil_div(nv * 32, 256), 256, 0, st>>>((int)nv, ray_off, vis, ray_pt, sp, vis_ptr, ctx->vis_idx.as<int>());
-  LAUNCHED(ctx);
-  k_segment_sort<<<(unsigned)std::min<int64_t>(nv, 148 * 8), 256, 8192 * 4, st>>>((int)nv, vis_ptr, ctx->vis_idx.as<int>());
-  LAUNCHED(ctx);
-  CK(cudaStreamSynchronize(st));
+
+  // The mask / ray / index buffers keep their size from call to call.  The pass is queued in one go with
+  // the capacities it has; kernels refuse to run when a size outgrows its buffer, and the host sees all
+  // three sizes at its single synchronisation at the end: a steady-state call waits for the device once.
+  long long sizes[3] = {0, 0, 0};  // ballot words, rays, visible pairs
+  unsigned long long steps = 0;
+  for (int attempt = 0;; ++attempt) {
+    const long long mask_cap = (long long)(ctx->vis_mask.cap / 4);
+    const long long ray_cap = (long long)std::min(std::min(ctx->vis_rayview.cap / 4, ctx->vis_raypt.cap / 4), ctx->vis_flag.cap);
+    const long long out_cap = (long long)(ctx->vis_idx.cap / 4);
+    CK(cudaMemsetAsync(ctx->vis_counters.p, 0, 8 * 8, st));
+    k_view_setup<<<ceil_div(nv, 128), 128, 0, st>>>(ctx->vis_poses.as<double>(), nv, vh, hw, np_dist, fp_dist, g, views);
+    LAUNCHED(ctx);
+    k_view_bound<<<ceil_div(nv, 128), 128, 0, st>>>(views, (int)nv, g, pcs, words);
+    LAUNCHED(ctx);
+    { int rc = scan_exclusive<long long>(ctx, words, nv, word_off); if (rc) return rc; }
+    uint32_t* vmask = ctx->vis_mask.as<uint32_t>();
+    int* ray_view = ctx->vis_rayview.as<int>();
+    int* ray_pt = ctx->vis_raypt.as<int>();
+    uint8_t* vis = ctx->vis_flag.as<uint8_t>();
+    CK(cudaMemsetAsync(ray_count, 0, (size_t)nv * 4 * 2, st));
+    k_view_gather<false><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, pcs, sp, ray_count, nullptr, nullptr,
+                                                                nullptr, word_off, vmask, mask_cap, ray_cap);
+    LAUNCHED(ctx);
+    { int rc = scan_exclusive<long long>(ctx, ray_count, nv, ray_off); if (rc) return rc; }
+    k_view_gather<true><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, pcs, sp, nullptr, ray_off, ray_view, ray_pt,
+                                                               word_off, vmask, mask_cap, ray_cap);
+    LAUNCHED(ctx);
+    CK(cudaEventRecord(ctx->vev[2], st));
+    // --- occlusion rays
+    {
+      const int blocks = ctx->sm_count * 8;
+      if (count_steps)
+        k_view_rays<true><<<blocks, 256, 0, st>>>(ctx->map, views, 0, sp, ray_view, ray_pt, ray_off + nv, ray_cap, vis, vis_count,
+                                                  ctx->vis_counters.as<unsigned long long>());
+      else
+        k_view_rays<false><<<blocks, 256, 0, st>>>(ctx->map, views, 0, sp, ray_view, ray_pt, ray_off + nv, ray_cap, vis, vis_count,
+                                                   ctx->vis_counters.as<unsigned long long>());
+      LAUNCHED(ctx);
+    }
+    CK(cudaEventRecord(ctx->vev[3], st));
+    { int rc = scan_exclusive<long long>(ctx, vis_count, nv, vis_ptr); if (rc) return rc; }
+    k_view_compact<<<ceil_div(nv * 32, 256), 256, 0, st>>>((int)nv, ray_off, vis, ray_pt, sp, vis_ptr, ctx->vis_idx.as<int>(), ray_cap,
+                                                          out_cap);
+    LAUNCHED(ctx);
+    k_segment_sort<<<(unsigned)std::min<int64_t>(nv, 148 * 8), 256, 8192 * 4, st>>>((int)nv, vis_ptr, ctx->vis_idx.as<int>(), out_cap);
+    LAUNCHED(ctx);
+    CK(cudaEventRecord(ctx->vev[4], st));
+    CK(cudaMemcpyAsync(&sizes[0], word_off + nv, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&sizes[1], ray_off + nv, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&sizes[2], vis_ptr + nv, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&steps, ctx->vis_counters.p, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    bool again = false;
+    if (sizes[0] > mask_cap) { CK(ctx->vis_mask.reserve((size_t)(sizes[0] + sizes[0] / 8 + 64) * 4)); again = true; }
+    if (!again && sizes[1] > ray_cap) {
+      const size_t want = (size_t)(sizes[1] + sizes[1] / 8 + 64);
+      CK(ctx->vis_rayview.reserve(want * 4));
+      CK(ctx->vis_raypt.reserve(want * 4));
+      CK(ctx->vis_flag.reserve(want));
+      again = true;
+    }
+    if (!again && sizes[2] > out_cap) { CK(ctx->vis_idx.reserve((size_t)(sizes[2] + sizes[2] / 8 + 64) * 4)); again = true; }
+    if (!again) break;
+    if (attempt > 4) return fail(ctx, SSPP_ERR_CUDA, "visibility: buffers still too small after growing them");
+  }
+  cudaEventElapsedTime(&ctx->vis_timings[0], ctx->vev[0], ctx->vev[4]);
+  cudaEventElapsedTime(&ctx->vis_timings[1], ctx->vev[0], ctx->vev[1]);
+  cudaEventElapsedTime(&ctx->vis_timings[2], ctx->vev[1], ctx->vev[2]);
+  cudaEventElapsedTime(&ctx->vis_timings[3], ctx->vev[2], ctx->vev[3]);
+  cudaEventElapsedTime(&ctx->vis_timings[4], ctx->vev[3], ctx->vev[4]);
   ctx->has_vis = true;
   ctx->vis_nv = nv;
-  ctx->vis_total = total;
-  if (stats) { stats->visible_pairs = total; stats->rays = nrays; }
+  ctx->vis_total = sizes[2];
+  if (stats) { stats->visible_pairs = sizes[2]; stats->rays = sizes[1]; stats->voxel_steps = count_steps ? (int64_t)steps : 0; }
+  return SSPP_OK;
+}
+
+int sspp_gpu_visibility_timings(sspp_gpu_ctx* ctx, float ms[8]) {
+  if (!ctx || !ms) return SSPP_ERR_INVALID;
+  for (int i = 0; i < 8; ++i) ms[i] = ctx->vis_timings[i];
   return SSPP_OK;
 }
 

@@ -170,10 +170,14 @@ __global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__
                                                      const int* __restrict__ cell_start, const float4* __restrict__ sp,
                                                      int* __restrict__ ray_count, const long long* __restrict__ ray_off,
                                                      int* __restrict__ ray_view, int* __restrict__ ray_pt,
-                                                     const long long* __restrict__ word_off, uint32_t* __restrict__ mask) {
+                                                     const long long* __restrict__ word_off, uint32_t* __restrict__ mask,
+                                                     long long mask_cap, long long ray_cap) {
   int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   int lane = threadIdx.x & 31;
   if (w >= nv) return;
+  // the buffers keep their size from call to call; when this call's sizes outgrow them every kernel of
+  // the pass returns at once and the host, at its one synchronisation, grows them and repeats the pass
+  if (word_off[nv] > mask_cap || (FILL && ray_off[nv] > ray_cap)) return;
   const ViewRec R = views[v0 + w];
   long long base = FILL ? ray_off[w] : 0;
   uint32_t* mw = mask + word_off[w];
@@ -207,50 +211,64 @@ __global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__
   if (!FILL && lane == 0) ray_count[w] = filled;
 }
 
-// one thread per occlusion ray
+// one thread per occlusion ray, blocks of 256 rays handed out grid-stride (the ray count lives on the device:
+// ray_off[nv]).  COUNT: the instrumented variant also counts the cells castRay looks up.
+template <bool COUNT>
 __global__ void __launch_bounds__(256) k_view_rays(DeviceMap m, const ViewRec* __restrict__ views, int64_t v0,
                                                    const float4* __restrict__ sp, const int* __restrict__ ray_view,
-                                                   const int* __restrict__ ray_pt, long long nrays, uint8_t* __restrict__ vis,
-                                                   int* vis_count) {
-  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  bool visible = false;
-  int w = -1;
-  if (i < nrays) {
-    w = ray_view[i];
-    const ViewRec& R = views[v0 + w];
-    float4 p = sp[ray_pt[i]];
-    float ox = R.T[0], oy = R.T[1], oz = R.T[2];
-    float dx = f_sub(p.x, ox), dy = f_sub(p.y, oy), dz = f_sub(p.z, oz);
-    CellOccupiedOnly cell;  // ignoreUnknown = true: unknown cells are walked through
-    cell.m = &m;
-    int hx, hy, hz;
-    bool hit = cast_ray(m.ks, ox, oy, oz, dx, dy, dz, true, norm3f(dx, dy, dz), cell, hx, hy, hz);
-    if (!hit) visible = true;
-    else {
-      int kx, ky, kz;
-      visible = coord_to_key(m.ks, (double)p.x, kx) && coord_to_key(m.ks, (double)p.y, ky) &&
-                coord_to_key(m.ks, (double)p.z, kz) && kx == hx && ky == hy && kz == hz;
+                                                   const int* __restrict__ ray_pt, const long long* __restrict__ ray_total,
+                                                   long long ray_cap, uint8_t* __restrict__ vis, int* vis_count,
+                                                   unsigned long long* steps_total) {
+  const long long nrays = *ray_total;
+  if (nrays > ray_cap) return;
+  unsigned long long my_steps = 0;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x; i0 < nrays; i0 += (long long)gridDim.x * blockDim.x) {
+    const long long i = i0 + threadIdx.x;
+    bool visible = false;
+    int w = -1;
+    if (i < nrays) {
+      w = ray_view[i];
+      const ViewRec& R = views[v0 + w];
+      float4 p = sp[ray_pt[i]];
+      float ox = R.T[0], oy = R.T[1], oz = R.T[2];
+      float dx = f_sub(p.x, ox), dy = f_sub(p.y, oy), dz = f_sub(p.z, oz);
+      CellOccupiedOnly cell;  // ignoreUnknown = true: unknown cells are walked through
+      cell.m = &m;
+      int hx, hy, hz, nsteps = 0;
+      bool hit = cast_ray(m.ks, ox, oy, oz, dx, dy, dz, true, norm3f(dx, dy, dz), cell, hx, hy, hz, COUNT ? &nsteps : nullptr);
+      if (COUNT) my_steps += (unsigned long long)nsteps;
+      if (!hit) visible = true;
+      else {
+        int kx, ky, kz;
+        visible = coord_to_key(m.ks, (double)p.x, kx) && coord_to_key(m.ks, (double)p.y, ky) &&
+                  coord_to_key(m.ks, (double)p.z, kz) && kx == hx && ky == hy && kz == hz;
+      }
+      vis[i] = visible ? 1 : 0;
     }
-    vis[i] = visible ? 1 : 0;
+    // rays of one viewpoint are contiguous: aggregate the count per warp where the warp is uniform
+    unsigned bal = __ballot_sync(0xffffffffu, visible);
+    int w0 = __shfl_sync(0xffffffffu, w, 0);
+    bool uniform = __all_sync(0xffffffffu, w == w0 || w < 0);
+    if (uniform) {
+      if ((threadIdx.x & 31) == 0 && bal && w0 >= 0) atomicAdd(vis_count + w0, __popc(bal));
+    } else if (visible) {
+      atomicAdd(vis_count + w, 1);
+    }
   }
-  // rays of one viewpoint are contiguous: aggregate the count per warp where the warp is uniform
-  unsigned bal = __ballot_sync(0xffffffffu, visible);
-  int w0 = __shfl_sync(0xffffffffu, w, 0);
-  bool uniform = __all_sync(0xffffffffu, w == w0 || w < 0);
-  if (uniform) {
-    if ((threadIdx.x & 31) == 0 && bal && w0 >= 0) atomicAdd(vis_count + w0, __popc(bal));
-  } else if (visible) {
-    atomicAdd(vis_count + w, 1);
+  if (COUNT) {
+    for (int o = 16; o; o >>= 1) my_steps += __shfl_xor_sync(0xffffffffu, my_steps, o);
+    if ((threadIdx.x & 31) == 0 && my_steps) atomicAdd(steps_total, my_steps);
   }
 }
 
 // one warp per viewpoint: compact the visible rays' ORIGINAL point indices
 __global__ void k_view_compact(int nv, const long long* __restrict__ ray_off, const uint8_t* __restrict__ vis,
                                const int* __restrict__ ray_pt, const float4* __restrict__ sp,
-                               const long long* __restrict__ vis_ptr, int* __restrict__ out) {
+                               const long long* __restrict__ vis_ptr, int* __restrict__ out, long long ray_cap, long long out_cap) {
   int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   int lane = threadIdx.x & 31;
   if (w >= nv) return;
+  if (ray_off[nv] > ray_cap || vis_ptr[nv] > out_cap) return;
   long long b = ray_off[w], e = ray_off[w + 1], o = vis_ptr[w];
   for (long long j0 = b; j0 < e; j0 += 32) {
     long long j = j0 + lane;
@@ -269,9 +287,10 @@ __device__ __forceinline__ void cmpswap(int* a, long long i, long long j, long l
     if (x > y) { a[i] = y; a[j] = x; }
   }
 }
-__global__ void __launch_bounds__(256) k_segment_sort(int nv, const long long* __restrict__ ptr, int* data) {
+__global__ void __launch_bounds__(256) k_segment_sort(int nv, const long long* __restrict__ ptr, int* data, long long data_cap) {
   extern __shared__ int sh[];
   const int SM_CAP = 8192;
+  if (ptr[nv] > data_cap) return;
   for (int w = blockIdx.x; w < nv; w += gridDim.x) {
     const long long b = ptr[w], len = ptr[w + 1] - b;
     if (len < 2) continue;

@@ -39,7 +39,7 @@ class PeerBlocks(ctypes.Structure):
 
 class Frustum(ctypes.Structure):
     _fields_ = [("hfov_deg", ctypes.c_double), ("vfov_deg", ctypes.c_double), ("near_dist", ctypes.c_double),
-                ("far_dist", ctypes.c_double)]
+                ("far_dist", ctypes.c_double), ("count_steps", ctypes.c_int32), ("reserved", ctypes.c_int32)]
 
 
 class SensorModel(ctypes.Structure):
@@ -48,7 +48,7 @@ class SensorModel(ctypes.Structure):
 
 
 class VisibilityStats(ctypes.Structure):
-    _fields_ = [("visible_pairs", c_i64), ("rays", c_i64)]
+    _fields_ = [("visible_pairs", c_i64), ("rays", c_i64), ("voxel_steps", c_i64)]
 
 
 _lib = None
@@ -83,6 +83,7 @@ def load_library():
         "sspp_gpu_connect": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_fetch": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_connect_fetch_device": (ctypes.c_int, [c_vp, c_vp, c_vp]),
+        "sspp_gpu_connect_row_classes": (ctypes.c_int, [c_vp, c_vp]),
         "sspp_gpu_assemble_csr_blocks": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
         "sspp_gpu_peer_buffer_create": (ctypes.c_int, [c_vp, c_i64, ctypes.POINTER(c_vp), c_vp]),
         "sspp_gpu_peer_buffer_open": (ctypes.c_int, [c_vp, c_vp, ctypes.POINTER(c_vp)]),
@@ -104,6 +105,7 @@ def load_library():
         "sspp_gpu_set_model_points": (ctypes.c_int, [c_vp, c_vp, c_i64]),
         "sspp_gpu_visibility": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(Frustum), ctypes.POINTER(VisibilityStats)]),
         "sspp_gpu_visibility_fetch": (ctypes.c_int, [c_vp, c_vp, c_vp]),
+        "sspp_gpu_visibility_timings": (ctypes.c_int, [c_vp, c_vp]),
         "sspp_gpu_measure_l2_bandwidth": (ctypes.c_int, [c_vp, c_i64, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
         "sspp_gpu_launch_count": (c_i64, [c_vp]),
     }
@@ -235,6 +237,12 @@ class Engine:
         self._ck(self.L.sspp_gpu_connect_fetch(self.h, _p(rp), _p(col)))
         return rp[:stats.rows + 1], col[:stats.edges]
 
+    def connect_row_classes(self, stats):
+        """uint8 per row of the last connect: 0 no pair, 1 pyramid, 2 row key box free, 3 decided pair by pair."""
+        out = np.zeros(max(stats.rows, 1), dtype=np.uint8)
+        self._ck(self.L.sspp_gpu_connect_row_classes(self.h, _p(out)))
+        return out[:stats.rows]
+
     def connect_fetch_device(self, row_ptr_dev, col_idx_dev):
         """D2D copy of the last CSR into caller-owned device buffers (raw addresses)."""
         self._ck(self.L.sspp_gpu_connect_fetch_device(self.h, c_vp(row_ptr_dev), c_vp(col_idx_dev)))
@@ -358,17 +366,25 @@ class Engine:
         a = np.ascontiguousarray(xyz, dtype=np.float32).reshape(-1, 3)
         self._ck(self.L.sspp_gpu_set_model_points(self.h, _p(a), len(a)))
 
-    def visibility(self, poses, hfov_deg, vfov_deg, near, far, fetch=True):
-        P = _f64(poses, 7)
-        fr = Frustum(hfov_deg, vfov_deg, near, far)
+    def visibility(self, poses, hfov_deg, vfov_deg, near, far, fetch=True, count_steps=False, vp_out=None, idx_out=None):
+        """vp_out / idx_out: caller's (e.g. pinned) arrays for the result; idx_out must hold the visible pairs."""
+        P = poses if (isinstance(poses, np.ndarray) and poses.dtype == np.float64 and poses.flags.c_contiguous) else _f64(poses, 7)
+        fr = Frustum(hfov_deg, vfov_deg, near, far, int(bool(count_steps)), 0)
         st = VisibilityStats()
-        self._ck(self.L.sspp_gpu_visibility(self.h, _p(P), len(P), ctypes.byref(fr), ctypes.byref(st)))
+        nv = P.size // 7
+        self._ck(self.L.sspp_gpu_visibility(self.h, _p(P), nv, ctypes.byref(fr), ctypes.byref(st)))
         if not fetch:
             return st
-        vp = np.zeros(len(P) + 1, dtype=np.int64)
-        idx = np.zeros(max(st.visible_pairs, 1), dtype=np.int32)
+        vp = np.zeros(nv + 1, dtype=np.int64) if vp_out is None else vp_out
+        idx = np.zeros(max(st.visible_pairs, 1), dtype=np.int32) if idx_out is None else idx_out
+        assert len(vp) >= nv + 1 and len(idx) >= st.visible_pairs
         self._ck(self.L.sspp_gpu_visibility_fetch(self.h, _p(vp), _p(idx)))
-        return st, vp, idx[:st.visible_pairs]
+        return st, vp[:nv + 1], idx[:st.visible_pairs]
+
+    def visibility_timings(self):
+        t = np.zeros(8, dtype=np.float32)
+        self._ck(self.L.sspp_gpu_visibility_timings(self.h, _p(t)))
+        return t
 
     # ---- measurement
     def stream(self):

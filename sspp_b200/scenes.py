@@ -140,3 +140,48 @@ def viewpoints_near(points, n, standoff=3.0, seed=46):
             v[l] = (m[l, j] + m[j, l]) / s
             q[i] = v
     return np.ascontiguousarray(np.concatenate([pos, q], axis=1))
+
+
+def map_window(occ_bits, known_bits, key_min, lo_xyz, hi_xyz, res, margin_vox=3):
+    """The sub-volume of a packed map that covers the metric box [lo_xyz, hi_xyz] grown by `margin_vox`
+    voxels, as (key_min, dims, occ_bits, known_bits) in the same host format — what an oracle octree
+    needs to answer queries whose rays stay inside the box (the oracle cannot hold a 512^3 map)."""
+    nz, ny, nxw = occ_bits.shape
+    nx = nxw * 32
+    lo, hi = [], []
+    for a, n in zip(range(3), (nx, ny, nz)):
+        k0 = int(np.floor(lo_xyz[a] / res)) + 32768 - margin_vox - int(key_min[a])
+        k1 = int(np.floor(hi_xyz[a] / res)) + 32768 + margin_vox + 1 - int(key_min[a])
+        lo.append(max(k0, 0))
+        hi.append(min(k1, n))
+    xw0, xw1 = lo[0] // 32, (hi[0] + 31) // 32
+    sub_o = unpack_bits(occ_bits[lo[2]:hi[2], lo[1]:hi[1], xw0:xw1], (xw1 - xw0) * 32)[:, :, lo[0] - xw0 * 32: hi[0] - xw0 * 32]
+    sub_k = unpack_bits(known_bits[lo[2]:hi[2], lo[1]:hi[1], xw0:xw1], (xw1 - xw0) * 32)[:, :, lo[0] - xw0 * 32: hi[0] - xw0 * 32]
+    kmin = np.array([int(key_min[a]) + lo[a] for a in range(3)], dtype=np.int32)
+    dims = np.array([hi[a] - lo[a] for a in range(3)], dtype=np.int32)
+    return kmin, dims, pack_bits(sub_o), pack_bits(sub_k)
+
+
+def window_pairs(nodes, core_lo, core_hi, radius):
+    """Rows = nodes inside the box [core_lo, core_hi); returns (rows, i, j, same): for every row all ordered
+    in-radius pairs (i = row's list index, j = the other node's), with the reference's predicate
+    sqrt(dx*dx + dy*dy + dz*dz) <= radius in double, left to right (Dist, include/sspp/utils.h:356-359;
+    src/pathplanner.cpp:541), i != j; `same` marks pairs at identical positions (connected without a test)."""
+    from scipy.spatial import cKDTree
+    core_lo, core_hi = np.asarray(core_lo, float), np.asarray(core_hi, float)
+    near = np.nonzero(np.all((nodes >= core_lo - radius * 1.01) & (nodes <= core_hi + radius * 1.01), axis=1))[0]
+    sub = nodes[near]
+    in_core = np.all((sub >= core_lo) & (sub < core_hi), axis=1)
+    rows_local = np.nonzero(in_core)[0]
+    tree = cKDTree(sub)
+    nb = tree.query_ball_point(sub[rows_local], radius * 1.0001)
+    ii = np.repeat(rows_local, [len(x) for x in nb])
+    jj = np.concatenate([np.asarray(x, dtype=np.int64) for x in nb]) if len(nb) else np.zeros(0, dtype=np.int64)
+    keep = ii != jj
+    ii, jj = ii[keep], jj[keep]
+    d = sub[jj] - sub[ii]
+    dist = np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2])
+    keep = dist <= radius
+    ii, jj = ii[keep], jj[keep]
+    same = np.all(sub[ii] == sub[jj], axis=1)
+    return near[rows_local], near[ii], near[jj], same

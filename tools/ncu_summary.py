@@ -2,7 +2,10 @@
 """Summarise one `ncu --set full --import-source on` capture of a kernel into the text file kept
 under profiles/ (the .ncu-rep itself stays in gpurun_out/, which is scratch).
 
-    python tools/ncu_summary.py gpurun_out/k_edges.ncu-rep > profiles/r01_k_edges_ncu_summary.txt
+    python tools/ncu_summary.py gpurun_out/k_edges.ncu-rep [kernel-name-substring] > profiles/r01_k_edges_ncu_summary.txt
+
+With a kernel name the first launch whose name contains it is summarised (a capture of the whole step
+holds one launch of every kernel); without, the last launch of the report.
 
 First block: `metric value` lines (bench.py reads dram__bytes_read.sum / dram__bytes_write.sum, in
 Mbyte, from it), then the warp-stall reasons per issue-active warp, then the instruction count and
@@ -17,7 +20,9 @@ METRICS = ["gpu__time_duration.sum", "smsp__inst_executed.sum", "smsp__issue_act
            "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size",
            "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
            "smsp__thread_inst_executed_per_inst_executed.ratio", "l1tex__t_sector_hit_rate.pct", "lts__t_sector_hit_rate.pct",
-           "lts__t_bytes.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+           "lts__t_bytes.sum", "lts__t_sectors_op_read.sum", "lts__t_sectors_op_write.sum", "l1tex__t_bytes.sum",
+           "lts__t_sectors_srcunit_tex_op_read.sum", "lts__t_sectors_srcunit_ltcfabric.sum", "nvlrx__bytes.sum", "nvltx__bytes.sum",
+           "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
            "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
            "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
            "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active"]
@@ -29,8 +34,17 @@ def ncu(rep, *args):
 
 def main():
     rep = sys.argv[1]
+    kern = sys.argv[2] if len(sys.argv) > 2 else None
     rows = list(csv.reader(io.StringIO(ncu(rep, "--page", "raw"))))
     hdr, units, vals = rows[0], rows[1], rows[-1]
+    sel = []
+    if kern:
+        ki = hdr.index("Kernel Name")
+        match = [r for r in rows[2:] if len(r) > ki and kern in r[ki]]
+        if not match:
+            raise SystemExit("no launch of a kernel named *%s* in %s" % (kern, rep))
+        vals = match[0]
+        sel = ["-k", "regex:" + kern, "-c", "1"]
     print("# %s" % vals[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "# kernel")
     for m in METRICS:
         if m in hdr:
@@ -47,7 +61,7 @@ def main():
     for v, name in sorted(stalls, reverse=True):
         print("%.3f %s" % (v, name))
 
-    rows = list(csv.reader(io.StringIO(ncu(rep, "--page", "source", "--print-source", "cuda,sass"))))
+    rows = list(csv.reader(io.StringIO(ncu(rep, *sel, "--page", "source", "--print-source", "cuda,sass"))))
     agg = collections.defaultdict(lambda: [0, 0, 0])
     fname, have_hdr, tot_i, tot_s = None, False, 0, 0
     for r in rows:
