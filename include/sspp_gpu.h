@@ -131,7 +131,8 @@ typedef struct sspp_connect_stats {
   int64_t tested_pairs;    /* of those, pairs at different positions = pairs handed to the collision test (pathplanner.cpp:547) */
   int64_t rays_per_pair;   /* size of the ray lattice nx*ny*nz */
   int64_t pyramid_rows;    /* rows answered by the pyramid */
-  int64_t tile_rows;       /* reserved, always 0 (kept so the struct layout does not change) */
+  int64_t tile_rows;       /* rows accepted whole because the key box spanned by ALL their pairs holds no blocked voxel
+                              (the field keeps its round-1 name so the struct layout does not change) */
   int64_t box_pairs;       /* tested pairs accepted because the key box they sweep is free */
   int64_t lattice_pairs;   /* tested pairs that ran the ray lattice */
   int64_t voxel_steps;     /* with count_steps: lookups up to and including the first non-free voxel of the first

@@ -209,7 +209,8 @@ __device__ __forceinline__ bool pairs_unusable(const ConnectArgs& a, const long 
 
 // counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows, [3] voxel steps (instrumented),
 //           [4] next work row (edge kernel's ticket), [5] pairs accepted by their key box,
-//           [6] pairs that ran the ray lattice, [8] rows that overflowed their slot,
+//           [6] pairs that ran the ray lattice, [7] rows accepted by the key box of all their pairs,
+//           [8] rows that overflowed their slot,
 //           [16 + c] work rows of chunk c, [32 + c] next work row of chunk c (edge kernel's ticket)
 //
 // One thread per source row walks the 27 neighbouring cells (9 contiguous ranges of the cell-sorted
@@ -444,20 +445,90 @@ __device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, doubl
   return true;
 }
 
+// Blocked voxels of a key box (absolute keys, inclusive; at most 32 voxels per axis), looked at by the whole
+// warp at once: the y-runs of the box are spread over the lanes (y fastest in memory), every word is read
+// once.  Besides "any blocked voxel" the scan leaves the three axis PROJECTIONS of the blocked voxels,
+// relative to the box's low corner: bit i of xp is set iff some blocked voxel of the box has x = lox + i
+// (yp, zp likewise).  A smaller box inside this one whose x-range misses xp — or whose y-range misses yp,
+// or z-range zp — holds no blocked voxel: an implication, never an estimate.
+struct BoxProj {
+  int lo[3], hi[3];
+  unsigned xp, yp, zp;
+  bool valid;  // false: the box left the window / was too wide — nothing may be concluded from the projections
+};
+__device__ __forceinline__ unsigned range_mask(int b0, int b1) {  // bits b0..b1, 0 <= b0 <= b1 <= 31
+  return (0xffffffffu >> (31 - b1)) & (0xffffffffu << b0);
+}
+__device__ __forceinline__ BoxProj warp_box_scan(const DeviceMap& m, int lane, int lox, int hix, int loy, int hiy, int loz, int hiz) {
+  BoxProj P;
+  P.lo[0] = lox; P.lo[1] = loy; P.lo[2] = loz;
+  P.hi[0] = hix; P.hi[1] = hiy; P.hi[2] = hiz;
+  P.xp = P.yp = P.zp = 0xffffffffu;
+  P.valid = false;
+  const int x0 = lox - m.kmin[0], x1 = hix - m.kmin[0];
+  const int y0 = loy - m.kmin[1], y1 = hiy - m.kmin[1];
+  const int z0 = loz - m.kmin[2], z1 = hiz - m.kmin[2];
+  if (x0 < 0 || y0 < 0 || z0 < 0 || x1 >= m.dims[0] || y1 >= m.dims[1] || z1 >= m.dims[2] || x0 > x1 || y0 > y1 || z0 > z1 ||
+      x1 - x0 > 31 || y1 - y0 > 31 || z1 - z0 > 31)
+    return P;
+  const int ny = y1 - y0 + 1;
+  // lanes = (z sub-row, y): yb = ny rounded up to a power of two, 32 / yb z-slices per iteration
+  const int sh = ny <= 1 ? 0 : 32 - __clz(ny - 1);
+  const int ly = lane & ((1 << sh) - 1), lz = lane >> sh, zstep = 32 >> sh;
+  const int w0 = x0 >> 5, w1 = x1 >> 5;
+  const unsigned m0 = (w0 == w1) ? range_mask(x0 & 31, x1 & 31) : (0xffffffffu << (x0 & 31));
+  const unsigned m1 = (w0 == w1) ? 0u : (0xffffffffu >> (31 - (x1 & 31)));
+  unsigned a0 = 0, a1 = 0, zb = 0;
+  if (ly < ny) {
+    const uint32_t* base0 = m.blocked + map_word(m, w0, y0 + ly, 0);
+    const size_t wstride = (size_t)m.dims[2] * m.dims[1];
+    for (int z = z0 + lz; z <= z1; z += zstep) {
+      unsigned b0 = __ldg(base0 + (size_t)z * m.dims[1]) & m0;
+      unsigned b1 = m1 ? (__ldg(base0 + wstride + (size_t)z * m.dims[1]) & m1) : 0u;
+      a0 |= b0;
+      a1 |= b1;
+      zb |= (b0 | b1) ? (1u << (z - z0)) : 0u;
+    }
+  }
+  const unsigned long long both = (((unsigned long long)a1 << 32) | a0) >> (x0 & 31);
+  P.xp = __reduce_or_sync(0xffffffffu, (unsigned)both);
+  P.yp = __reduce_or_sync(0xffffffffu, (a0 | a1) ? (1u << ly) : 0u);
+  P.zp = __reduce_or_sync(0xffffffffu, zb);
+  P.valid = true;
+  return P;
+}
+// does the key box [lo, hi] provably hold no blocked voxel?  Only a box INSIDE the scanned one can be judged
+// (outside it the projections know nothing).
+__device__ __forceinline__ bool proj_free(const BoxProj& P, int lox, int hix, int loy, int hiy, int loz, int hiz) {
+  if (!P.valid || lox < P.lo[0] || hix > P.hi[0] || loy < P.lo[1] || hiy > P.hi[1] || loz < P.lo[2] || hiz > P.hi[2] || lox > hix ||
+      loy > hiy || loz > hiz)
+    return false;
+  return !(P.xp & range_mask(lox - P.lo[0], hix - P.lo[0])) || !(P.yp & range_mask(loy - P.lo[1], hiy - P.lo[1])) ||
+         !(P.zp & range_mask(loz - P.lo[2], hiz - P.lo[2]));
+}
+
 // Cheap verdict on one ray before any DDA arithmetic: RAY_FREE / RAY_BLOCKED are final, RAY_WALK
 // means the exact walk has to decide.  `fast` enables the key-box shortcut of line_status_fast.
 enum { RAY_FREE = 0, RAY_BLOCKED = 1, RAY_WALK = 2 };
+// okey: the ray's origin key when the caller already has it (NULL: computed here from the origin); P: the
+// projections of the blocked voxels of a box that holds the ray's key box, or an invalid one.
 __device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float ox, float oy, float oz, float ex, float ey,
-                                            float ez) {
+                                            float ez, const int* okey, const BoxProj& P) {
   int kx, ky, kz, ekx, eky, ekz;
-  if (!coord_to_key(m.ks, (double)ox, kx) || !coord_to_key(m.ks, (double)oy, ky) || !coord_to_key(m.ks, (double)oz, kz) ||
-      !coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
+  if (okey) {
+    kx = okey[0]; ky = okey[1]; kz = okey[2];
+    if (kx < 0) return RAY_FREE;
+  } else if (!coord_to_key(m.ks, (double)ox, kx) || !coord_to_key(m.ks, (double)oy, ky) || !coord_to_key(m.ks, (double)oz, kz)) {
     return RAY_FREE;  // out of key range: upstream leaves the ray empty
+  }
+  if (!coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
+    return RAY_FREE;
   if (kx == ekx && ky == eky && kz == ekz) return RAY_FREE;
   if (fast) {
     const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
     const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
     const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
+    if (proj_free(P, lox, hix, loy, hiy, loz, hiz)) return RAY_FREE;
     if (!box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) return RAY_FREE;
   }
   if (map_blocked(m, kx, ky, kz)) return RAY_BLOCKED;  // the start voxel is the first one the walk tests
@@ -589,28 +660,16 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
 
   const double px = me.x, py = me.y, pz = me.z;
   const int R = lat.rays;
-  const bool fast = a.use_pyramid != 0;
-  // Row-level verdicts: every ray starts at p + offset whatever the pair, and the start voxel is the
-  // first one a walk tests.  A ray whose start voxel is blocked therefore rejects every pair of this
-  // row for which that ray is not empty (its end key differs from its start key).
+  const bool fast = !COUNT && a.use_pyramid != 0;
+  // Row-level verdicts, computed when the first pair needs them: every ray starts at p + offset whatever
+  // the pair, and the start voxel is the first one a walk tests.  A ray whose start voxel is blocked
+  // therefore rejects every pair of this row for which that ray is not empty (its end key differs from
+  // its start key).  The origin keys are kept for the per-ray checks (-1: outside the key space).
   unsigned startmask = 0;
-  if (!COUNT && fast && R <= 32) {
-    bool blk = false;
-    if (lane < R) {
-      double ox, oy, oz;
-      ray_offset(sm, lane, ox, oy, oz);
-      int kx, ky, kz;
-      if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
-          coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz)) {
-        sm.okey[warp][lane][0] = kx; sm.okey[warp][lane][1] = ky; sm.okey[warp][lane][2] = kz;
-        blk = map_blocked(m, kx, ky, kz) != 0;
-      }
-    }
-    startmask = __ballot_sync(0xffffffffu, blk);
-    __syncwarp();
-  }
+  bool start_done = false;
   int nacc = 0;
   unsigned n_box = 0, n_lat = 0;
+  bool row_box_free = fast;
   unsigned long long nsteps = 0;
   for (int base = 0; base < n; base += 32) {
     const int nb = min(32, n - base);
@@ -622,30 +681,65 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     if (mine_valid) { const NodeRec o = load_node(a.sn + c.x); qx = o.x; qy = o.y; qz = o.z; }
     bool rejected = false;
     bool needs = mine_valid && !same;
-    // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
-    if (needs && startmask) {
-      for (unsigned mb = startmask; mb; mb &= mb - 1) {
-        const int q = __ffs(mb) - 1;
-        double ox, oy, oz;
-        ray_offset(sm, q, ox, oy, oz);
-        int ekx, eky, ekz;
-        if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
-            coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
-            (ekx != sm.okey[warp][q][0] || eky != sm.okey[warp][q][1] || ekz != sm.okey[warp][q][2])) {
-          needs = false;
-          rejected = true;
-          break;
-        }
+    // stage 1: the key box all rays of the pair stay in (one lane per pair) ...
+    int lox = 0, hix = 0, loy = 0, hiy = 0, loz = 0, hiz = 0;
+    bool boxed = false;
+    BoxProj P;
+    P.valid = false;
+    if (fast) {
+      boxed = needs && pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
+              pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
+              pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz);
+      // ... and the box that holds all of them, scanned once by the whole warp.  No blocked voxel in it:
+      // every pair of the batch is accepted.  Otherwise the projections of what is blocked decide most pairs
+      // (a pair whose x-, y- or z-range holds no blocked voxel of the batch box is free), and later most rays.
+      if (__any_sync(0xffffffffu, boxed)) {
+        const int big = 1 << 20;
+        const int ulx = __reduce_min_sync(0xffffffffu, boxed ? lox : big), uhx = __reduce_max_sync(0xffffffffu, boxed ? hix : -big);
+        const int uly = __reduce_min_sync(0xffffffffu, boxed ? loy : big), uhy = __reduce_max_sync(0xffffffffu, boxed ? hiy : -big);
+        const int ulz = __reduce_min_sync(0xffffffffu, boxed ? loz : big), uhz = __reduce_max_sync(0xffffffffu, boxed ? hiz : -big);
+        P = warp_box_scan(m, lane, ulx, uhx, uly, uhy, ulz, uhz);
+        if (boxed && proj_free(P, lox, hix, loy, hiy, loz, hiz)) needs = false;
       }
     }
-    // stage 2b: the pair's key box (one lane per pair)
-    if (!COUNT && fast && needs) {
-      int lox, hix, loy, hiy, loz, hiz;
-      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
-          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
-          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
-          (!box_maybe_blocked_coarse(m, lox, hix, loy, hiy, loz, hiz) || !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)))
-        needs = false;
+    if (__any_sync(0xffffffffu, needs)) {
+      row_box_free = false;
+      if (fast && R <= 32 && !start_done) {
+        bool blk = false;
+        if (lane < R) {
+          double ox, oy, oz;
+          ray_offset(sm, lane, ox, oy, oz);
+          int kx = -1, ky = -1, kz = -1;
+          if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
+              coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz)) {
+            blk = map_blocked(m, kx, ky, kz) != 0;
+          } else {
+            kx = -1;
+          }
+          sm.okey[warp][lane][0] = kx; sm.okey[warp][lane][1] = ky; sm.okey[warp][lane][2] = kz;
+        }
+        startmask = __ballot_sync(0xffffffffu, blk);
+        start_done = true;
+        __syncwarp();
+      }
+      // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
+      if (needs && startmask) {
+        for (unsigned mb = startmask; mb; mb &= mb - 1) {
+          const int q = __ffs(mb) - 1;
+          double ox, oy, oz;
+          ray_offset(sm, q, ox, oy, oz);
+          int ekx, eky, ekz;
+          if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
+              coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
+              (ekx != sm.okey[warp][q][0] || eky != sm.okey[warp][q][1] || ekz != sm.okey[warp][q][2])) {
+            needs = false;
+            rejected = true;
+            break;
+          }
+        }
+      }
+      // stage 2b: the pair's own key box, word by word (one lane per pair)
+      if (fast && needs && boxed && !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) needs = false;
     }
     unsigned need = __ballot_sync(0xffffffffu, needs);
     unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs && !rejected);  // same-position or box-free pairs
@@ -687,6 +781,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
       __syncwarp();
       const int W = __popc(need) * R;
+      const bool have_okey = start_done;
       unsigned blockedmask = 0;
       int qn = 0;
       for (int w0 = 0; w0 < W; w0 += 32) {
@@ -701,7 +796,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
             ray_offset(sm, q, ox, oy, oz);
             const double* f = sm.far_end[warp][k];
             verdict = ray_precheck(m, fast, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
-                                   d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)));
+                                   d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? sm.okey[warp][q] : nullptr, P);
           }
         }
         blockedmask |= __reduce_or_sync(0xffffffffu, verdict == RAY_BLOCKED ? (1u << k) : 0u);
@@ -728,6 +823,10 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
   }
   if (lane == 0) {
     deg[r] = nacc;
+    if (row_box_free) {
+      a.row_class[r] = 2;
+      atomicAdd(counters + 7, 1ull);
+    }
     if (n_box) atomicAdd(counters + 5, (unsigned long long)n_box);
     if (n_lat) atomicAdd(counters + 6, (unsigned long long)n_lat);
   }

@@ -850,7 +850,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     stats->tested_pairs = (int64_t)hc[1];
     stats->pyramid_rows = (int64_t)hc[2];
     stats->voxel_steps = count_steps ? (int64_t)hc[3] : 0;
-    stats->tile_rows = 0;
+    stats->tile_rows = (int64_t)hc[7];  // rows accepted whole by the key box of all their pairs
     stats->box_pairs = (int64_t)hc[5];
     stats->lattice_pairs = (int64_t)hc[6];
     stats->edges = E;
