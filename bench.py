@@ -40,10 +40,9 @@ UNIT = "edges/s"
 
 
 def metric_name(regions=1):
-    if regions > 1:
-        return ("collision-checked edges/s (connectNodes graph build, %dM nodes / 512x512x%d voxels = %d S4a regions, weak scaling)"
-                % (regions, 512 * regions, regions))
-    return "collision-checked edges/s (connectNodes graph build, 1M nodes / 512^3 voxels)"
+    """One string for every N (the driver checks that the metric is the same across the scaling runs): weak scaling
+    keeps one S4a region — 10^6 nodes in 512^3 voxels — per GPU; config.workload spells out the scene of the run."""
+    return "collision-checked edges/s (connectNodes graph build, 1M nodes / 512^3 voxels per GPU)"
 
 
 # stdout must carry exactly ONE line, the JSON result: file descriptor 1 is pointed at stderr for the
@@ -481,6 +480,113 @@ def gpu_visibility_leg(eng, torch, ext_stream, occ, known, key_min, dims, K, flu
     return vis
 
 
+S5 = {"n_vox": 1024, "res": 0.15, "lattice": 216, "spacing": 0.7, "radius": 1.05, "np": 5_000_000, "nv": 262_144}
+
+
+def s5_leg(torch, dist, local_rank, rank, world, steps=3):
+    """BASELINE configs[4], STRONG scaling of one fixed scene over the ranks of this run: 1024^3 voxels
+    @0.15 m, 216^3 = 10 077 696 lattice nodes @0.7 m, R 1.05 (100 rays per pair), 5*10^6 model points.
+    connect: rows cut by work (sspp_gpu_balanced_cuts), whole CSR assembled on every rank (peer push).
+    visibility: viewpoints cut in equal blocks, (view_ptr, point_idx) assembled on every rank the same way.
+    The one-GPU time of the same scene is measured in the same run (every rank runs the whole scene alone).
+    Times: wall clock between a barrier + device synchronisation on both sides, max over the ranks."""
+    from sspp_b200 import scenes, sharded
+    from sspp_b200.engine import Engine
+    dev = torch.device("cuda", local_rank)
+    key_min, dims, occ, known = scenes.synthetic_map(n_vox=S5["n_vox"], res=S5["res"], seed=42)
+    nodes = scenes.lattice_nodes(S5["lattice"], S5["spacing"])
+    n = len(nodes)
+    e = Engine(local_rank)
+    e.map_create(S5["res"], key_min, dims, True)
+    e.map_upload_dense(occ, known)
+    e.set_nodes(nodes)
+
+    def timed(fn, reps):
+        out = []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            dist.barrier()
+            t0 = time.perf_counter()
+            r = fn()
+            torch.cuda.synchronize()
+            e.synchronize()
+            out.append(time.perf_counter() - t0)
+        t = torch.tensor([float(np.mean(out[1:] if len(out) > 1 else out))], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]) * 1e3, r
+
+    # ---- connect
+    one_ms, st1 = timed(lambda: e.connect(radius=S5["radius"], box=BOX), steps + 1)
+    cuts = e.balanced_cuts(world, 8, radius=S5["radius"], box=BOX)
+    asm = sharded.PeerCsrAssembler(e, n, dev, cuts=cuts)
+
+    def sharded_connect():
+        st = e.connect(radius=S5["radius"], box=BOX, rows=asm.rows)
+        asm.assemble(st)
+        return st
+    sh_ms, stg = timed(sharded_connect, steps + 2)
+    dev_ms = torch.tensor([float(e.connect_timings()[0])], dtype=torch.float64, device=dev)
+    allms = torch.empty(world, dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(allms, dev_ms)
+    # equal-count cuts for comparison (what balancing buys)
+    asm_eq = sharded.PeerCsrAssembler(e, n, dev)
+
+    def sharded_connect_eq():
+        st = e.connect(radius=S5["radius"], box=BOX, rows=asm_eq.rows)
+        asm_eq.assemble(st)
+        return st
+    eq_ms, _ = timed(sharded_connect_eq, steps + 2)
+    dev_ms_eq = torch.tensor([float(e.connect_timings()[0])], dtype=torch.float64, device=dev)
+    allms_eq = torch.empty(world, dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(allms_eq, dev_ms_eq)
+    same = True
+    if rank == 0:  # the assembled graph against the one-GPU graph of the same scene
+        sf = e.connect(radius=S5["radius"], box=BOX)
+        rpf, colf = e.connect_fetch(sf)
+        rp, col = asm_eq.out_rp.cpu().numpy(), asm_eq.out_col.cpu().numpy()
+        same = bool(np.array_equal(rp, rpf) and np.array_equal(col[: sf.edges], colf))
+    asm.close()
+    asm_eq.close()
+    tested = float(st1.tested_pairs)
+    out = {"workload": "S5 (BASELINE configs[4]): 1024^3 voxels @0.15 m (seed 42), 216^3 = %d lattice nodes @0.7 m, R 1.05, box "
+                       "(0.5,0.5,0.3) -> %d rays/pair; %d model points; strong scaling over %d GPUs, map / nodes / points replicated"
+                       % (n, st1.rays_per_pair, S5["np"], world),
+           "connect": {"tested_pairs": int(tested), "edges": int(st1.edges), "one_gpu_ms": one_ms, "n_gpu_ms": sh_ms,
+                       "speedup": one_ms / sh_ms, "edges_per_s_one_gpu": tested / (one_ms * 1e-3), "edges_per_s_n_gpu": tested / (sh_ms * 1e-3),
+                       "row_cuts": "work-balanced (sspp_gpu_balanced_cuts, weight 8 for rows that need the edge test)",
+                       "cuts": [int(c) for c in cuts], "connect_device_ms_per_rank": [round(float(x), 3) for x in allms.cpu()],
+                       "equal_row_cuts": {"n_gpu_ms": eq_ms, "connect_device_ms_per_rank": [round(float(x), 3) for x in allms_eq.cpu()]},
+                       "csr_equals_one_gpu": same,
+                       "includes": "binning, count, edge test, CSR, exchange (counts all-gather + peer push + closing all-reduce)"}}
+    # ---- visibility
+    pts = scenes.surface_points(occ, known, key_min, dims, S5["res"], S5["np"], seed=45)
+    poses = scenes.viewpoints_near(pts, S5["nv"], standoff=VIS["standoff"], seed=46)
+    fr = (VIS["hfov"], VIS["vfov"], VIS["near"], VIS["far"])
+    e.set_model_points(pts)
+    v1_ms, vs1 = timed(lambda: e.visibility(poses, *fr, fetch=False), steps + 2)
+    vasm = sharded.PeerCsrAssembler(e, len(poses), dev, kind="visibility")
+    mine = np.ascontiguousarray(poses[vasm.rows[0]:vasm.rows[1]])
+
+    def sharded_vis():
+        vs = e.visibility(mine, *fr, fetch=False)
+        vasm.assemble(vs)
+        return vs
+    vn_ms, vsn = timed(sharded_vis, steps + 2)
+    vsame = True
+    if rank == 0:
+        _, vpf, idxf = e.visibility(poses, *fr)
+        vsame = bool(np.array_equal(vasm.out_rp.cpu().numpy(), vpf) and np.array_equal(vasm.out_col.cpu().numpy()[: len(idxf)], idxf))
+    vasm.close()
+    out["visibility"] = {"viewpoints": int(S5["nv"]), "model_points": int(S5["np"]), "rays": int(vs1.rays), "visible_pairs": int(vs1.visible_pairs),
+                         "one_gpu_ms": v1_ms, "n_gpu_ms": vn_ms, "speedup": v1_ms / vn_ms, "rays_per_s_one_gpu": vs1.rays / (v1_ms * 1e-3),
+                         "rays_per_s_n_gpu": vs1.rays / (vn_ms * 1e-3), "result_equals_one_gpu": vsame,
+                         "note": "%d viewpoints per pass (3 m from random surface points); a pass over all 10^7 way-points of the "
+                                 "scene is %d such batches" % (S5["nv"], -(-n // S5["nv"])),
+                         "includes": "pose upload, frustum gather, occlusion rays, compaction + sort, exchange of (view_ptr, point_idx)"}
+    e.close()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # GPU arm
 # ------------------------------------------------------------------------------------------------
@@ -492,6 +598,7 @@ def main():
     ap.add_argument("--impl", default="sspp_b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-visibility", action="store_true")
+    ap.add_argument("--no-s5", action="store_true", help="N>1: skip the strong-scaling object of BASELINE configs[4] (S5)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = one S4a region per GPU in one map / one search space (default); strong = S4a split over the GPUs")
     ap.add_argument("--assembler", default="peer", choices=["streamed", "peer", "nccl"],
@@ -723,10 +830,34 @@ def main():
         rpb, colb = eng.connect_fetch(sb)
         assert np.array_equal(rpa, rpb) and np.array_equal(cola, colb), "pyramid skip changed the graph"
 
+    # ---- N > 1: strong scaling of the fixed S5 scene (BASELINE configs[4]); every rank takes part, rank 0 reports
+    s5, s5_hung = None, False
+    if distributed and not args.no_s5:
+        # in a thread with a deadline: whatever happens in there (a rank failing inside a collective leaves the others
+        # waiting), the headline line above is still printed and every rank still exits
+        box = {}
+
+        def run_s5():
+            try:
+                torch.cuda.set_device(local_rank)
+                box["s5"] = s5_leg(torch, dist, local_rank, rank, world)
+            except Exception as e:
+                box["s5"] = {"error": repr(e)}
+        th = threading.Thread(target=run_s5, daemon=True)
+        th.start()
+        th.join(timeout=float(os.environ.get("SSPP_S5_DEADLINE_S", "420")))
+        s5 = box.get("s5", {"error": "did not finish within the deadline"})
+        # no collective after this point: a rank that failed or timed out in there must not leave the others waiting
+        s5_hung = True
+
     if rank != 0:
-        if distributed:
+        if distributed and not s5_hung:
             dist.barrier()
             dist.destroy_process_group()
+        if s5_hung:
+            sys.stdout.flush()
+            sys.stderr.flush()
+            os._exit(0)
         return
 
     # ---- roofline of the dominant kernel (k_edges), per launch, this rank's share
@@ -808,8 +939,10 @@ def main():
                     "ms_per_step": float(e2e_tot[0]) * 1e3 / K},
             "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
             "parity_on_bench_scene": parity, "visibility": vis,
-            "tested_pairs_per_step": tested_all, "edges_per_step": edges_all, "multi_gpu": multi}
+            "tested_pairs_per_step": tested_all, "edges_per_step": edges_all, "multi_gpu": multi, "s5": s5}
     emit(line)
+    if s5_hung:
+        os._exit(0)
     if distributed:
         dist.barrier()
         dist.destroy_process_group()

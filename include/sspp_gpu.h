@@ -122,6 +122,9 @@ typedef struct sspp_connect_params {
   int32_t use_pyramid;   /* 1: rows whose whole reach is free in the coarse pyramid skip the DDA (same result) */
   int32_t count_steps;   /* 1: also count the voxel lookups the reference semantics require (instrumented run:
                             disables the pyramid skip; for the byte model of the roofline, not for timing) */
+  int32_t count_only;    /* 1: stop after the neighbour count (stats: rows, in_radius_pairs, tested_pairs, pyramid_rows);
+                            no edge test, no CSR — what sspp_gpu_balanced_cuts runs */
+  int32_t reserved;      /* 0 */
 } sspp_connect_params;
 
 typedef struct sspp_connect_stats {
@@ -131,8 +134,7 @@ typedef struct sspp_connect_stats {
   int64_t tested_pairs;    /* of those, pairs at different positions = pairs handed to the collision test (pathplanner.cpp:547) */
   int64_t rays_per_pair;   /* size of the ray lattice nx*ny*nz */
   int64_t pyramid_rows;    /* rows answered by the pyramid */
-  int64_t tile_rows;       /* rows accepted whole because the key box spanned by ALL their pairs holds no blocked voxel
-                              (the field keeps its round-1 name so the struct layout does not change) */
+  int64_t tile_rows;       /* reserved, always 0 (kept so the struct layout does not change) */
   int64_t box_pairs;       /* tested pairs accepted because the key box they sweep is free */
   int64_t lattice_pairs;   /* tested pairs that ran the ray lattice */
   int64_t voxel_steps;     /* with count_steps: lookups up to and including the first non-free voxel of the first
@@ -145,9 +147,9 @@ int sspp_gpu_connect(sspp_gpu_ctx* ctx, const sspp_connect_params* params, sspp_
 int sspp_gpu_connect_fetch(sspp_gpu_ctx* ctx, int64_t* row_ptr, int32_t* col_idx);
 /* Diagnostics for the parity tests (no counterpart in the reference): how each row of the last connect
  * was answered, one byte per row — 0 the row has no in-radius pair; 1 every pair accepted because the
- * row's whole reach is free in the coarse pyramid (or no map is used); 2 every pair accepted because the
- * key box spanned by all of the row's rays holds no blocked voxel; 3 the row was decided pair by pair
- * (start voxels, pair key boxes, ray lattice).  The tests use it to draw oracle checks from every class. */
+ * row's whole reach is free in the coarse pyramid (or no map is used); 2 reserved; 3 the row was decided
+ * pair by pair (start voxels, pair key boxes, ray lattice).  The tests use it to draw oracle checks from
+ * every class. */
 int sspp_gpu_connect_row_classes(sspp_gpu_ctx* ctx, uint8_t* row_class);
 /* Same, into DEVICE buffers of the caller (e.g. the send buffers of an NCCL all-gather). */
 int sspp_gpu_connect_fetch_device(sspp_gpu_ctx* ctx, int64_t* row_ptr_device, int32_t* col_idx_device);
@@ -186,13 +188,18 @@ int sspp_gpu_connect_push_csr(sspp_gpu_ctx* ctx, int world, int rank, const int6
                               const int64_t* row_base_device, int64_t* const* row_ptr_peers, int32_t* const* col_idx_peers,
                               int64_t col_capacity, int64_t* overflow_device);
 /* Multi-GPU, transfer overlapped with the edge test: sspp_gpu_connect, with the edge test and the
- * compaction run in row chunks and every finished chunk copied over NVLink (copy engines, peer
- * pointers from sspp_gpu_peer_buffer_open) into slot [rank] of EVERY rank's block buffers while the
- * next chunk is computed.  Block buffers as sspp_gpu_assemble_csr_blocks reads them: row_ptr blocks of
- * row_stride int64 per rank (relative to the block, entry [rows] = the block's edge count), column
- * blocks of col_stride int32 per rank.  Returns when this rank's copies have landed; after a barrier
- * over the ranks, sspp_gpu_assemble_csr_blocks on the local buffers yields the whole-graph CSR.
- * SSPP_ERR_RANGE (nothing sent) when the block's edges exceed col_stride; stats->edges = size needed.
+ * compaction run in row chunks (sizes 4:3:2:1 above 65 536 rows) and every finished chunk stored through
+ * NVLink peer pointers (sspp_gpu_peer_buffer_open) into slot [rank] of EVERY rank's block buffers by a small
+ * push kernel on a second, high-priority stream while the next chunk's edge kernel runs (which leaves half
+ * the SMs one CTA slot free for it).  The push kernel takes the chunk's edge range from device memory, so the
+ * host queues the whole pass without waiting for anything in between.  Block buffers as
+ * sspp_gpu_assemble_csr_blocks reads them: row_ptr blocks of row_stride int64 per rank (relative to the
+ * block, entry [rows] = the block's edge count), column blocks of col_stride int32 per rank (col_stride a
+ * multiple of 4, buffers 16-byte aligned).  Returns when this rank's stores have been issued and retired;
+ * after a barrier over the ranks, sspp_gpu_assemble_csr_blocks on the local buffers yields the whole-graph CSR.
+ * SSPP_ERR_RANGE when the block's edges exceed col_stride (stats->edges = size needed): the chunks that
+ * still fitted HAVE been sent, so the peers' slots then hold a partial block — the caller must not pack
+ * them, but agree on larger slots with its peers (a MAX all-reduce of stats->edges) and run the pass again.
  * No counterpart in the reference (one process). */
 typedef struct sspp_peer_blocks {
   int32_t world, rank;
@@ -202,6 +209,14 @@ typedef struct sspp_peer_blocks {
 } sspp_peer_blocks;
 int sspp_gpu_connect_to_peers(sspp_gpu_ctx* ctx, const sspp_connect_params* params, const sspp_peer_blocks* peers,
                               sspp_connect_stats* stats);
+/* Candidate-balanced row partition (SURVEY.md §8 e "Partitioning"; the outer loop being split is
+ * src/pathplanner.cpp:536): `world` + 1 cut points over the list indices, cuts[0] = 0, cuts[world] = n, such that
+ * every block [cuts[g], cuts[g+1]) carries about the same WORK rather than the same number of rows.  Work of a
+ * row = its in-radius pairs, times `work_row_weight` when the row has to go through the edge test (its reach is
+ * not free in the coarse pyramid; 8 is the measured cost ratio on the S4 scenes).  Runs the neighbour count over
+ * all rows (no edge test), so it is a set-up step per node set, not part of a connect pass; every rank that holds
+ * the same nodes and map computes the same cuts, no message needed. */
+int sspp_gpu_balanced_cuts(sspp_gpu_ctx* ctx, const sspp_connect_params* params, int world, int work_row_weight, int64_t* cuts);
 /* Device addresses of the last CSR (valid until the next connect on this context). */
 int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_device, const int32_t** col_idx_device);
 
@@ -295,6 +310,16 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* sensor_poses, int64_t n
                         sspp_visibility_stats* stats);
 /* view_ptr: nv+1 entries; point_idx: visible_pairs entries, ascending within a viewpoint. */
 int sspp_gpu_visibility_fetch(sspp_gpu_ctx* ctx, int64_t* view_ptr, int32_t* point_idx);
+/* Multi-GPU visibility (the hook runs per way-point — include/sspp/heuristic_interface.h:40, src/astar.cpp:318 —
+ * and is independent per viewpoint, so it shards like the rows of connectNodes; SURVEY.md §8 e): every rank
+ * runs sspp_gpu_visibility on a contiguous block of the viewpoints, with the model points and the map
+ * replicated, and this call writes the block — view_ptr rebased by the visible-pair counts of the lower
+ * ranks — into the whole-result buffers of all `world` ranks through NVLink peer memory, exactly as
+ * sspp_gpu_connect_push_csr does for the adjacency (same arguments, same overflow rule, same barrier
+ * contract).  The assembled (view_ptr, point_idx) is byte-identical to one visibility call over all viewpoints. */
+int sspp_gpu_visibility_push(sspp_gpu_ctx* ctx, int world, int rank, const int64_t* pair_counts_device,
+                             const int64_t* view_base_device, int64_t* const* view_ptr_peers, int32_t* const* point_idx_peers,
+                             int64_t idx_capacity, int64_t* overflow_device);
 /* Milliseconds the kernels of the last sspp_gpu_visibility spent on the stream (CUDA events):
  * [0] total, [1] point binning (0 when the cached binning was reused), [2] viewpoint set-up + frustum
  * gather (count and fill), [3] the occlusion rays (k_view_rays), [4] compaction + per-viewpoint sort. */

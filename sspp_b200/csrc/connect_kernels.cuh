@@ -103,17 +103,6 @@ __global__ void k_cell_sort(const int* __restrict__ cell_start, int ncells, Node
   }
 }
 
-// n_sorted_ptr: how many nodes were binned (device side); positions beyond it hold nothing
-__global__ void k_row_flags(const NodeRec* __restrict__ sn, int64_t n, const int* __restrict__ n_sorted_ptr, int64_t lo,
-                            int64_t hi, int* __restrict__ flag) {
-  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < n) flag[s] = (s < *n_sorted_ptr && sn[s].idx >= lo && sn[s].idx < hi) ? 1 : 0;
-}
-__global__ void k_row_scatter(const int* __restrict__ flag, const int* __restrict__ pos, int64_t n, int* __restrict__ rows) {
-  int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < n && flag[s]) rows[pos[s]] = (int)s;
-}
-
 // pair classification shared by count and gather: 0 = not connected, 1 = goes to the collision test,
 // 2 = same position (connected without a test).  S = candidate, T = source row ("temp").
 // The reference tests sqrt(d2) <= radius (Dist, include/sspp/utils.h:356-359).  sqrt is monotone and
@@ -164,9 +153,13 @@ struct ConnectArgs {
   NodeGrid g;
   const int* cell_start;
   const NodeRec* sn;  // binned nodes, cell order
-  const int* rows;  // sorted positions of the rows to process, or NULL = all
+  // Rows to process: list indices [lo, hi).  The row kernels run over the sorted positions [0, nscan) and skip
+  // what is not a row of this shard: positions beyond the binned count (*n_sorted: a shard bins only the nodes
+  // its rows can reach) and nodes outside [lo, hi).  nrows = hi - lo sizes every per-row array.
+  const int* n_sorted;  // device: number of binned nodes, or NULL = nscan
+  int nscan;
   int nrows;
-  int64_t lo;  // first list index of this shard
+  int64_t lo, hi;
   double r2max;  // largest d2 with sqrt(d2) <= radius
   int mode;
   int use_map;
@@ -185,7 +178,7 @@ struct ConnectArgs {
   int nchunks;
   int chunk_lo[SSPP_MAX_CHUNKS + 1];
   // Diagnostics (sspp_gpu_connect_row_classes): how every row was answered — 0 no pair, 1 reach free in the
-  // coarse pyramid (k_count), 2 the key box of all its pairs holds no blocked voxel (k_edges), 3 pair by pair
+  // coarse pyramid (k_count), 3 pair by pair in k_edges (2 is reserved)
   uint8_t* row_class;
 };
 
@@ -209,8 +202,7 @@ __device__ __forceinline__ bool pairs_unusable(const ConnectArgs& a, const long 
 
 // counters: [0] in-radius pairs, [1] tested pairs, [2] pyramid rows, [3] voxel steps (instrumented),
 //           [4] next work row (edge kernel's ticket), [5] pairs accepted by their key box,
-//           [6] pairs that ran the ray lattice, [7] rows accepted by the key box of all their pairs,
-//           [8] rows that overflowed their slot,
+//           [6] pairs that ran the ray lattice, [8] rows that overflowed their slot,
 //           [16 + c] work rows of chunk c, [32 + c] next work row of chunk c (edge kernel's ticket)
 //
 // One thread per source row walks the 27 neighbouring cells (9 contiguous ranges of the cell-sorted
@@ -228,9 +220,11 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
   unsigned long long inr = 0, tested = 0, pyr = 0;
   bool is_work = false;
   int chunk = 0;
-  if (t < a.nrows) {
-    int s = a.rows ? a.rows[t] : t;
-    const NodeRec me = load_node(a.sn + s);
+  NodeRec me;
+  me.idx = -1;
+  if (t < a.nscan && (!a.n_sorted || t < *a.n_sorted)) me = load_node(a.sn + t);
+  if (me.idx >= a.lo && me.idx < a.hi) {
+    const int s = t;
     const double px = me.x, py = me.y, pz = me.z;
     int r = (int)(me.idx - a.lo);
     int cx = grid_cell_axis(a.g, px, 0), cy = grid_cell_axis(a.g, py, 1), cz = grid_cell_axis(a.g, pz, 2);
@@ -445,75 +439,13 @@ __device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, doubl
   return true;
 }
 
-// Blocked voxels of a key box (absolute keys, inclusive; at most 32 voxels per axis), looked at by the whole
-// warp at once: the y-runs of the box are spread over the lanes (y fastest in memory), every word is read
-// once.  Besides "any blocked voxel" the scan leaves the three axis PROJECTIONS of the blocked voxels,
-// relative to the box's low corner: bit i of xp is set iff some blocked voxel of the box has x = lox + i
-// (yp, zp likewise).  A smaller box inside this one whose x-range misses xp — or whose y-range misses yp,
-// or z-range zp — holds no blocked voxel: an implication, never an estimate.
-struct BoxProj {
-  int lo[3], hi[3];
-  unsigned xp, yp, zp;
-  bool valid;  // false: the box left the window / was too wide — nothing may be concluded from the projections
-};
-__device__ __forceinline__ unsigned range_mask(int b0, int b1) {  // bits b0..b1, 0 <= b0 <= b1 <= 31
-  return (0xffffffffu >> (31 - b1)) & (0xffffffffu << b0);
-}
-__device__ __forceinline__ BoxProj warp_box_scan(const DeviceMap& m, int lane, int lox, int hix, int loy, int hiy, int loz, int hiz) {
-  BoxProj P;
-  P.lo[0] = lox; P.lo[1] = loy; P.lo[2] = loz;
-  P.hi[0] = hix; P.hi[1] = hiy; P.hi[2] = hiz;
-  P.xp = P.yp = P.zp = 0xffffffffu;
-  P.valid = false;
-  const int x0 = lox - m.kmin[0], x1 = hix - m.kmin[0];
-  const int y0 = loy - m.kmin[1], y1 = hiy - m.kmin[1];
-  const int z0 = loz - m.kmin[2], z1 = hiz - m.kmin[2];
-  if (x0 < 0 || y0 < 0 || z0 < 0 || x1 >= m.dims[0] || y1 >= m.dims[1] || z1 >= m.dims[2] || x0 > x1 || y0 > y1 || z0 > z1 ||
-      x1 - x0 > 31 || y1 - y0 > 31 || z1 - z0 > 31)
-    return P;
-  const int ny = y1 - y0 + 1;
-  // lanes = (z sub-row, y): yb = ny rounded up to a power of two, 32 / yb z-slices per iteration
-  const int sh = ny <= 1 ? 0 : 32 - __clz(ny - 1);
-  const int ly = lane & ((1 << sh) - 1), lz = lane >> sh, zstep = 32 >> sh;
-  const int w0 = x0 >> 5, w1 = x1 >> 5;
-  const unsigned m0 = (w0 == w1) ? range_mask(x0 & 31, x1 & 31) : (0xffffffffu << (x0 & 31));
-  const unsigned m1 = (w0 == w1) ? 0u : (0xffffffffu >> (31 - (x1 & 31)));
-  unsigned a0 = 0, a1 = 0, zb = 0;
-  if (ly < ny) {
-    const uint32_t* base0 = m.blocked + map_word(m, w0, y0 + ly, 0);
-    const size_t wstride = (size_t)m.dims[2] * m.dims[1];
-    for (int z = z0 + lz; z <= z1; z += zstep) {
-      unsigned b0 = __ldg(base0 + (size_t)z * m.dims[1]) & m0;
-      unsigned b1 = m1 ? (__ldg(base0 + wstride + (size_t)z * m.dims[1]) & m1) : 0u;
-      a0 |= b0;
-      a1 |= b1;
-      zb |= (b0 | b1) ? (1u << (z - z0)) : 0u;
-    }
-  }
-  const unsigned long long both = (((unsigned long long)a1 << 32) | a0) >> (x0 & 31);
-  P.xp = __reduce_or_sync(0xffffffffu, (unsigned)both);
-  P.yp = __reduce_or_sync(0xffffffffu, (a0 | a1) ? (1u << ly) : 0u);
-  P.zp = __reduce_or_sync(0xffffffffu, zb);
-  P.valid = true;
-  return P;
-}
-// does the key box [lo, hi] provably hold no blocked voxel?  Only a box INSIDE the scanned one can be judged
-// (outside it the projections know nothing).
-__device__ __forceinline__ bool proj_free(const BoxProj& P, int lox, int hix, int loy, int hiy, int loz, int hiz) {
-  if (!P.valid || lox < P.lo[0] || hix > P.hi[0] || loy < P.lo[1] || hiy > P.hi[1] || loz < P.lo[2] || hiz > P.hi[2] || lox > hix ||
-      loy > hiy || loz > hiz)
-    return false;
-  return !(P.xp & range_mask(lox - P.lo[0], hix - P.lo[0])) || !(P.yp & range_mask(loy - P.lo[1], hiy - P.lo[1])) ||
-         !(P.zp & range_mask(loz - P.lo[2], hiz - P.lo[2]));
-}
-
 // Cheap verdict on one ray before any DDA arithmetic: RAY_FREE / RAY_BLOCKED are final, RAY_WALK
 // means the exact walk has to decide.  `fast` enables the key-box shortcut of line_status_fast.
+// okey: the ray's origin key with its start voxel already known to be free (the row-level start stage
+// computed both; -1 = origin outside the key space), or NULL = derive them here.
 enum { RAY_FREE = 0, RAY_BLOCKED = 1, RAY_WALK = 2 };
-// okey: the ray's origin key when the caller already has it (NULL: computed here from the origin); P: the
-// projections of the blocked voxels of a box that holds the ray's key box, or an invalid one.
 __device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float ox, float oy, float oz, float ex, float ey,
-                                            float ez, const int* okey, const BoxProj& P) {
+                                            float ez, const int* okey) {
   int kx, ky, kz, ekx, eky, ekz;
   if (okey) {
     kx = okey[0]; ky = okey[1]; kz = okey[2];
@@ -528,10 +460,11 @@ __device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float
     const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
     const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
     const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
-    if (proj_free(P, lox, hix, loy, hiy, loz, hiz)) return RAY_FREE;
     if (!box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) return RAY_FREE;
   }
-  if (map_blocked(m, kx, ky, kz)) return RAY_BLOCKED;  // the start voxel is the first one the walk tests
+  // the start voxel is the first one the walk tests; with okey it is known to be free (a pair whose ray q
+  // starts in a blocked voxel and is not empty never reaches the ray stage)
+  if (!okey && map_blocked(m, kx, ky, kz)) return RAY_BLOCKED;
   return RAY_WALK;
 }
 
@@ -624,9 +557,11 @@ __global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long l
   if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * EDGE_WARPS + warp;
-  if (t >= a.nrows) return;
-  const int s = a.rows ? a.rows[t] : t;
-  const int r = (int)(a.sn[s].idx - a.lo);
+  if (t >= a.nscan || (a.n_sorted && t >= *a.n_sorted)) return;
+  const int s = t;
+  const long long idx = a.sn[s].idx;
+  if (idx < a.lo || idx >= a.hi) return;
+  const int r = (int)(idx - a.lo);
   long long off;
   int n;
   row_span(a, cand_off, r, off, n);
@@ -650,7 +585,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
                                          const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
                                          int* __restrict__ deg, unsigned long long* counters) {
   const RayLattice& lat = sm.lat;
-  const int s = a.rows ? a.rows[t] : t;
+  const int s = t;  // work lists hold sorted positions
   const NodeRec me = load_node(a.sn + s);
   const int r = (int)(me.idx - a.lo);
   long long off;
@@ -660,16 +595,29 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
 
   const double px = me.x, py = me.y, pz = me.z;
   const int R = lat.rays;
-  const bool fast = !COUNT && a.use_pyramid != 0;
-  // Row-level verdicts, computed when the first pair needs them: every ray starts at p + offset whatever
-  // the pair, and the start voxel is the first one a walk tests.  A ray whose start voxel is blocked
-  // therefore rejects every pair of this row for which that ray is not empty (its end key differs from
-  // its start key).  The origin keys are kept for the per-ray checks (-1: outside the key space).
+  const bool fast = a.use_pyramid != 0;
+  // Row-level verdicts: every ray starts at p + offset whatever the pair, and the start voxel is the
+  // first one a walk tests.  A ray whose start voxel is blocked therefore rejects every pair of this
+  // row for which that ray is not empty (its end key differs from its start key).
   unsigned startmask = 0;
-  bool start_done = false;
+  if (!COUNT && fast && R <= 32) {
+    bool blk = false;
+    if (lane < R) {
+      double ox, oy, oz;
+      ray_offset(sm, lane, ox, oy, oz);
+      int kx = -1, ky = -1, kz = -1;
+      if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
+          coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz))
+        blk = map_blocked(m, kx, ky, kz) != 0;
+      else
+        kx = -1;
+      sm.okey[warp][lane][0] = kx; sm.okey[warp][lane][1] = ky; sm.okey[warp][lane][2] = kz;
+    }
+    startmask = __ballot_sync(0xffffffffu, blk);
+    __syncwarp();
+  }
   int nacc = 0;
   unsigned n_box = 0, n_lat = 0;
-  bool row_box_free = fast;
   unsigned long long nsteps = 0;
   for (int base = 0; base < n; base += 32) {
     const int nb = min(32, n - base);
@@ -681,65 +629,30 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     if (mine_valid) { const NodeRec o = load_node(a.sn + c.x); qx = o.x; qy = o.y; qz = o.z; }
     bool rejected = false;
     bool needs = mine_valid && !same;
-    // stage 1: the key box all rays of the pair stay in (one lane per pair) ...
-    int lox = 0, hix = 0, loy = 0, hiy = 0, loz = 0, hiz = 0;
-    bool boxed = false;
-    BoxProj P;
-    P.valid = false;
-    if (fast) {
-      boxed = needs && pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
-              pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
-              pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz);
-      // ... and the box that holds all of them, scanned once by the whole warp.  No blocked voxel in it:
-      // every pair of the batch is accepted.  Otherwise the projections of what is blocked decide most pairs
-      // (a pair whose x-, y- or z-range holds no blocked voxel of the batch box is free), and later most rays.
-      if (__any_sync(0xffffffffu, boxed)) {
-        const int big = 1 << 20;
-        const int ulx = __reduce_min_sync(0xffffffffu, boxed ? lox : big), uhx = __reduce_max_sync(0xffffffffu, boxed ? hix : -big);
-        const int uly = __reduce_min_sync(0xffffffffu, boxed ? loy : big), uhy = __reduce_max_sync(0xffffffffu, boxed ? hiy : -big);
-        const int ulz = __reduce_min_sync(0xffffffffu, boxed ? loz : big), uhz = __reduce_max_sync(0xffffffffu, boxed ? hiz : -big);
-        P = warp_box_scan(m, lane, ulx, uhx, uly, uhy, ulz, uhz);
-        if (boxed && proj_free(P, lox, hix, loy, hiy, loz, hiz)) needs = false;
+    // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
+    if (needs && startmask) {
+      for (unsigned mb = startmask; mb; mb &= mb - 1) {
+        const int q = __ffs(mb) - 1;
+        double ox, oy, oz;
+        ray_offset(sm, q, ox, oy, oz);
+        int ekx, eky, ekz;
+        if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
+            coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
+            (ekx != sm.okey[warp][q][0] || eky != sm.okey[warp][q][1] || ekz != sm.okey[warp][q][2])) {
+          needs = false;
+          rejected = true;
+          break;
+        }
       }
     }
-    if (__any_sync(0xffffffffu, needs)) {
-      row_box_free = false;
-      if (fast && R <= 32 && !start_done) {
-        bool blk = false;
-        if (lane < R) {
-          double ox, oy, oz;
-          ray_offset(sm, lane, ox, oy, oz);
-          int kx = -1, ky = -1, kz = -1;
-          if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
-              coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz)) {
-            blk = map_blocked(m, kx, ky, kz) != 0;
-          } else {
-            kx = -1;
-          }
-          sm.okey[warp][lane][0] = kx; sm.okey[warp][lane][1] = ky; sm.okey[warp][lane][2] = kz;
-        }
-        startmask = __ballot_sync(0xffffffffu, blk);
-        start_done = true;
-        __syncwarp();
-      }
-      // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
-      if (needs && startmask) {
-        for (unsigned mb = startmask; mb; mb &= mb - 1) {
-          const int q = __ffs(mb) - 1;
-          double ox, oy, oz;
-          ray_offset(sm, q, ox, oy, oz);
-          int ekx, eky, ekz;
-          if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
-              coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
-              (ekx != sm.okey[warp][q][0] || eky != sm.okey[warp][q][1] || ekz != sm.okey[warp][q][2])) {
-            needs = false;
-            rejected = true;
-            break;
-          }
-        }
-      }
-      // stage 2b: the pair's own key box, word by word (one lane per pair)
-      if (fast && needs && boxed && !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) needs = false;
+    // stage 2b: the pair's key box (one lane per pair)
+    if (!COUNT && fast && needs) {
+      int lox, hix, loy, hiy, loz, hiz;
+      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
+          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
+          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
+          (!box_maybe_blocked_coarse(m, lox, hix, loy, hiy, loz, hiz) || !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)))
+        needs = false;
     }
     unsigned need = __ballot_sync(0xffffffffu, needs);
     unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs && !rejected);  // same-position or box-free pairs
@@ -781,7 +694,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
       __syncwarp();
       const int W = __popc(need) * R;
-      const bool have_okey = start_done;
+      const bool have_okey = !COUNT && fast && R <= 32;  // the start stage above ran for this row
       unsigned blockedmask = 0;
       int qn = 0;
       for (int w0 = 0; w0 < W; w0 += 32) {
@@ -796,7 +709,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
             ray_offset(sm, q, ox, oy, oz);
             const double* f = sm.far_end[warp][k];
             verdict = ray_precheck(m, fast, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
-                                   d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? sm.okey[warp][q] : nullptr, P);
+                                   d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? sm.okey[warp][q] : nullptr);
           }
         }
         blockedmask |= __reduce_or_sync(0xffffffffu, verdict == RAY_BLOCKED ? (1u << k) : 0u);
@@ -823,10 +736,6 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
   }
   if (lane == 0) {
     deg[r] = nacc;
-    if (row_box_free) {
-      a.row_class[r] = 2;
-      atomicAdd(counters + 7, 1ull);
-    }
     if (n_box) atomicAdd(counters + 5, (unsigned long long)n_box);
     if (n_lat) atomicAdd(counters + 6, (unsigned long long)n_lat);
   }
@@ -981,5 +890,72 @@ k_push_csr(PushPeers p, const long long* __restrict__ edge_counts, const long lo
   }
 }
 
+
+// Chunk-wise variant for the exchange that overlaps the edge test (sspp_gpu_connect_to_peers): one finished row
+// chunk of this rank's block — rows [r0, r1) and the edges [chunk_base[c], chunk_base[c + 1]) the chunk scan left
+// on the device — goes into slot [rank] of EVERY rank's block buffers (block-relative row pointers, columns at the
+// same offset as in the local block), by plain stores through NVLink peer pointers.  Everything the kernel needs
+// is in device memory, so the host queues it behind the chunk's compaction without waiting for anything; a few
+// dozen CTAs are enough to keep the links busy, which lets it run beside the next chunk's edge kernel.  A chunk
+// that would end beyond the slot (col_stride) is not sent: the host learns the block's size at the end of the
+// pass and reports it.  `last`: the chunk also carries row_ptr[rows] = the block's edge count.
+__global__ void __launch_bounds__(256)
+k_push_chunk(PushPeers p, const long long* __restrict__ chunk_base, int c, int last, const long long* __restrict__ rp,
+             const int* __restrict__ col, int r0, int r1, long long col_stride) {
+  const long long e0 = chunk_base[c], e1 = chunk_base[c + 1];
+  if (e1 > col_stride) return;
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+  const long long nrp = (long long)(r1 - r0) + (last ? 1 : 0);
+  for (long long i = tid; i < nrp; i += nth) {
+    const long long v = rp[r0 + i];
+    for (int j = 0; j < p.world; ++j) {
+      int k = p.rank + 1 + j;
+      if (k >= p.world) k -= p.world;
+      p.rp[k][r0 + i] = v;
+    }
+  }
+  const long long edges = e1 - e0;
+  long long head = (4 - (e0 & 3)) & 3;  // slots start 16-byte aligned and the offset e0 is the same in all of them
+  if (head > edges) head = edges;
+  const long long nvec = (edges - head) >> 2, tail0 = head + (nvec << 2);
+  for (long long i = tid; i < head + (edges - tail0); i += nth) {
+    const long long e = e0 + (i < head ? i : tail0 + (i - head));
+    const int v = col[e];
+    for (int k = 0; k < p.world; ++k) p.col[k][e] = v;
+  }
+  for (long long q = tid; q < nvec; q += nth) {
+    const long long e = e0 + head + (q << 2);
+    const int4 v = *reinterpret_cast<const int4*>(col + e);
+    for (int j = 0; j < p.world; ++j) {
+      int k = p.rank + 1 + j;
+      if (k >= p.world) k -= p.world;
+      *reinterpret_cast<int4*>(p.col[k] + e) = v;
+    }
+  }
+}
+
+// Row weights for the balanced partition: in-radius pairs, times `heavy` for rows that need the edge test.
+__global__ void k_row_weights(const int* __restrict__ cand_count, const uint8_t* __restrict__ row_free, int use_map, int heavy,
+                              int64_t n, int* __restrict__ w) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const int c = cand_count[r];
+  w[r] = (use_map && !row_free[r]) ? c * heavy : c;
+}
+// cuts[g] = first row whose weight prefix reaches g/world of the total (prefix: n + 1 exclusive sums)
+__global__ void k_find_cuts(const long long* __restrict__ prefix, int64_t n, int world, long long* __restrict__ cuts) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g > world) return;
+  if (g == 0) { cuts[0] = 0; return; }
+  if (g == world) { cuts[world] = n; return; }
+  const long long total = prefix[n];
+  const long long target = (long long)(((__int128)total * g) / world);
+  int64_t lo = 0, hi = n;  // smallest r with prefix[r] >= target
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (prefix[mid] >= target) hi = mid; else lo = mid + 1;
+  }
+  cuts[g] = lo;
+}
 
 }  // namespace

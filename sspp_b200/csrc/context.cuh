@@ -69,7 +69,7 @@ struct sspp_gpu_ctx {
 
   // chunked delivery of the CSR to host buffers (sspp_gpu_connect_nodes_host)
   cudaStream_t copy_stream = nullptr;
-  cudaStream_t peer_stream[SSPP_MAX_PEERS] = {};  // sspp_gpu_connect_to_peers: one copy stream per destination GPU
+  cudaStream_t push_stream = nullptr;  // sspp_gpu_connect_to_peers: the chunk pushes, beside the next chunk's edge kernel
   cudaEvent_t chunk_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   long long* pinned = nullptr;  // small pinned host block the chunk totals land in
   DevBuf chunk_base;

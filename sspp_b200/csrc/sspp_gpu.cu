@@ -131,7 +131,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
   ctx->chunk_base.release();
   for (int c = 0; c < 8; ++c) if (ctx->chunk_ev[c]) cudaEventDestroy(ctx->chunk_ev[c]);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
-  for (int p = 0; p < SSPP_MAX_PEERS; ++p) if (ctx->peer_stream[p]) cudaStreamDestroy(ctx->peer_stream[p]);
+  if (ctx->push_stream) cudaStreamDestroy(ctx->push_stream);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
   for (void* q : ctx->peer_opened) cudaIpcCloseMemHandle(q);
   for (void* q : ctx->peer_created) cudaFree(q);
@@ -604,22 +604,6 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   k_cell_sort<<<ceil_div(ncells, 256), 256, 0, st>>>(ctx->cell_start.as<int>(), (int)ncells, ctx->sx.as<NodeRec>());
   LAUNCHED(ctx);
 
-  // rows of this shard, in cell order
-  const int* rows = nullptr;
-  if (sharded) {
-    CK(ctx->row_flag.reserve((size_t)n * 4));
-    CK(ctx->rows.reserve((size_t)(n + 1) * 4 + (size_t)nrows * 4));
-    int* pos = ctx->rows.as<int>();
-    int* rows_w = pos + (n + 1);
-    k_row_flags<<<ceil_div(n, 256), 256, 0, st>>>(ctx->sx.as<NodeRec>(), n, ctx->cell_start.as<int>() + ncells, lo, hi,
-                                                 ctx->row_flag.as<int>());
-    LAUNCHED(ctx);
-    int rc = scan_exclusive<int>(ctx, ctx->row_flag.as<int>(), n, pos);
-    if (rc) return rc;
-    k_row_scatter<<<ceil_div(n, 256), 256, 0, st>>>(ctx->row_flag.as<int>(), pos, n, rows_w);
-    LAUNCHED(ctx);
-    rows = rows_w;
-  }
   CK(cudaEventRecord(ctx->ev[1], st));
 
   // --- 3. count in-radius pairs per row
@@ -627,9 +611,11 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   a.g = g;
   a.cell_start = ctx->cell_start.as<int>();
   a.sn = ctx->sx.as<NodeRec>();
-  a.rows = rows;
+  a.n_sorted = sharded ? ctx->cell_start.as<int>() + ncells : nullptr;
+  a.nscan = (int)n;
   a.nrows = (int)nrows;
   a.lo = lo;
+  a.hi = hi;
   a.r2max = radius_threshold(prm->radius);
   a.mode = prm->position_mode;
   a.use_map = use_map;
@@ -656,6 +642,14 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   for (int c = 0; c <= SSPP_MAX_CHUNKS; ++c) {
     const int64_t done = (int64_t)c * (2 * K - c + 1) / 2, all = (int64_t)K * (K + 1) / 2;  // sum of (K - j), j < c
     a.chunk_lo[c] = (int)(c >= K ? nrows : (nrows * done) / all);
+  }
+  const bool to_peers = sink && sink->peers;
+  if (to_peers && !ctx->push_stream) {
+    // the chunk pushes run beside the next chunk's edge kernel: highest priority, so that their few CTAs are
+    // placed as soon as an SM has room
+    int lo_prio = 0, hi_prio = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+    CK(cudaStreamCreateWithPriority(&ctx->push_stream, cudaStreamNonBlocking, hi_prio));
   }
   if (chunked) {
     if (!ctx->copy_stream) CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
@@ -689,7 +683,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     if (a.slot && (double)nrows * a.slot > 3.0e9) a.slot = 0;  // slots beyond ~36 GB of pair buffers: scan instead
     if (a.slot) CK(reserve_pairs((long long)nrows * a.slot));
   }
-  k_count<false><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
+  k_count<false><<<ceil_div(n, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
                                                       ctx->counters.as<unsigned long long>(), nullptr,
                                                       a.slot ? ctx->candA.as<int2>() : nullptr, ctx->work_rows.as<int>(),
                                                       ctx->deg.as<int>(), 0);
@@ -699,6 +693,18 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     if (rc) return rc;
   }
   CK(cudaEventRecord(ctx->ev[2], st));
+  if (prm->count_only) {
+    unsigned long long hc3[3];
+    CK(cudaMemcpyAsync(hc3, ctx->counters.p, sizeof(hc3), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (stats) {
+      stats->rows = nrows;
+      stats->in_radius_pairs = (int64_t)hc3[0];
+      stats->tested_pairs = (int64_t)hc3[1];
+      stats->pyramid_rows = (int64_t)hc3[2];
+    }
+    return SSPP_OK;
+  }
 
   // --- 4/5. edge test and CSR.  The pair buffers keep their size from call to call; the kernels
   // refuse to run when the pairs do not fit (a slot overflowed / the scanned total exceeds the
@@ -720,10 +726,10 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   for (int attempt = 0;; ++attempt) {
     const long long cap = pair_capacity();
     if (!a.slot) {
-      k_count<true><<<ceil_div(nrows, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
+      k_count<true><<<ceil_div(n, 256), 256, 0, st>>>(a, ctx->map, nullptr, nullptr, nullptr, ctx->cand_off.as<long long>(),
                                                          ctx->candA.as<int2>(), nullptr, nullptr, cap);
       LAUNCHED(ctx);
-      k_rows_accept<<<ceil_div(nrows, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
+      k_rows_accept<<<ceil_div(n, EDGE_WARPS), EDGE_WARPS * 32, 0, st>>>(a, ctx->cand_off.as<long long>(),
                                                                           ctx->row_free.as<uint8_t>(), ctx->candA.as<int2>(),
                                                                           ctx->candB.as<int2>(), ctx->acc.as<int>(),
                                                                           ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(),
@@ -742,22 +748,6 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       const long long e0 = pin[c], e1 = pin[c + 1];
       if (e1 > sink->col_capacity) { range_fail = true; return SSPP_OK; }
       const int r0 = a.chunk_lo[c], r1 = a.chunk_lo[c + 1];
-      if (sink->peers) {
-        const sspp_peer_blocks* pb = sink->peers;
-        const bool last = (c == K - 1);  // the last chunk also carries row_ptr[rows] = the block's edge count
-        for (int j = 0; j < pb->world; ++j) {
-          // one stream per destination, so that the copies to different GPUs run on different copy engines
-          // side by side; start with the right-hand neighbour, finish with the own slot
-          const int p = (pb->rank + 1 + j) % pb->world;
-          if (!ctx->peer_stream[p]) CK(cudaStreamCreateWithFlags(&ctx->peer_stream[p], cudaStreamNonBlocking));
-          if (e1 > e0)
-            CK(cudaMemcpyAsync(pb->col_blocks[p] + (size_t)pb->rank * pb->col_stride + e0, ctx->col_idx.as<int>() + e0,
-                               (size_t)(e1 - e0) * 4, cudaMemcpyDefault, ctx->peer_stream[p]));
-          CK(cudaMemcpyAsync(pb->row_ptr_blocks[p] + (size_t)pb->rank * pb->row_stride + r0, ctx->row_ptr.as<long long>() + r0,
-                             (size_t)(r1 - r0 + (last ? 1 : 0)) * 8, cudaMemcpyDefault, ctx->peer_stream[p]));
-        }
-        return SSPP_OK;
-      }
       if (e1 > e0)
         CK(cudaMemcpyAsync(sink->col_idx + e0, ctx->col_idx.as<int>() + e0, (size_t)(e1 - e0) * 4, cudaMemcpyDeviceToHost,
                            ctx->copy_stream));
@@ -768,7 +758,14 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     if (chunked) pin[0] = 0;
     for (int c = 0; c < K; ++c) {
       if (use_map) {
-        const int blocks = ctx->sm_count * EDGE_MIN_BLOCKS;
+        // exchange overlapped with the edge test: half the SMs keep one CTA slot free for the push kernel of the
+        // chunk before (SSPP_PUSH_ROOM = CTAs left out)
+        int room = 0;
+        if (to_peers && K > 1) {
+          room = ctx->sm_count / 2;
+          if (const char* env = getenv("SSPP_PUSH_ROOM")) room = std::max(0, atoi(env));
+        }
+        const int blocks = std::max(ctx->sm_count, ctx->sm_count * EDGE_MIN_BLOCKS - room);
         if (count_steps)
           k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
                                                             ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
@@ -799,7 +796,27 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
             cap, r0, r1);
         LAUNCHED(ctx);
       }
-      if (chunked) {
+      if (to_peers) {
+        // device-driven: the push of chunk c is queued behind its compaction and reads the chunk's edge range from
+        // chunk_base in device memory; the host waits for nothing between the chunks
+        const sspp_peer_blocks* pb = sink->peers;
+        PushPeers pp;
+        pp.world = pb->world;
+        pp.rank = pb->rank;
+        for (int k = 0; k < SSPP_MAX_PEERS; ++k) { pp.rp[k] = nullptr; pp.col[k] = nullptr; }
+        for (int k = 0; k < pb->world; ++k) {
+          pp.rp[k] = (long long*)pb->row_ptr_blocks[k] + (size_t)pb->rank * pb->row_stride;
+          pp.col[k] = pb->col_blocks[k] + (size_t)pb->rank * pb->col_stride;
+        }
+        CK(cudaEventRecord(ctx->chunk_ev[c], st));
+        CK(cudaStreamWaitEvent(ctx->push_stream, ctx->chunk_ev[c], 0));
+        int pblocks = ctx->sm_count / 2;
+        if (const char* env = getenv("SSPP_PUSH_BLOCKS")) pblocks = std::max(1, atoi(env));
+        k_push_chunk<<<pblocks, 256, 0, ctx->push_stream>>>(pp, ctx->chunk_base.as<long long>(), c, c == K - 1 ? 1 : 0,
+                                                            ctx->row_ptr.as<long long>(), ctx->col_idx.as<int>(), r0, r1,
+                                                            (long long)pb->col_stride);
+        LAUNCHED(ctx);
+      } else if (chunked) {
         CK(cudaMemcpyAsync((void*)(pin + c + 1), ctx->chunk_base.as<long long>() + c + 1, 8, cudaMemcpyDeviceToHost, st));
         if (c == 0) CK(cudaMemcpyAsync((void*)(pin + 16), ctx->counters.p, 9 * 8, cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(ctx->chunk_ev[c], st));
@@ -810,7 +827,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       }
     }
     CK(cudaEventRecord(ctx->ev[4], st));
-    if (chunked) {
+    if (chunked && !to_peers) {
       pin[0] = 0;
       int rc = drain(K - 1);
       if (rc) return rc;
@@ -818,14 +835,18 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hc, ctx->counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
-    if (chunked) {
+    if (to_peers) {
+      CK(cudaStreamSynchronize(ctx->push_stream));  // this rank's stores have been issued and retired
+      const bool usable = a.slot ? (hc[8] == 0) : ((long long)hc[0] <= cap);
+      if (usable) {
+        if (E > sink->peers->col_stride) range_error = true;  // the chunks beyond the slot were not sent
+        else sink->delivered = true;
+      }
+    } else if (chunked) {
       CK(cudaStreamSynchronize(ctx->copy_stream));
-      if (sink->peers)
-        for (int p = 0; p < sink->peers->world; ++p)
-          if (ctx->peer_stream[p]) CK(cudaStreamSynchronize(ctx->peer_stream[p]));
       if (range_fail) range_error = true;  // reported below, once the resident result is registered (connect_fetch still works)
       if (!copies_off && !range_fail) {
-        if (!sink->peers) sink->row_ptr[nrows] = E;
+        sink->row_ptr[nrows] = E;
         sink->delivered = true;
       }
     }
@@ -850,7 +871,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     stats->tested_pairs = (int64_t)hc[1];
     stats->pyramid_rows = (int64_t)hc[2];
     stats->voxel_steps = count_steps ? (int64_t)hc[3] : 0;
-    stats->tile_rows = (int64_t)hc[7];  // rows accepted whole by the key box of all their pairs
+    stats->tile_rows = 0;
     stats->box_pairs = (int64_t)hc[5];
     stats->lattice_pairs = (int64_t)hc[6];
     stats->edges = E;
@@ -974,15 +995,15 @@ int sspp_gpu_peer_buffer_release(sspp_gpu_ctx* ctx, void* device_ptr) {
   return fail(ctx, SSPP_ERR_INVALID, "peer_buffer_release: not a peer buffer of this context");
 }
 
-int sspp_gpu_connect_push_csr(sspp_gpu_ctx* ctx, int world, int rank, const int64_t* edge_counts_device,
-                              const int64_t* row_base_device, int64_t* const* row_ptr_peers, int32_t* const* col_idx_peers,
-                              int64_t col_capacity, int64_t* overflow_device) {
-  if (!ctx) return SSPP_ERR_INVALID;
-  if (!ctx->has_result) return fail(ctx, SSPP_ERR_STATE, "connect_push_csr: no connect result");
+namespace {
+// one block of a CSR-shaped result (row pointers relative to the block + items) into the whole-result buffers of all ranks
+int push_block(sspp_gpu_ctx* ctx, const char* who, const long long* rp_local, const int* items_local, int world, int rank,
+               const int64_t* counts_device, const int64_t* row_base_device, int64_t* const* row_ptr_peers,
+               int32_t* const* col_idx_peers, int64_t col_capacity, int64_t* overflow_device) {
   if (world < 1 || world > SSPP_MAX_PEERS || rank < 0 || rank >= world)
-    return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: world must be 1..SSPP_MAX_PEERS and rank inside it");
-  if (!edge_counts_device || !row_base_device || !row_ptr_peers || !col_idx_peers || !overflow_device || col_capacity < 0)
-    return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: null argument");
+    return fail(ctx, SSPP_ERR_INVALID, std::string(who) + ": world must be 1..SSPP_MAX_PEERS and rank inside it");
+  if (!counts_device || !row_base_device || !row_ptr_peers || !col_idx_peers || !overflow_device || col_capacity < 0)
+    return fail(ctx, SSPP_ERR_INVALID, std::string(who) + ": null argument");
   PushPeers p;
   p.world = world;
   p.rank = rank;
@@ -991,16 +1012,67 @@ int sspp_gpu_connect_push_csr(sspp_gpu_ctx* ctx, int world, int rank, const int6
     p.col[k] = nullptr;
   }
   for (int k = 0; k < world; ++k) {
-    if (!row_ptr_peers[k] || !col_idx_peers[k]) return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: null peer buffer");
-    if (((uintptr_t)col_idx_peers[k] & 15) != 0) return fail(ctx, SSPP_ERR_INVALID, "connect_push_csr: column buffers must be 16-byte aligned");
+    if (!row_ptr_peers[k] || !col_idx_peers[k]) return fail(ctx, SSPP_ERR_INVALID, std::string(who) + ": null peer buffer");
+    if (((uintptr_t)col_idx_peers[k] & 15) != 0) return fail(ctx, SSPP_ERR_INVALID, std::string(who) + ": column buffers must be 16-byte aligned");
     p.rp[k] = (long long*)row_ptr_peers[k];
     p.col[k] = col_idx_peers[k];
   }
   CK(cudaSetDevice(ctx->device));
-  k_push_csr<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(p, (const long long*)edge_counts_device, (const long long*)row_base_device,
-                                                         ctx->row_ptr.as<long long>(), ctx->col_idx.as<int>(),
-                                                         (long long)col_capacity, (long long*)overflow_device);
+  k_push_csr<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(p, (const long long*)counts_device, (const long long*)row_base_device,
+                                                         rp_local, items_local, (long long)col_capacity, (long long*)overflow_device);
   LAUNCHED(ctx);
+  return SSPP_OK;
+}
+}  // namespace
+
+int sspp_gpu_connect_push_csr(sspp_gpu_ctx* ctx, int world, int rank, const int64_t* edge_counts_device,
+                              const int64_t* row_base_device, int64_t* const* row_ptr_peers, int32_t* const* col_idx_peers,
+                              int64_t col_capacity, int64_t* overflow_device) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!ctx->has_result) return fail(ctx, SSPP_ERR_STATE, "connect_push_csr: no connect result");
+  return push_block(ctx, "connect_push_csr", ctx->row_ptr.as<long long>(), ctx->col_idx.as<int>(), world, rank, edge_counts_device,
+                    row_base_device, row_ptr_peers, col_idx_peers, col_capacity, overflow_device);
+}
+
+int sspp_gpu_visibility_push(sspp_gpu_ctx* ctx, int world, int rank, const int64_t* pair_counts_device,
+                             const int64_t* view_base_device, int64_t* const* view_ptr_peers, int32_t* const* point_idx_peers,
+                             int64_t idx_capacity, int64_t* overflow_device) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!ctx->has_vis) return fail(ctx, SSPP_ERR_STATE, "visibility_push: no visibility result");
+  return push_block(ctx, "visibility_push", ctx->vis_ptr.as<long long>(), ctx->vis_idx.as<int>(), world, rank, pair_counts_device,
+                    view_base_device, view_ptr_peers, point_idx_peers, idx_capacity, overflow_device);
+}
+
+int sspp_gpu_balanced_cuts(sspp_gpu_ctx* ctx, const sspp_connect_params* params, int world, int work_row_weight, int64_t* cuts) {
+  if (!ctx || !params || !cuts) return fail(ctx, SSPP_ERR_INVALID, "balanced_cuts: null argument");
+  if (world < 1 || world > 4096 || work_row_weight < 1 || work_row_weight > 1024)
+    return fail(ctx, SSPP_ERR_INVALID, "balanced_cuts: world must be 1..4096 and work_row_weight 1..1024");
+  const int64_t n = ctx->n_nodes;
+  if (n == 0 || world == 1) {
+    for (int g = 0; g <= world; ++g) cuts[g] = g == world ? n : 0;
+    return SSPP_OK;
+  }
+  sspp_connect_params p = *params;
+  p.row_begin = p.row_end = 0;  // the counting pass runs over all rows
+  p.count_only = 1;
+  p.count_steps = 0;
+  p.use_pyramid = 1;
+  sspp_connect_stats st;
+  int rc = connect_impl(ctx, &p, &st, nullptr);
+  if (rc) return rc;
+  CK(ctx->q0.reserve((size_t)n * 4));
+  CK(ctx->q1.reserve((size_t)(n + 1) * 8));
+  CK(ctx->q2.reserve((size_t)(world + 1) * 8));
+  k_row_weights<<<ceil_div(n, 256), 256, 0, ctx->stream>>>(ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(), p.use_map ? 1 : 0,
+                                                          work_row_weight, n, ctx->q0.as<int>());
+  LAUNCHED(ctx);
+  rc = scan_exclusive<long long>(ctx, ctx->q0.as<int>(), n, ctx->q1.as<long long>());
+  if (rc) return rc;
+  k_find_cuts<<<ceil_div(world + 1, 128), 128, 0, ctx->stream>>>(ctx->q1.as<long long>(), n, world, ctx->q2.as<long long>());
+  LAUNCHED(ctx);
+  CK(cudaMemcpyAsync(cuts, ctx->q2.p, (size_t)(world + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  for (int g = 1; g <= world; ++g) cuts[g] = std::max(cuts[g], cuts[g - 1]);
   return SSPP_OK;
 }
 

@@ -23,7 +23,8 @@ class SsppError(RuntimeError):
 class ConnectParams(ctypes.Structure):
     _fields_ = [("radius", ctypes.c_double), ("box", ctypes.c_double * 3), ("use_map", ctypes.c_int32),
                 ("position_mode", ctypes.c_int32), ("row_begin", c_i64), ("row_end", c_i64),
-                ("use_pyramid", ctypes.c_int32), ("count_steps", ctypes.c_int32)]
+                ("use_pyramid", ctypes.c_int32), ("count_steps", ctypes.c_int32), ("count_only", ctypes.c_int32),
+                ("reserved", ctypes.c_int32)]
 
 
 class ConnectStats(ctypes.Structure):
@@ -84,6 +85,7 @@ def load_library():
         "sspp_gpu_connect_fetch": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_connect_fetch_device": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_connect_row_classes": (ctypes.c_int, [c_vp, c_vp]),
+        "sspp_gpu_balanced_cuts": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), ctypes.c_int, ctypes.c_int, c_vp]),
         "sspp_gpu_assemble_csr_blocks": (ctypes.c_int, [c_vp, c_vp, c_vp, ctypes.c_int, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
         "sspp_gpu_peer_buffer_create": (ctypes.c_int, [c_vp, c_i64, ctypes.POINTER(c_vp), c_vp]),
         "sspp_gpu_peer_buffer_open": (ctypes.c_int, [c_vp, c_vp, ctypes.POINTER(c_vp)]),
@@ -106,6 +108,7 @@ def load_library():
         "sspp_gpu_visibility": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(Frustum), ctypes.POINTER(VisibilityStats)]),
         "sspp_gpu_visibility_fetch": (ctypes.c_int, [c_vp, c_vp, c_vp]),
         "sspp_gpu_visibility_timings": (ctypes.c_int, [c_vp, c_vp]),
+        "sspp_gpu_visibility_push": (ctypes.c_int, [c_vp, ctypes.c_int, ctypes.c_int, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
         "sspp_gpu_measure_l2_bandwidth": (ctypes.c_int, [c_vp, c_i64, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]),
         "sspp_gpu_launch_count": (c_i64, [c_vp]),
     }
@@ -237,8 +240,15 @@ class Engine:
         self._ck(self.L.sspp_gpu_connect_fetch(self.h, _p(rp), _p(col)))
         return rp[:stats.rows + 1], col[:stats.edges]
 
+    def balanced_cuts(self, world, work_row_weight=8, **kw):
+        """world + 1 cut points over the list indices with about equal work per block (set-up step, runs the count pass)."""
+        p = self.params(**kw)
+        cuts = np.zeros(world + 1, dtype=np.int64)
+        self._ck(self.L.sspp_gpu_balanced_cuts(self.h, ctypes.byref(p), world, work_row_weight, _p(cuts)))
+        return cuts
+
     def connect_row_classes(self, stats):
-        """uint8 per row of the last connect: 0 no pair, 1 pyramid, 2 row key box free, 3 decided pair by pair."""
+        """uint8 per row of the last connect: 0 no pair, 1 pyramid, 3 decided pair by pair (2 reserved)."""
         out = np.zeros(max(stats.rows, 1), dtype=np.uint8)
         self._ck(self.L.sspp_gpu_connect_row_classes(self.h, _p(out)))
         return out[:stats.rows]
@@ -380,6 +390,13 @@ class Engine:
         assert len(vp) >= nv + 1 and len(idx) >= st.visible_pairs
         self._ck(self.L.sspp_gpu_visibility_fetch(self.h, _p(vp), _p(idx)))
         return st, vp[:nv + 1], idx[:st.visible_pairs]
+
+    def visibility_push(self, world, rank, pair_counts, view_base, vp_peers, idx_peers, idx_capacity, overflow):
+        """as connect_push_csr, for the last visibility result (raw device addresses; lists of `world` peer buffers)"""
+        a = (c_vp * world)(*[c_vp(int(x)) for x in vp_peers])
+        b = (c_vp * world)(*[c_vp(int(x)) for x in idx_peers])
+        self._ck(self.L.sspp_gpu_visibility_push(self.h, world, rank, c_vp(pair_counts), c_vp(view_base), a, b,
+                                                 int(idx_capacity), c_vp(overflow)))
 
     def visibility_timings(self):
         t = np.zeros(8, dtype=np.float32)

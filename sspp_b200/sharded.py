@@ -13,18 +13,31 @@ NVLink peer memory; NCCL only carries the 8-byte edge counts and the closing bar
 GpuCsrAssembler (NCCL all-gather of padded slots + a packing kernel) stays as the comparison.
 
 StreamedPeerAssembler goes one step further and overlaps the exchange with the edge test:
-sspp_gpu_connect_to_peers runs the test in row chunks and copies every finished chunk into slot
-[rank] of all ranks' block buffers over NVLink (copy engines) while the next chunk is computed; what
-is left after the pass is one MAX all-reduce (barrier + "does every block fit") and the local packing
-kernel.
+sspp_gpu_connect_to_peers runs the test in row chunks and a small push kernel on a second stream stores
+every finished chunk into slot [rank] of all ranks' block buffers over NVLink while the next chunk's edge
+kernel runs (all of it queued by the host in one go: the chunk sizes stay on the device); what is left
+after the pass is one MAX all-reduce (barrier + "does every block fit") and the local packing kernel.
+
+The same push serves the visibility pass (PeerCsrAssembler(kind="visibility")): viewpoints are split in
+contiguous blocks like rows, and (view_ptr, point_idx) is assembled on every rank.  Row blocks may be cut
+by work instead of by count (Engine.balanced_cuts -> the `cuts` argument of the assemblers).
 """
 import torch
 import torch.distributed as dist
 
 
 def row_range(n, rank, world):
-    """Contiguous block of list indices owned by `rank`."""
+    """Contiguous block of list indices owned by `rank` (equal row counts)."""
     return (n * rank) // world, (n * (rank + 1)) // world
+
+
+def row_cuts(n, world, cuts=None):
+    """world + 1 cut points: the given ones (e.g. Engine.balanced_cuts: equal WORK per block) or equal row counts."""
+    if cuts is None:
+        return [row_range(n, g, world)[0] for g in range(world)] + [n]
+    cuts = [int(c) for c in cuts]
+    assert len(cuts) == world + 1 and cuts[0] == 0 and cuts[-1] == n and all(a <= b for a, b in zip(cuts, cuts[1:]))
+    return cuts
 
 
 def gather_counts(rows, edges, device):
@@ -69,12 +82,13 @@ class GpuCsrAssembler:
     column slot size follows a MAX all-reduce of the ranks' block sizes (8 bytes, every call), so all
     ranks grow their slots in the same call."""
 
-    def __init__(self, eng, n_nodes, device):
+    def __init__(self, eng, n_nodes, device, cuts=None):
         self.eng = eng
         self.world = dist.get_world_size()
         self.rank = dist.get_rank()
         self.device = device
-        base = [row_range(n_nodes, g, self.world)[0] for g in range(self.world)] + [n_nodes]
+        base = row_cuts(n_nodes, self.world, cuts)
+        self.rows = (base[self.rank], base[self.rank + 1])
         self.row_base = torch.tensor(base, dtype=torch.int64, device=device)
         self.stride_r = max(base[g + 1] - base[g] for g in range(self.world)) + 1
         self.n = n_nodes
@@ -185,13 +199,18 @@ class PeerCsrAssembler:
     The column buffers are sized on the first call and re-made, on all ranks alike, if a graph outgrows
     them (every rank sees the same total, so the decision needs no extra message)."""
 
-    def __init__(self, eng, n_nodes, device):
+    def __init__(self, eng, n_nodes, device, cuts=None, kind="connect"):
+        """kind: "connect" (rows = way-points, items = adjacency) or "visibility" (rows = viewpoints, items = visible
+        point indices: the same exchange on (view_ptr, point_idx), SURVEY 8 e).  cuts: world + 1 row cut points."""
+        assert kind in ("connect", "visibility")
+        self.kind = kind
         self.eng = eng
         self.world = dist.get_world_size()
         self.rank = dist.get_rank()
         self.device = device
         self.n = n_nodes
-        base = [row_range(n_nodes, g, self.world)[0] for g in range(self.world)] + [n_nodes]
+        base = row_cuts(n_nodes, self.world, cuts)
+        self.rows = (base[self.rank], base[self.rank + 1])
         self.row_base = torch.tensor(base, dtype=torch.int64, device=device)
         self.ext_stream = torch.cuda.ExternalStream(eng.stream(), device=device)
         self.my_count = torch.zeros(1, dtype=torch.int64, device=device)
@@ -221,17 +240,19 @@ class PeerCsrAssembler:
         self.out_col = device_view(self.col_ptr, self.col_cap, torch.int32, self.device)
 
     def assemble(self, stats):
-        """stats: the ConnectStats of this rank's sspp_gpu_connect.  Returns (row_ptr, col_idx) device
-        tensors of the whole graph (col_idx is the buffer; row_ptr[-1] entries of it are valid)."""
+        """stats: the ConnectStats of this rank's sspp_gpu_connect (or the VisibilityStats of its
+        sspp_gpu_visibility).  Returns (row_ptr, col_idx) device tensors of the whole graph (col_idx is the
+        buffer; row_ptr[-1] entries of it are valid)."""
         cur = torch.cuda.current_stream()
-        self.my_count.fill_(int(stats.edges))
+        push = self.eng.connect_push_csr if self.kind == "connect" else self.eng.visibility_push
+        self.my_count.fill_(int(stats.edges if self.kind == "connect" else stats.visible_pairs))
         dist.all_gather_into_tensor(self.counts, self.my_count)
         if self.col_cap == 0:
             self._size_columns(int(self.counts.sum().item()))
         for attempt in range(2):
             self.ext_stream.wait_event(cur.record_event())
-            self.eng.connect_push_csr(self.world, self.rank, self.counts.data_ptr(), self.row_base.data_ptr(), self.rp_peers,
-                                      self.col_peers, self.col_cap, self.overflow.data_ptr())
+            push(self.world, self.rank, self.counts.data_ptr(), self.row_base.data_ptr(), self.rp_peers, self.col_peers, self.col_cap,
+                 self.overflow.data_ptr())
             cur.wait_event(self.ext_stream.record_event())
             dist.all_reduce(self.overflow, op=dist.ReduceOp.MAX)
             over = int(self.overflow.item())
@@ -258,13 +279,13 @@ class StreamedPeerAssembler:
     rank may already be writing the next graph's chunks into its peers while they still pack the last
     one (the barrier of the call in between orders the reuse of a set)."""
 
-    def __init__(self, eng, n_nodes, device):
+    def __init__(self, eng, n_nodes, device, cuts=None):
         self.eng = eng
         self.world = dist.get_world_size()
         self.rank = dist.get_rank()
         self.device = device
         self.n = n_nodes
-        base = [row_range(n_nodes, g, self.world)[0] for g in range(self.world)] + [n_nodes]
+        base = row_cuts(n_nodes, self.world, cuts)
         self.rows = (base[self.rank], base[self.rank + 1])
         self.row_base = torch.tensor(base, dtype=torch.int64, device=device)
         self.stride_r = max(base[g + 1] - base[g] for g in range(self.world)) + 1

@@ -55,7 +55,7 @@ def _enumerate_rays(eng, orc, w, res, start, end):
     return out
 
 
-def _check_scene(eng, orc, res, km, dm, occ, known, nodes, radius, cores, min_pairs, want_classes=(1, 2, 3)):
+def _check_scene(eng, orc, res, km, dm, occ, known, nodes, radius, cores, min_pairs, want_classes=(1, 3)):
     n = len(nodes)
     eng.set_nodes(nodes)
     st = eng.connect(radius=radius, box=BOX)

@@ -145,7 +145,7 @@ def test_connect_to_peers_blocks_pack_to_one_gpu_csr(eng, lattice, world):
             assert int(over.item()) == 0
             assert np.array_equal(out_rp.cpu().numpy(), rp_full), "row_ptr on rank %d differs" % k
             assert np.array_equal(out_col.cpu().numpy()[: st.edges], col_full), "col_idx on rank %d differs" % k
-        # a slot that is too small: nothing is sent, the error carries the size needed
+        # a slot that is too small: the error carries the size needed (the caller resizes and runs the pass again)
         with pytest.raises(SsppError) as ei:
             ranks[0].connect_to_peers(world, 0, [t.data_ptr() for t in rp_blk], [t.data_ptr() for t in col_blk], stride_r,
                                       edges[0] // 2, radius=1.5, box=BOX, rows=(bounds[0], bounds[1]))
@@ -153,6 +153,97 @@ def test_connect_to_peers_blocks_pack_to_one_gpu_csr(eng, lattice, world):
     finally:
         for e in ranks:
             e.close()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_visibility_blocks_push_to_one_gpu_result(eng, orc, world):
+    """Sharded visibility (SURVEY 8 e: "for visibility: same pattern on (counts, indices)"): every rank computes a
+    contiguous block of the viewpoints, sspp_gpu_visibility_push writes the blocks into all ranks' whole-result
+    buffers, and (view_ptr, point_idx) equals one call over all viewpoints — and the oracle's answer."""
+    import torch
+    dev = torch.device("cuda", 0)
+    res = 0.3
+    km, dm, occ, known = scenes.synthetic_map(n_vox=64, res=res, seed=5, n_boxes=8, n_spheres=6, region=14.0)
+    pts = scenes.surface_points(occ, known, km, dm, res, 20000, seed=45)
+    poses = scenes.viewpoints_near(pts, 301, standoff=2.5, seed=46)
+    fr = (58.0, 45.0, 0.7, 6.0)
+    eng.map_create(res, km, dm, True)
+    eng.map_upload_dense(occ, known)
+    eng.set_model_points(pts)
+    st, vp_full, idx_full = eng.visibility(poses, *fr)
+    assert st.visible_pairs > 1000
+    w = orc.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    vp_o, idx_o, _, _ = w.visibility(poses, *fr, pts)
+    w.close()
+    assert np.array_equal(vp_full, vp_o) and np.array_equal(idx_full, idx_o)
+    nv = len(poses)
+    bounds = [(nv * g) // world for g in range(world + 1)]
+    ranks = [Engine(0) for _ in range(world)]
+    try:
+        stats = []
+        for g, e in enumerate(ranks):
+            e.map_create(res, km, dm, True)
+            e.map_upload_dense(occ, known)
+            e.set_model_points(pts)
+            stats.append(e.visibility(poses[bounds[g]:bounds[g + 1]], *fr, fetch=False))
+        counts = torch.tensor([s.visible_pairs for s in stats], dtype=torch.int64, device=dev)
+        assert int(counts.sum()) == st.visible_pairs
+        view_base = torch.tensor(bounds, dtype=torch.int64, device=dev)
+        cap = ((st.visible_pairs + 3) // 4) * 4 + 8
+        out_vp = [torch.full((nv + 1,), -1, dtype=torch.int64, device=dev) for _ in range(world)]
+        out_idx = [torch.full((cap,), -1, dtype=torch.int32, device=dev) for _ in range(world)]
+        over = torch.zeros(1, dtype=torch.int64, device=dev)
+        torch.cuda.synchronize()
+        for g, e in enumerate(ranks):
+            e.visibility_push(world, g, counts.data_ptr(), view_base.data_ptr(), [t.data_ptr() for t in out_vp],
+                              [t.data_ptr() for t in out_idx], cap, over.data_ptr())
+        for e in ranks:
+            e.synchronize()
+        assert int(over.item()) == 0
+        for k in range(world):
+            assert np.array_equal(out_vp[k].cpu().numpy(), vp_full), "view_ptr of peer %d differs" % k
+            assert np.array_equal(out_idx[k].cpu().numpy()[: st.visible_pairs], idx_full), "point_idx of peer %d differs" % k
+        with pytest.raises(SsppError):  # no visibility result on a fresh context
+            Engine(0).visibility_push(world, 0, counts.data_ptr(), view_base.data_ptr(), [t.data_ptr() for t in out_vp],
+                                      [t.data_ptr() for t in out_idx], cap, over.data_ptr())
+    finally:
+        for e in ranks:
+            e.close()
+
+
+def test_balanced_cuts_split_the_work_not_the_rows(eng):
+    """sspp_gpu_balanced_cuts (SURVEY 8 e "split by prefix-sum of candidate counts"): the cut points are where the
+    weighted prefix of the per-row pair counts crosses g/G of the total — recomputed here from the engine's own
+    per-row data — and the blocks they define still concatenate to the one-GPU CSR."""
+    res = 0.3
+    km, dm, occ, known = scenes.synthetic_map(n_vox=96, res=res, seed=7, n_boxes=20, n_spheres=14, region=22.0)
+    rng = np.random.RandomState(5)
+    # dense cloud on one side, sparse on the other: equal row counts would be badly unbalanced
+    nodes = np.ascontiguousarray(np.concatenate([rng.uniform([-11, -11, -11], [0, 11, 11], (9000, 3)),
+                                                 rng.uniform([0, -11, -11], [11, 11, 11], (3000, 3))]))
+    n = len(nodes)
+    eng.map_create(res, km, dm, True)
+    eng.map_upload_dense(occ, known)
+    eng.set_nodes(nodes)
+    st = eng.connect(radius=1.5, box=BOX)
+    rp, col = eng.connect_fetch(st)
+    cls = eng.connect_row_classes(st)
+    s0 = eng.connect(radius=1.5, use_map=False)
+    deg0 = np.diff(eng.connect_fetch(s0)[0])  # in-radius pairs per row
+    for world, heavy in ((2, 8), (5, 8), (3, 1)):
+        cuts = eng.balanced_cuts(world, heavy, radius=1.5, box=BOX)
+        w = deg0 * np.where(cls == 3, heavy, 1)
+        prefix = np.concatenate([[0], np.cumsum(w)])
+        want = [0] + [int(np.searchsorted(prefix, (int(prefix[-1]) * g) // world, side="left")) for g in range(1, world)] + [n]
+        assert list(cuts) == want
+        loads = [int(prefix[cuts[g + 1]] - prefix[cuts[g]]) for g in range(world)]
+        assert max(loads) <= 1.05 * (prefix[-1] / world) + w.max()
+        parts = [eng.connect_fetch(eng.connect(radius=1.5, box=BOX, rows=(int(cuts[g]), int(cuts[g + 1])))) for g in range(world)]
+        assert np.array_equal(np.concatenate([q[1] for q in parts]), col)
+        base = np.cumsum([0] + [len(q[1]) for q in parts])
+        assert np.array_equal(np.concatenate([parts[g][0][:-1] + base[g] for g in range(world)] + [[base[-1]]]), rp)
+    assert list(eng.balanced_cuts(1, 8, radius=1.5, box=BOX)) == [0, n]
 
 
 def _ipc_rank(rank, world, port, q):
@@ -191,6 +282,30 @@ def _ipc_rank(rank, world, port, q):
             ok = ok and np.array_equal(rp, rpf) and np.array_equal(col[: sf.edges], colf)
             dist.barrier()
         sasm.close()
+        # rows cut by work (every rank computes the same cuts from the same nodes and map) ...
+        cuts = e.balanced_cuts(world, 8, radius=1.5, box=BOX)
+        basm = sharded.PeerCsrAssembler(e, n, dev, cuts=cuts)
+        st = e.connect(radius=1.5, box=BOX, rows=basm.rows)
+        rp, col = basm.assemble(st)
+        sf = e.connect(radius=1.5, box=BOX)
+        rpf, colf = e.connect_fetch(sf)
+        ok = ok and np.array_equal(rp.cpu().numpy(), rpf) and np.array_equal(col.cpu().numpy()[: sf.edges], colf)
+        dist.barrier()
+        basm.close()
+        # ... and the visibility pass sharded by viewpoint
+        km, dm, occ, known = scenes.synthetic_map(n_vox=64, res=0.3, seed=5, n_boxes=8, n_spheres=6, region=64 * 0.3 * 0.75)
+        pts = scenes.surface_points(occ, known, km, dm, 0.3, 20000, seed=45)
+        poses = scenes.viewpoints_near(pts, 777, standoff=2.5, seed=46)
+        e.set_model_points(pts)
+        vasm = sharded.PeerCsrAssembler(e, len(poses), dev, kind="visibility")
+        for _ in range(2):
+            vs = e.visibility(poses[vasm.rows[0]:vasm.rows[1]], 58.0, 45.0, 0.7, 6.0, fetch=False)
+            vp, idx = vasm.assemble(vs)
+            dist.barrier()
+        vf, vpf, idxf = e.visibility(poses, 58.0, 45.0, 0.7, 6.0)
+        ok = ok and np.array_equal(vp.cpu().numpy(), vpf) and np.array_equal(idx.cpu().numpy()[: vf.visible_pairs], idxf)
+        dist.barrier()
+        vasm.close()
         q.put((rank, bool(ok)))
     finally:
         e.close()
