@@ -229,6 +229,29 @@ class RefPlanner:
         return path[:k], int(stats[0]), int(stats[1])
 
 
+class RefCoveragePlanner(RefPlanner):
+    """The reference's own PathPlanner driven through oracle/ref_harness.cpp's HarnessCoverage: the authored
+    coverage semantics on the oracle, so that the reference's dynamic sampling loop can run (only with LIB_REF)."""
+
+    def __init__(self, orc, radius, world, cam):
+        self.L = orc.L
+        self.world = world
+        self.h = self.L.ref_coverage_planner_create(radius, world.h if world else None, _p(_f64(cam["mount_xyz"])),
+                                                    _p(_f64(cam["mount_rpy"])), cam["hfov"], cam["vfov"], cam["near"], cam["far"])
+
+    def set_model_points(self, pts):
+        a = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+        self.L.ref_coverage_set_model(self.h, _p(a), len(a))
+
+    def set_clustering(self, tolerance, min_size, standoff):
+        self.L.ref_coverage_set_clustering(self.h, tolerance, min_size, standoff)
+
+    def dynamic_sampling(self, start, size, start_res, res_decrement):
+        out = np.zeros(3, dtype=np.int64)
+        self.L.ref_dynamic_sampling(self.h, _p(_f64(start)), _p(_f64(size)), start_res, res_decrement, _p(out))
+        return int(out[0]), int(out[1]), int(out[2])
+
+
 class Oracle:
     def __init__(self, path=LIB_ORACLE):
         if not os.path.exists(path):
@@ -294,6 +317,12 @@ class Oracle:
             L.ref_get_csr.argtypes = [vp, vp, vp, lng]
             L.ref_astar.restype = lng
             L.ref_astar.argtypes = [vp, vp, vp, lng, vp]
+            if hasattr(L, "ref_coverage_planner_create"):
+                L.ref_coverage_planner_create.restype = vp
+                L.ref_coverage_planner_create.argtypes = [dbl, vp, vp, vp, dbl, dbl, dbl, dbl]
+                L.ref_coverage_set_model.argtypes = [vp, vp, lng]
+                L.ref_coverage_set_clustering.argtypes = [vp, dbl, ctypes.c_int, dbl]
+                L.ref_dynamic_sampling.argtypes = [vp, vp, vp, dbl, dbl, vp]
 
     def world(self, resolution, treat_unknown=True):
         return World(self, resolution, treat_unknown)
@@ -301,6 +330,10 @@ class Oracle:
     def planner(self, radius, world=None):
         assert self.has_ref
         return RefPlanner(self, radius, world)
+
+    def coverage_planner(self, radius, world, cam):
+        assert self.has_ref
+        return RefCoveragePlanner(self, radius, world, cam)
 
     def ray_lattice(self, box, res):
         offs = [np.zeros(4096) for _ in range(3)]

@@ -276,3 +276,45 @@ def test_dynamic_sampling_loop(eng):
     assert len(col) == e1 and col.max() < n1
     coarse.close()
     fine.close()
+
+
+def test_dynamic_sampling_loop_equals_the_references_own_loop(eng, ref):
+    """f3 pinned: the REFERENCE'S OWN PathPlanner::dynamicNodesGenerationAndConnection (src/pathplanner.cpp:765-891,
+    compiled unmodified into oracle/_ref) is driven through a harness heuristic that implements the authored coverage
+    semantics on the oracle (oracle/ref_harness.cpp: HarnessCoverage), and the mirror's GPU-backed loop must build
+    the same search space: the same way-points in the same list order, the same adjacency, the same connection count
+    and the same covered model points — over three stages (3.0 m, 1.9 m, 0.8 m samples; the fourth resolution is
+    negative and ends the loop).  The scene is small because the reference checks for duplicate connections in
+    O(E^2) after every stage (checkSearchSpaceDuplications, :568-610): 645 way-points / 38 864 connections take it 11 s."""
+    from sspp_b200 import scenes
+    res = 0.25
+    km, dm, occ, known = scenes.synthetic_map(n_vox=64, res=res, seed=4, n_boxes=4, n_spheres=3, region=7.0)
+    allp = scenes.surface_points(occ, known, km, dm, res, 20000, seed=45)
+    c = allp[np.argmin(np.linalg.norm(allp, axis=1))]
+    pts = np.ascontiguousarray(allp[np.linalg.norm(allp - c, axis=1) < 3.0][:1500])  # the part of the model to inspect
+    cam = dict(mount_xyz=[0.0, 0.0, 0.0], mount_rpy=[0.0, 0.0, 0.0], hfov=90.0, vfov=70.0, near=0.3, far=5.0)
+    w = ref.world(res, True)
+    w.build_dense(km, dm, occ, known)
+    r = ref.coverage_planner(1.6, w, cam)
+    r.set_model_points(pts)
+    r.set_clustering(0.6, 20, 0.8)
+    p = host_lib.HostPlanner(1.6, device=0, coverage=cam)
+    p.map_create(res, km, dm, True)
+    p.map_upload_dense(occ, known)
+    p.set_model_points(pts)
+    p.set_clustering(0.6, 20, 0.8)
+    args = ([0, 0, 0], [10, 10, 4], 3.0, 1.1)
+    n_r, e_r, cov_r = r.dynamic_sampling(*args)
+    n_h, e_h, cov_h = p.dynamic_sampling(*args)
+    print("dynamic sampling: reference %d way-points, %d connections, %d of %d model points covered; mirror %d / %d / %d"
+          % (n_r, e_r, cov_r, len(pts), n_h, e_h, cov_h))
+    assert n_r > 300 and e_r > 10000 and 0 < cov_r <= len(pts)
+    assert (n_h, e_h, cov_h) == (n_r, e_r, cov_r)
+    poses_r, ids_r = r.nodes()
+    poses_h, ids_h = p.nodes()
+    assert np.array_equal(poses_h, poses_r) and np.array_equal(ids_h, ids_r)
+    (rp_r, col_r), (rp_h, col_h) = r.csr(), p.csr()
+    assert np.array_equal(rp_h, rp_r) and np.array_equal(col_h, col_r)
+    r.close()
+    p.close()
+    w.close()
