@@ -185,3 +185,26 @@ def window_pairs(nodes, core_lo, core_hi, radius):
     ii, jj = ii[keep], jj[keep]
     same = np.all(sub[ii] == sub[jj], axis=1)
     return near[rows_local], near[ii], near[jj], same
+
+
+def aircraft_model(res=0.25):
+    """S2 stand-in for the inspected aircraft (SURVEY.md §8 d; the reference ships the viewpoints of
+    resources/SearchSpaceUAV_1.5m_1to4_NEW.txt but not the model they were sampled around): an ellipsoid fuselage along
+    y, two box wings, tail plane and fin, inside x in [-30, 30], y in [-36, 36], z in [0, 15], voxelised at `res`
+    over the bounding box of the fixture's way-points (x +-34.5, y +-40.5, z -3 .. 19.5).  Everything else known-free.
+    -> key_min, dims, occ_bits, known_bits"""
+    lo = np.array([-34.5, -40.5, -3.0])
+    hi = np.array([34.5, 40.5, 19.5])
+    k0 = np.floor(lo / res).astype(np.int64)
+    n = (np.ceil(hi / res).astype(np.int64) - k0)
+    cx = (k0[0] + np.arange(n[0]) + 0.5) * res
+    cy = (k0[1] + np.arange(n[1]) + 0.5) * res
+    cz = (k0[2] + np.arange(n[2]) + 0.5) * res
+    Z, Y, X = np.meshgrid(cz, cy, cx, indexing="ij")
+    occ = ((X / 3.0) ** 2 + (Y / 34.0) ** 2 + ((Z - 5.0) / 3.0) ** 2) <= 1.0                      # fuselage
+    occ |= (np.abs(X) <= 29.0) & (np.abs(Y - 2.0) <= 4.0 - np.abs(X) * 0.08) & (np.abs(Z - 4.0) <= 0.5)  # wings, tapering
+    occ |= (np.abs(X) <= 9.0) & (np.abs(Y + 30.0) <= 2.0) & (np.abs(Z - 6.0) <= 0.4)                  # tail plane
+    occ |= (np.abs(X) <= 0.5) & (np.abs(Y + 30.0) <= 3.5) & (Z >= 7.0) & (Z <= 14.5)                   # fin
+    known = np.ones_like(occ)
+    key_min = (k0 + 32768).astype(np.int32)
+    return key_min, n.astype(np.int32), pack_bits(occ), pack_bits(known)

@@ -143,3 +143,33 @@ def make_cam_fixture():
 if __name__ == "__main__" and "--extra" in sys.argv:
     make_casarea()
     make_cam_fixture()
+
+
+def make_full_config2():
+    """BASELINE configs[1] at its FULL size: all 14 765 row-aligned UAV / camera poses of
+    resources/SearchSpaceUAV_1.5m_1to4_NEW.txt and SearchSpaceCam_1.5m_1to4_NEW.txt (read by
+    src/pathplanner.cpp:204-269), and the graph the reference's own connectNodes builds on them (R 2.5, no map:
+    the manager == NULL case).  The poses are stored as the files give them (three decimals), the adjacency as
+    row_ptr + a checksum + its first 4096 columns.      python tests/golden/make_golden.py --full"""
+    O = oracle_lib.Oracle(oracle_lib.LIB_REF)
+    uav = np.loadtxt("/root/reference/resources/SearchSpaceUAV_1.5m_1to4_NEW.txt")
+    cam = np.loadtxt("/root/reference/resources/SearchSpaceCam_1.5m_1to4_NEW.txt")
+    assert uav.shape == cam.shape == (14765, 7)
+    p = O.planner(2.5)
+    p.insert_nodes(uav)
+    poses, ids = p.nodes()
+    E = p.connect()
+    rp, col = p.csr()
+    h = np.bitwise_xor.reduce((col.astype(np.uint64) + 1) * np.uint64(0x9E3779B97F4A7C15) ^
+                              np.repeat(np.arange(len(rp) - 1, dtype=np.uint64), np.diff(rp)) * np.uint64(0xC2B2AE3D27D4EB4F))
+    # list order is insertion order reversed: SearchSpaceNode::id counts insertNode calls (src/searchspace.cpp:64-67),
+    # so ids[i] is the file row of list entry i — and of its camera pose
+    np.savez_compressed(os.path.join(HERE, "config2_full.npz"), poses=poses, ids=ids, cam_rows=cam, row_ptr=rp.astype(np.int32),
+                        col_hash=np.uint64(h), connections=E, col_head=col[:4096])
+    assert np.array_equal(poses, uav[ids])
+    print("config2 full", len(poses), "stored of", len(uav), "E", E, hex(int(h)))
+    p.close()
+
+
+if __name__ == "__main__" and "--full" in sys.argv:
+    make_full_config2()
