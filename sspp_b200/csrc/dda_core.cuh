@@ -173,7 +173,10 @@ SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float 
 
 // OccupancyOcTreeBase::castRay.  `cell` returns CELL_FREE / CELL_OCCUPIED / CELL_UNKNOWN for a key.
 // Returns true when an occupied voxel was reached (hit_k* = its key).
-template <class Cell>
+// EDGE = false: the caller has shown that the walk cannot come near the border of the 16-bit key space (origin key
+// further than max_range / res + 3 voxels from 0 and 65535 on every axis), so upstream's "leaving the key space"
+// test, which then can never fire, is left out of the loop.
+template <bool EDGE = true, class Cell>
 SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float dirx, float diry, float dirz,
                       bool ignore_unknown, double max_range, Cell& cell, int& hx, int& hy, int& hz, int* steps = nullptr) {
   int kx, ky, kz;
@@ -231,7 +234,7 @@ SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float di
     const bool d2 = !d0 && !d1;
     const int ksel = d0 ? kx : (d1 ? ky : kz);
     const int ssel = d0 ? sx : (d1 ? sy : sz);
-    if ((ssel < 0 && ksel == 0) || (ssel > 0 && ksel == 65535)) return false;  // leaving the key space
+    if (EDGE && ((ssel < 0 && ksel == 0) || (ssel > 0 && ksel == 65535))) return false;  // leaving the key space
     const int kn = ksel + ssel;
     const double tn = d_add(d0 ? tx : (d1 ? ty : tz), d0 ? dtx : (d1 ? dty : dtz));
     kx = d0 ? kn : kx;

@@ -85,6 +85,20 @@ struct CellOccupiedOnly {
   }
 };
 
+// The same for a walk that provably stays inside the mapped window: no bounds test, 32-bit word index
+// (the planes of any map that fits the 16-bit key space hold fewer than 2^31 words only up to 4096^3 / 32:
+// the caller checks map_words).
+struct CellOccupiedInside {
+  const uint32_t* occ;
+  int kx0, ky0, kz0;
+  unsigned ny, nz;
+  __device__ __forceinline__ int operator()(int kx, int ky, int kz) const {
+    const unsigned x = (unsigned)(kx - kx0), y = (unsigned)(ky - ky0), z = (unsigned)(kz - kz0);
+    const unsigned w = ((x >> 5) * nz + z) * ny + y;
+    return ((__ldg(occ + w) >> (x & 31)) & 1u) ? CELL_OCCUPIED : CELL_FREE;
+  }
+};
+
 struct BlockedGlobal {
   const DeviceMap* m;
   __device__ __forceinline__ int operator()(int kx, int ky, int kz) const { return map_blocked(*m, kx, ky, kz); }

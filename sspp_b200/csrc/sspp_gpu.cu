@@ -1542,7 +1542,7 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
     CK(cudaMemsetAsync(ctx->vis_counters.p, 0, 8 * 8, st));
     k_view_setup<<<ceil_div(nv, 128), 128, 0, st>>>(ctx->vis_poses.as<double>(), nv, vh, hw, np_dist, fp_dist, g, views);
     LAUNCHED(ctx);
-    k_view_bound<<<ceil_div(nv, 128), 128, 0, st>>>(views, (int)nv, g, pcs, words);
+    k_view_bound<<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, (int)nv, g, pcs, words);
     LAUNCHED(ctx);
     { int rc = scan_exclusive<long long>(ctx, words, nv, word_off); if (rc) return rc; }
     uint32_t* vmask = ctx->vis_mask.as<uint32_t>();

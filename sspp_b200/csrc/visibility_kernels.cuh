@@ -145,24 +145,60 @@ __global__ void k_pts_scatter(const float* __restrict__ xyz, int64_t n, const in
   sp[pos] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], __int_as_float((int)i));
 }
 
-// Ballot words a viewpoint's gather loop produces: one per 32 candidate points of every (z, y) run of
-// its cell box.  The count pass stores its ballots there and the fill pass reads them back instead
-// of loading the points and running the six-plane test a second time.
-__global__ void k_view_bound(const ViewRec* __restrict__ views, int nv, PointGrid g, const int* __restrict__ cell_start,
-                             int* __restrict__ words) {
-  int w = blockIdx.x * blockDim.x + threadIdx.x;
-  if (w >= nv) return;
-  const ViewRec& R = views[w];
-  int n = 0;
-  for (int cz = R.c0[2]; cz <= R.c1[2]; ++cz)
-    for (int cy = R.c0[1]; cy <= R.c1[1]; ++cy) {
-      const int cb = (cz * g.n[1] + cy) * g.n[0];
-      n += (cell_start[cb + R.c1[0] + 1] - cell_start[cb + R.c0[0]] + 31) >> 5;
-    }
-  words[w] = n;
+// The points a viewpoint has to test: for every (z, y) row of cells inside the frustum's bounding box, the run of x
+// cells the frustum can reach.  Each of the six planes bounds x on that row: a point (x, y, z) of the row passes
+// plane k only if a x + min over the row's y/z extent of (b y + c z) + d <= 0, which is a half-line in x.  The frustum
+// test itself runs in float with its own rounding, so the bound is relaxed by `tol`, forty times the worst rounding
+// error of that float expression, and the row's y/z extent is widened by a thousandth of a cell: a cell is only
+// left out when no point binned into it can pass the float test.  Returns the binned range [b, e) of the row.
+__device__ __forceinline__ void view_row_range(const ViewRec& R, const PointGrid& g, const int* __restrict__ cell_start, int cz,
+                                               int cy, int& b, int& e) {
+  const double cell = 1.0 / g.inv_cell, widen = cell * 1e-3, big = 1e30;
+  const double y0 = cy == 0 ? -big : g.min[1] + cy * cell - widen, y1 = cy == g.n[1] - 1 ? big : g.min[1] + (cy + 1) * cell + widen;
+  const double z0 = cz == 0 ? -big : g.min[2] + cz * cell - widen, z1 = cz == g.n[2] - 1 ? big : g.min[2] + (cz + 1) * cell + widen;
+  const double xm = fmax(fabs(g.min[0]), fabs(g.min[0] + g.n[0] * cell)), ym = fmax(fabs(g.min[1]), fabs(g.min[1] + g.n[1] * cell)),
+               zm = fmax(fabs(g.min[2]), fabs(g.min[2] + g.n[2] * cell));
+  double xlo = -big, xhi = big;
+  bool empty = false;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const double pa = R.pl[k][0], pb = R.pl[k][1], pc = R.pl[k][2], pd = R.pl[k][3];
+    const double tol = 1e-5 * (fabs(pa) * xm + fabs(pb) * ym + fabs(pc) * zm + fabs(pd)) + 1e-9;
+    const double myz = fmin(pb * y0, pb * y1) + fmin(pc * z0, pc * z1);
+    const double rhs = tol - myz - pd;  // a x <= rhs is necessary for the point to pass plane k
+    if (pa > 0.0) xhi = fmin(xhi, rhs / pa);
+    else if (pa < 0.0) xlo = fmax(xlo, rhs / pa);
+    else if (rhs < 0.0) empty = true;
+  }
+  int ca = R.c0[0], cb = R.c1[0];
+  if (xlo > -big) ca = max(ca, pgrid_axis(g, xlo - widen, 0));
+  if (xhi < big) cb = min(cb, pgrid_axis(g, xhi + widen, 0));
+  if (empty || ca > cb || !(xlo <= xhi)) { b = e = 0; return; }
+  const int base = (cz * g.n[1] + cy) * g.n[0];
+  b = cell_start[base + ca];
+  e = cell_start[base + cb + 1];
 }
 
-// one warp per viewpoint: in-frustum points of the cells its bounding box touches.
+// Ballot words a viewpoint's gather loop produces: one per 32 candidate points of every row of its cell box.  The
+// count pass stores its ballots there and the fill pass reads them back instead of loading the points and running
+// the six-plane test a second time.  One warp per viewpoint, one lane per row.
+__global__ void __launch_bounds__(256) k_view_bound(const ViewRec* __restrict__ views, int nv, PointGrid g,
+                                                    const int* __restrict__ cell_start, int* __restrict__ words) {
+  const int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (w >= nv) return;
+  const ViewRec& R = views[w];
+  const int nyr = R.c1[1] - R.c0[1] + 1, nrows = nyr * (R.c1[2] - R.c0[2] + 1);
+  int n = 0;
+  for (int r = lane; r < nrows; r += 32) {
+    int b, e;
+    view_row_range(R, g, cell_start, R.c0[2] + r / nyr, R.c0[1] + r % nyr, b, e);
+    n += (e - b + 31) >> 5;
+  }
+  for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+  if (lane == 0) words[w] = n;
+}
+
+// one warp per viewpoint: in-frustum points of the cells its frustum can reach.
 // FILL == false: run the frustum test, keep the ballots, count.  FILL == true (after the scan of the
 // counts): write (viewpoint, binned position) per ray from the stored ballots.
 template <bool FILL>
@@ -182,10 +218,14 @@ __global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__
   long long base = FILL ? ray_off[w] : 0;
   uint32_t* mw = mask + word_off[w];
   int filled = 0, it = 0;
-  for (int cz = R.c0[2]; cz <= R.c1[2]; ++cz)
-    for (int cy = R.c0[1]; cy <= R.c1[1]; ++cy) {
-      int cb = (cz * g.n[1] + cy) * g.n[0];
-      int b = cell_start[cb + R.c0[0]], e = cell_start[cb + R.c1[0] + 1];
+  const int nyr = R.c1[1] - R.c0[1] + 1, nrows = nyr * (R.c1[2] - R.c0[2] + 1);
+  for (int r0 = 0; r0 < nrows; r0 += 32) {
+    // the lanes work out the runs of 32 rows side by side, then the warp walks them one after the other
+    int rb = 0, re = 0;
+    if (r0 + lane < nrows) view_row_range(R, g, cell_start, R.c0[2] + (r0 + lane) / nyr, R.c0[1] + (r0 + lane) % nyr, rb, re);
+    const int nr = min(32, nrows - r0);
+    for (int rr = 0; rr < nr; ++rr) {
+      const int b = __shfl_sync(0xffffffffu, rb, rr), e = __shfl_sync(0xffffffffu, re, rr);
       for (int j0 = b; j0 < e; j0 += 32, ++it) {
         int j = j0 + lane;
         unsigned bal;
@@ -208,6 +248,7 @@ __global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__
         filled += __popc(bal);
       }
     }
+  }
   if (!FILL && lane == 0) ray_count[w] = filled;
 }
 
@@ -221,21 +262,50 @@ __global__ void __launch_bounds__(256) k_view_rays(DeviceMap m, const ViewRec* _
                                                    unsigned long long* steps_total) {
   const long long nrays = *ray_total;
   if (nrays > ray_cap) return;
+  const bool small_map = (long long)(m.dims[0] >> 5) * m.dims[1] * m.dims[2] < (1ll << 31);
   unsigned long long my_steps = 0;
   for (long long i0 = (long long)blockIdx.x * blockDim.x; i0 < nrays; i0 += (long long)gridDim.x * blockDim.x) {
     const long long i = i0 + threadIdx.x;
     bool visible = false;
     int w = -1;
-    if (i < nrays) {
+    const bool have = i < nrays;
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    float ox = 0.f, oy = 0.f, oz = 0.f;
+    if (have) {
       w = ray_view[i];
       const ViewRec& R = views[v0 + w];
-      float4 p = sp[ray_pt[i]];
-      float ox = R.T[0], oy = R.T[1], oz = R.T[2];
-      float dx = f_sub(p.x, ox), dy = f_sub(p.y, oy), dz = f_sub(p.z, oz);
-      CellOccupiedOnly cell;  // ignoreUnknown = true: unknown cells are walked through
-      cell.m = &m;
+      p = sp[ray_pt[i]];
+      ox = R.T[0]; oy = R.T[1]; oz = R.T[2];
+    }
+    const float dx = f_sub(p.x, ox), dy = f_sub(p.y, oy), dz = f_sub(p.z, oz);
+    const double range = norm3f(dx, dy, dz);
+    // A ray whose whole reach — origin key +- (range / res + 3) voxels — lies inside the mapped window (and so well
+    // inside the key space) needs neither the window test per voxel nor the key-space test per step.  The warp takes
+    // that path only when all its rays qualify (they share a viewpoint, so they almost always agree).
+    bool inside = !have;
+    if (have && small_map) {
+      int kx, ky, kz;
+      if (coord_to_key(m.ks, (double)ox, kx) && coord_to_key(m.ks, (double)oy, ky) && coord_to_key(m.ks, (double)oz, kz)) {
+        const int reach = (int)fmin(ceil(range * m.ks.res_factor), 100000.0) + 3;
+        inside = kx - reach >= m.kmin[0] && kx + reach < m.kmin[0] + m.dims[0] && ky - reach >= m.kmin[1] &&
+                 ky + reach < m.kmin[1] + m.dims[1] && kz - reach >= m.kmin[2] && kz + reach < m.kmin[2] + m.dims[2] &&
+                 m.kmin[0] > 0 && m.kmin[1] > 0 && m.kmin[2] > 0;
+      }
+    }
+    inside = __all_sync(0xffffffffu, inside);
+    if (have) {
       int hx, hy, hz, nsteps = 0;
-      bool hit = cast_ray(m.ks, ox, oy, oz, dx, dy, dz, true, norm3f(dx, dy, dz), cell, hx, hy, hz, COUNT ? &nsteps : nullptr);
+      bool hit;
+      if (inside) {
+        CellOccupiedInside cell;
+        cell.occ = m.occ; cell.kx0 = m.kmin[0]; cell.ky0 = m.kmin[1]; cell.kz0 = m.kmin[2];
+        cell.ny = (unsigned)m.dims[1]; cell.nz = (unsigned)m.dims[2];
+        hit = cast_ray<false>(m.ks, ox, oy, oz, dx, dy, dz, true, range, cell, hx, hy, hz, COUNT ? &nsteps : nullptr);
+      } else {
+        CellOccupiedOnly cell;  // ignoreUnknown = true: unknown cells are walked through
+        cell.m = &m;
+        hit = cast_ray(m.ks, ox, oy, oz, dx, dy, dz, true, range, cell, hx, hy, hz, COUNT ? &nsteps : nullptr);
+      }
       if (COUNT) my_steps += (unsigned long long)nsteps;
       if (!hit) visible = true;
       else {
