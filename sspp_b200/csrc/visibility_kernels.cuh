@@ -151,8 +151,9 @@ __global__ void k_pts_scatter(const float* __restrict__ xyz, int64_t n, const in
 // test itself runs in float with its own rounding, so the bound is relaxed by `tol`, forty times the worst rounding
 // error of that float expression, and the row's y/z extent is widened by a thousandth of a cell: a cell is only
 // left out when no point binned into it can pass the float test.  Returns the binned range [b, e) of the row.
-__device__ __forceinline__ void view_row_range(const ViewRec& R, const PointGrid& g, const int* __restrict__ cell_start, int cz,
-                                               int cy, int& b, int& e) {
+__device__ __noinline__ void view_row_range(const ViewRec* __restrict__ Rg, const PointGrid& g, const int* __restrict__ cell_start,
+                                            int cz, int cy, int& b, int& e) {
+  const ViewRec& R = *Rg;  // in global memory: the callers keep their register copy of the record to themselves
   const double cell = 1.0 / g.inv_cell, widen = cell * 1e-3, big = 1e30;
   const double y0 = cy == 0 ? -big : g.min[1] + cy * cell - widen, y1 = cy == g.n[1] - 1 ? big : g.min[1] + (cy + 1) * cell + widen;
   const double z0 = cz == 0 ? -big : g.min[2] + cz * cell - widen, z1 = cz == g.n[2] - 1 ? big : g.min[2] + (cz + 1) * cell + widen;
@@ -160,7 +161,7 @@ __device__ __forceinline__ void view_row_range(const ViewRec& R, const PointGrid
                zm = fmax(fabs(g.min[2]), fabs(g.min[2] + g.n[2] * cell));
   double xlo = -big, xhi = big;
   bool empty = false;
-#pragma unroll
+#pragma unroll 1
   for (int k = 0; k < 6; ++k) {
     const double pa = R.pl[k][0], pb = R.pl[k][1], pc = R.pl[k][2], pd = R.pl[k][3];
     const double tol = 1e-5 * (fabs(pa) * xm + fabs(pb) * ym + fabs(pc) * zm + fabs(pd)) + 1e-9;
@@ -191,7 +192,7 @@ __global__ void __launch_bounds__(256) k_view_bound(const ViewRec* __restrict__ 
   int n = 0;
   for (int r = lane; r < nrows; r += 32) {
     int b, e;
-    view_row_range(R, g, cell_start, R.c0[2] + r / nyr, R.c0[1] + r % nyr, b, e);
+    view_row_range(views + w, g, cell_start, R.c0[2] + r / nyr, R.c0[1] + r % nyr, b, e);
     n += (e - b + 31) >> 5;
   }
   for (int o = 16; o; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
@@ -201,8 +202,11 @@ __global__ void __launch_bounds__(256) k_view_bound(const ViewRec* __restrict__ 
 // one warp per viewpoint: in-frustum points of the cells its frustum can reach.
 // FILL == false: run the frustum test, keep the ballots, count.  FILL == true (after the scan of the
 // counts): write (viewpoint, binned position) per ray from the stored ballots.
+#ifndef GATHER_MIN_BLOCKS
+#define GATHER_MIN_BLOCKS 6
+#endif
 template <bool FILL>
-__global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__ views, int64_t v0, int nv, PointGrid g,
+__global__ void __launch_bounds__(256, GATHER_MIN_BLOCKS) k_view_gather(const ViewRec* __restrict__ views, int64_t v0, int nv, PointGrid g,
                                                      const int* __restrict__ cell_start, const float4* __restrict__ sp,
                                                      int* __restrict__ ray_count, const long long* __restrict__ ray_off,
                                                      int* __restrict__ ray_view, int* __restrict__ ray_pt,
@@ -222,30 +226,43 @@ __global__ void __launch_bounds__(256) k_view_gather(const ViewRec* __restrict__
   for (int r0 = 0; r0 < nrows; r0 += 32) {
     // the lanes work out the runs of 32 rows side by side, then the warp walks them one after the other
     int rb = 0, re = 0;
-    if (r0 + lane < nrows) view_row_range(R, g, cell_start, R.c0[2] + (r0 + lane) / nyr, R.c0[1] + (r0 + lane) % nyr, rb, re);
+    if (r0 + lane < nrows) view_row_range(views + v0 + w, g, cell_start, R.c0[2] + (r0 + lane) / nyr, R.c0[1] + (r0 + lane) % nyr, rb, re);
     const int nr = min(32, nrows - r0);
     for (int rr = 0; rr < nr; ++rr) {
       const int b = __shfl_sync(0xffffffffu, rb, rr), e = __shfl_sync(0xffffffffu, re, rr);
-      for (int j0 = b; j0 < e; j0 += 32, ++it) {
-        int j = j0 + lane;
-        unsigned bal;
-        if (FILL) {
-          bal = mw[it];
+      if (FILL) {
+        for (int j0 = b; j0 < e; j0 += 32, ++it) {
+          const int j = j0 + lane;
+          const unsigned bal = mw[it];
           if ((bal >> lane) & 1u) {
             long long o = base + filled + __popc(bal & ((1u << lane) - 1u));
             ray_view[o] = w;
             ray_pt[o] = j;
           }
-        } else {
-          bool in = false;
-          if (j < e) {
-            float4 p = sp[j];
-            in = in_frustum_dev(R, p.x, p.y, p.z);
-          }
-          bal = __ballot_sync(0xffffffffu, in);
-          if (lane == 0) mw[it] = bal;
+          filled += __popc(bal);
         }
-        filled += __popc(bal);
+      } else {
+        // four chunks of 32 points per turn: the four loads of a lane are in flight together
+        for (int j0 = b; j0 < e; j0 += 128) {
+          float4 p[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int j = j0 + 32 * u + lane;
+            p[u] = (j < e) ? sp[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          unsigned mine = 0;
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int j = j0 + 32 * u + lane;
+            const bool in = (j < e) && in_frustum_dev(R, p[u].x, p[u].y, p[u].z);
+            const unsigned bal = __ballot_sync(0xffffffffu, in);
+            if (lane == u) mine = bal;
+            filled += __popc(bal);
+          }
+          const int nchunks = min(4, (e - j0 + 31) >> 5);
+          if (lane < nchunks) mw[it + lane] = mine;
+          it += nchunks;
+        }
       }
     }
   }
