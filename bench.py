@@ -389,7 +389,8 @@ def profile_traffic(kernel):
         if "dram__bytes_read.sum" in vals and "dram__bytes_write.sum" in vals:
             out["dram_bytes"] = vals["dram__bytes_read.sum"] + vals["dram__bytes_write.sum"]
             out["lts_bytes"] = vals.get("lts__t_bytes.sum")
-            out["source"] = "%s (ncu --set full of this command; dram__bytes_read.sum + dram__bytes_write.sum, lts__t_bytes.sum)" % os.path.relpath(path, REPO)
+            out["source"] = ("%s (ncu --set full of tools/profile_target.py = this scene and these calls, one warm launch per kernel; "
+                             "dram__bytes_read.sum + dram__bytes_write.sum, lts__t_bytes.sum)" % os.path.relpath(path, REPO))
             break
     return out
 

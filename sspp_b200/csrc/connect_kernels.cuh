@@ -292,6 +292,9 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
 // edge test: one warp per source row
 // ------------------------------------------------------------------------------------------------
 constexpr int EDGE_WARPS = 8;
+#ifndef SSPP_PAIR_COARSE
+#define SSPP_PAIR_COARSE 1  // tuning switch: 0 = pair boxes go to the fine plane without asking the 4x4x4 pyramid first
+#endif
 
 // Does the key box [lo, hi] (absolute keys, inclusive) hold a blocked voxel?  "true" may also mean
 // "cannot tell cheaply" (the box leaves the mapped window): callers then take the exact path.
@@ -456,7 +459,10 @@ __device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float
   if (!coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
     return RAY_FREE;
   if (kx == ekx && ky == eky && kz == ekz) return RAY_FREE;
-  if (fast) {
+#ifndef SSPP_RAY_BOX
+#define SSPP_RAY_BOX 1  // tuning switch: 0 = rays of the lattice stage go to the walk without their own key-box scan
+#endif
+  if (SSPP_RAY_BOX && fast) {
     const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
     const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
     const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
@@ -651,7 +657,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
           pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
           pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
-          (!box_maybe_blocked_coarse(m, lox, hix, loy, hiy, loz, hiz) || !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)))
+          ((SSPP_PAIR_COARSE && !box_maybe_blocked_coarse(m, lox, hix, loy, hiy, loz, hiz)) || !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)))
         needs = false;
     }
     unsigned need = __ballot_sync(0xffffffffu, needs);
