@@ -442,36 +442,15 @@ __device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, doubl
   return true;
 }
 
-// Cheap verdict on one ray before any DDA arithmetic: RAY_FREE / RAY_BLOCKED are final, RAY_WALK
-// means the exact walk has to decide.  `fast` enables the key-box shortcut of line_status_fast.
-// okey: the ray's origin key with its start voxel already known to be free (the row-level start stage
-// computed both; -1 = origin outside the key space), or NULL = derive them here.
-enum { RAY_FREE = 0, RAY_BLOCKED = 1, RAY_WALK = 2 };
-__device__ __forceinline__ int ray_precheck(const DeviceMap& m, bool fast, float ox, float oy, float oz, float ex, float ey,
-                                            float ez, const int* okey) {
-  int kx, ky, kz, ekx, eky, ekz;
-  if (okey) {
-    kx = okey[0]; ky = okey[1]; kz = okey[2];
-    if (kx < 0) return RAY_FREE;
-  } else if (!coord_to_key(m.ks, (double)ox, kx) || !coord_to_key(m.ks, (double)oy, ky) || !coord_to_key(m.ks, (double)oz, kz)) {
-    return RAY_FREE;  // out of key range: upstream leaves the ray empty
-  }
-  if (!coord_to_key(m.ks, (double)ex, ekx) || !coord_to_key(m.ks, (double)ey, eky) || !coord_to_key(m.ks, (double)ez, ekz))
-    return RAY_FREE;
-  if (kx == ekx && ky == eky && kz == ekz) return RAY_FREE;
-#ifndef SSPP_RAY_BOX
-#define SSPP_RAY_BOX 1  // tuning switch: 0 = rays of the lattice stage go to the walk without their own key-box scan
-#endif
-  if (SSPP_RAY_BOX && fast) {
-    const int lox = min(kx, ekx) - (ex < ox ? 1 : 0), hix = max(kx, ekx) + (ex > ox ? 1 : 0);
-    const int loy = min(ky, eky) - (ey < oy ? 1 : 0), hiy = max(ky, eky) + (ey > oy ? 1 : 0);
-    const int loz = min(kz, ekz) - (ez < oz ? 1 : 0), hiz = max(kz, ekz) + (ez > oz ? 1 : 0);
-    if (!box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)) return RAY_FREE;
-  }
-  // the start voxel is the first one the walk tests; with okey it is known to be free (a pair whose ray q
-  // starts in a blocked voxel and is not empty never reaches the ray stage)
-  if (!okey && map_blocked(m, kx, ky, kz)) return RAY_BLOCKED;
-  return RAY_WALK;
+// One ray of the lattice stage, out of line (the walk is the bulk of the edge kernel and inlining it would cost the
+// kernel its occupancy).  okey: the ray's origin key, whose voxel the row stage has already found free (kx < 0: origin
+// outside the key space — upstream leaves such a ray empty), or NULL = derive the key and test the start voxel here.
+__device__ __noinline__ int ray_status(const DeviceMap& m, float ox, float oy, float oz, float ex, float ey, float ez, const int* okey) {
+  BlockedGlobal cell;
+  cell.m = &m;
+  if (!okey) return line_status(m.ks, ox, oy, oz, ex, ey, ez, cell);
+  if (okey[0] < 0) return CELL_FREE;
+  return line_status_from(m.ks, ox, oy, oz, ex, ey, ez, okey[0], okey[1], okey[2], true, cell);
 }
 
 constexpr int RAY_TABLE_MAX = 256;
@@ -484,7 +463,6 @@ struct EdgeSmem {
   EdgeSmemSort sort;
   double far_end[EDGE_WARPS][32][3];  // far-end coordinates of the batch's pairs
   int slots[EDGE_WARPS][32];          // batch slots that still need rays, compacted
-  unsigned queue[EDGE_WARPS][64];     // (slot << 20 | ray) waiting for the exact walk
   int okey[EDGE_WARPS][32][3];        // origin keys of the first 32 rays of the row (they do not depend on the pair)
 };
 
@@ -497,25 +475,6 @@ __device__ __forceinline__ void ray_offset(const EdgeSmem& sm, int q, double& ox
     int iy = rem / sm.lat.n[2], iz = rem - iy * sm.lat.n[2];
     ox = sm.lat.off[0][ix]; oy = sm.lat.off[1][iy]; oz = sm.lat.off[2][iz];
   }
-}
-
-// Exact walks for the first `count` (<= 32) queue entries of this warp; returns the slots found blocked.
-__device__ __forceinline__ unsigned run_walks(const DeviceMap& m, const EdgeSmem& sm, int warp, int lane, int count,
-                                              unsigned blockedmask, double px, double py, double pz) {
-  unsigned bit = 0;
-  if (lane < count) {
-    const unsigned e = sm.queue[warp][lane];
-    const int k = (int)(e >> 20), q = (int)(e & 0xfffffu);
-    if (!((blockedmask >> k) & 1u)) {
-      double ox, oy, oz;
-      ray_offset(sm, q, ox, oy, oz);
-      const double* f = sm.far_end[warp][k];
-      int st = line_status_exact(m, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
-                                 d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)));
-      if (st != CELL_FREE) bit = 1u << k;
-    }
-  }
-  return __reduce_or_sync(0xffffffffu, bit);
 }
 
 // Edge test, one warp per source row.  Work is shed in stages, none of which can change a result
@@ -693,47 +652,32 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
         need &= ~took;
       }
     } else if (need) {
-      // stages 3-4: all (pair, ray) items of the batch flattened over the lanes.  A cheap verdict per
-      // ray first; rays that need the exact walk are queued and walked 32 at a time, so the warp
-      // stays full whatever the number of rays per pair, and a pair found blocked drops its other rays.
+      // stage 3: all (pair, ray) items of the batch flattened over the lanes and walked 32 at a time by the exact
+      // DDA, so the warp stays full whatever the number of rays per pair; a pair found blocked drops the rays it
+      // has left in later turns.  (A key-box test per ray before the walk was measured to cost more than the
+      // walks it saves - S4a 1.57 -> 1.36 ms without it - and is gone.)
       if (needs) sm.slots[warp][__popc(need & ((1u << lane) - 1u))] = lane;
       if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
       __syncwarp();
       const int W = __popc(need) * R;
       const bool have_okey = !COUNT && fast && R <= 32;  // the start stage above ran for this row
       unsigned blockedmask = 0;
-      int qn = 0;
       for (int w0 = 0; w0 < W; w0 += 32) {
         const int w = w0 + lane;
-        int verdict = RAY_FREE, k = 0, q = 0;
+        unsigned bit = 0;
         if (w < W) {
-          const int p = w / R;
-          q = w - p * R;
-          k = sm.slots[warp][p];
+          const int p = w / R, q = w - p * R, k = sm.slots[warp][p];
           if (!((blockedmask >> k) & 1u)) {
             double ox, oy, oz;
             ray_offset(sm, q, ox, oy, oz);
             const double* f = sm.far_end[warp][k];
-            verdict = ray_precheck(m, fast, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
-                                   d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? sm.okey[warp][q] : nullptr);
+            const int st = ray_status(m, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
+                                      d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? sm.okey[warp][q] : nullptr);
+            if (st != CELL_FREE) bit = 1u << k;
           }
         }
-        blockedmask |= __reduce_or_sync(0xffffffffu, verdict == RAY_BLOCKED ? (1u << k) : 0u);
-        const bool push = verdict == RAY_WALK && !((blockedmask >> k) & 1u);
-        const unsigned pb = __ballot_sync(0xffffffffu, push);
-        if (push) sm.queue[warp][qn + __popc(pb & ((1u << lane) - 1u))] = ((unsigned)k << 20) | (unsigned)q;
-        qn += __popc(pb);
-        __syncwarp();
-        if (qn >= 32) {
-          blockedmask |= run_walks(m, sm, warp, lane, 32, blockedmask, px, py, pz);
-          const unsigned moved = (lane + 32 < qn) ? sm.queue[warp][lane + 32] : 0u;
-          __syncwarp();
-          sm.queue[warp][lane] = moved;
-          qn -= 32;
-          __syncwarp();
-        }
+        blockedmask |= __reduce_or_sync(0xffffffffu, bit);
       }
-      if (qn > 0) blockedmask |= run_walks(m, sm, warp, lane, qn, blockedmask, px, py, pz);
       __syncwarp();
       accmask |= need & ~blockedmask;
     }

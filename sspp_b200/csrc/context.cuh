@@ -89,7 +89,7 @@ struct sspp_gpu_ctx {
   bool has_vis = false;
   int64_t vis_nv = 0, vis_total = 0;
   // binning of the model points, kept while the points and the cell size do not change
-  DevBuf pts_cell_start, pts_sorted, vis_views, vis_rayoff, vis_rayview, vis_raypt, vis_flag, vis_order, vis_ordcur;
+  DevBuf pts_cell_start, pts_sorted, vis_views, vis_rayoff, vis_rayview, vis_raypt, vis_flag;
   bool pts_binned = false;
   double pts_cell = 0;
   unsigned long long pts_bbox_host[7] = {0, 0, 0, 0, 0, 0, 0};

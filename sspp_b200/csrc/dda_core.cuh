@@ -122,17 +122,23 @@ SSPP_HD void dda_axis(const KeySpace& ks, float dir, float origin, int key, bool
 //  * upstream finds argmin(tMax) to advance, then min(tMax) to compare with the length, then
 //    argmin again on the unchanged values: one argmin per iteration serves both (the axis the tie
 //    rule picks always holds the minimum value).
+//
+// line_status_from: the same walk for a caller that already holds the origin key (kx, ky, kz valid) and, with
+// start_known_free, already knows that the start voxel does not stop the walk — the edge kernel's row stage
+// has both for every ray of a row.  line_status derives the origin key and calls it.
 template <class Cell>
-SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float ex, float ey, float ez, Cell& cell,
-                        int* steps = nullptr) {
-  int kx, ky, kz, ekx, eky, ekz;
-  if (!coord_to_key(ks, (double)ox, kx) || !coord_to_key(ks, (double)oy, ky) || !coord_to_key(ks, (double)oz, kz) ||
-      !coord_to_key(ks, (double)ex, ekx) || !coord_to_key(ks, (double)ey, eky) || !coord_to_key(ks, (double)ez, ekz))
+SSPP_HD int line_status_from(const KeySpace& ks, float ox, float oy, float oz, float ex, float ey, float ez, int kx, int ky, int kz,
+                             bool start_known_free, Cell& cell, int* steps = nullptr) {
+  int ekx, eky, ekz;
+  if (!coord_to_key(ks, (double)ex, ekx) || !coord_to_key(ks, (double)ey, eky) || !coord_to_key(ks, (double)ez, ekz))
     return CELL_FREE;
   if (kx == ekx && ky == eky && kz == ekz) return CELL_FREE;
-  if (steps) ++*steps;
-  int st = cell(kx, ky, kz);
-  if (st) return st;
+  int st;
+  if (!start_known_free) {
+    if (steps) ++*steps;
+    st = cell(kx, ky, kz);
+    if (st) return st;
+  }
 
   float dx = f_sub(ex, ox), dy = f_sub(ey, oy), dz = f_sub(ez, oz);
   float length = f_sqrt(f_add(f_add(f_mul(dx, dx), f_mul(dy, dy)), f_mul(dz, dz)));
@@ -169,6 +175,14 @@ SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float 
     if (st) return st;
   }
   return CELL_FREE;
+}
+
+template <class Cell>
+SSPP_HD int line_status(const KeySpace& ks, float ox, float oy, float oz, float ex, float ey, float ez, Cell& cell,
+                        int* steps = nullptr) {
+  int kx, ky, kz;
+  if (!coord_to_key(ks, (double)ox, kx) || !coord_to_key(ks, (double)oy, ky) || !coord_to_key(ks, (double)oz, kz)) return CELL_FREE;
+  return line_status_from(ks, ox, oy, oz, ex, ey, ez, kx, ky, kz, false, cell, steps);
 }
 
 // OccupancyOcTreeBase::castRay.  `cell` returns CELL_FREE / CELL_OCCUPIED / CELL_UNKNOWN for a key.

@@ -125,7 +125,7 @@ void sspp_gpu_destroy(sspp_gpu_ctx* ctx) {
                     &ctx->acc, &ctx->deg, &ctx->row_ptr, &ctx->col_idx, &ctx->counters, &ctx->scan_tmp, &ctx->lattice, &ctx->work_rows,
                     &ctx->q0, &ctx->q1, &ctx->q2, &ctx->q3, &ctx->q4, &ctx->pts, &ctx->vis_cnt, &ctx->vis_ptr,
                     &ctx->vis_idx, &ctx->vis_poses, &ctx->vis_counters, &ctx->vis_words, &ctx->vis_mask, &ctx->pts_cell_start, &ctx->pts_sorted,
-                    &ctx->vis_views, &ctx->vis_rayoff, &ctx->vis_rayview, &ctx->vis_raypt, &ctx->vis_flag, &ctx->vis_order, &ctx->vis_ordcur, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
+                    &ctx->vis_views, &ctx->vis_rayoff, &ctx->vis_rayview, &ctx->vis_raypt, &ctx->vis_flag, &ctx->dd_poses, &ctx->dd_xyz, &ctx->dd_state,
                     &ctx->dd_pend, &ctx->dd_dup, &ctx->dd_keep, &ctx->dd_misc};
   for (DevBuf* b : bufs) b->release();
   ctx->chunk_base.release();
@@ -1528,9 +1528,6 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
   int* words = ctx->vis_words.as<int>();
   long long* word_off = (long long*)(ctx->vis_words.as<char>() + (((size_t)nv * 4 + 7) & ~(size_t)7));
   CK(ctx->vis_counters.reserve(8 * 8));
-  CK(ctx->cell_cursor.reserve((size_t)(ncells + 1) * 4));
-  CK(ctx->vis_ordcur.reserve((size_t)(ncells + 1) * 4));
-  CK(ctx->vis_order.reserve((size_t)nv * 4));
   long long* vis_ptr = ctx->vis_ptr.as<long long>();
 
   // The mask / ray / index buffers keep their size from call to call.  The pass is queued in one go with
@@ -1545,15 +1542,7 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
     CK(cudaMemsetAsync(ctx->vis_counters.p, 0, 8 * 8, st));
     k_view_setup<<<ceil_div(nv, 128), 128, 0, st>>>(ctx->vis_poses.as<double>(), nv, vh, hw, np_dist, fp_dist, g, views);
     LAUNCHED(ctx);
-    // processing order: viewpoints by the cell of their sensor (counting sort over the point grid's cells)
-    CK(cudaMemsetAsync(ctx->cell_cursor.p, 0, (size_t)(ncells + 1) * 4, st));
-    k_view_order_hist<<<ceil_div(nv, 256), 256, 0, st>>>(views, (int)nv, g, ctx->cell_cursor.as<int>());
-    LAUNCHED(ctx);
-    { int rc = scan_exclusive<int>(ctx, ctx->cell_cursor.as<int>(), ncells, ctx->vis_ordcur.as<int>()); if (rc) return rc; }
-    k_view_order_scatter<<<ceil_div(nv, 256), 256, 0, st>>>(views, (int)nv, g, ctx->vis_ordcur.as<int>(), ctx->vis_order.as<int>());
-    LAUNCHED(ctx);
-    const int* order = ctx->vis_order.as<int>();
-    k_view_bound<<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, (int)nv, g, pcs, order, words);
+    k_view_bound<<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, (int)nv, g, pcs, words);
     LAUNCHED(ctx);
     { int rc = scan_exclusive<long long>(ctx, words, nv, word_off); if (rc) return rc; }
     uint32_t* vmask = ctx->vis_mask.as<uint32_t>();
@@ -1562,11 +1551,11 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
     uint8_t* vis = ctx->vis_flag.as<uint8_t>();
     CK(cudaMemsetAsync(ray_count, 0, (size_t)nv * 4 * 2, st));
     k_view_gather<false><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, pcs, sp, ray_count, nullptr, nullptr,
-                                                                nullptr, word_off, vmask, mask_cap, ray_cap, order);
+                                                                nullptr, word_off, vmask, mask_cap, ray_cap);
     LAUNCHED(ctx);
     { int rc = scan_exclusive<long long>(ctx, ray_count, nv, ray_off); if (rc) return rc; }
     k_view_gather<true><<<ceil_div(nv * 32, 256), 256, 0, st>>>(views, 0, (int)nv, g, pcs, sp, nullptr, ray_off, ray_view, ray_pt,
-                                                               word_off, vmask, mask_cap, ray_cap, order);
+                                                               word_off, vmask, mask_cap, ray_cap);
     LAUNCHED(ctx);
     CK(cudaEventRecord(ctx->vev[2], st));
     // --- occlusion rays

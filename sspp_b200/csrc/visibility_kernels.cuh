@@ -145,22 +145,6 @@ __global__ void k_pts_scatter(const float* __restrict__ xyz, int64_t n, const in
   sp[pos] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], __int_as_float((int)i));
 }
 
-// Processing order of the viewpoints: by the cell of the point grid their sensor sits in, so that the warps of a
-// CTA (consecutive entries of the order) walk the same cell rows at the same time and find each other's points in
-// L1.  Results are written by viewpoint index, so the order changes no output.  Counting sort: histogram, scan, scatter.
-__device__ __forceinline__ int view_cell(const ViewRec& R, const PointGrid& g) {
-  const int cx = pgrid_axis(g, (double)R.T[0], 0), cy = pgrid_axis(g, (double)R.T[1], 1), cz = pgrid_axis(g, (double)R.T[2], 2);
-  return (cz * g.n[1] + cy) * g.n[0] + cx;
-}
-__global__ void k_view_order_hist(const ViewRec* __restrict__ views, int nv, PointGrid g, int* count) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v < nv) atomicAdd(count + view_cell(views[v], g), 1);
-}
-__global__ void k_view_order_scatter(const ViewRec* __restrict__ views, int nv, PointGrid g, int* cursor, int* __restrict__ order) {
-  const int v = blockIdx.x * blockDim.x + threadIdx.x;
-  if (v < nv) order[atomicAdd(cursor + view_cell(views[v], g), 1)] = v;
-}
-
 // The points a viewpoint has to test: for every (z, y) row of cells inside the frustum's bounding box, the run of x
 // cells the frustum can reach.  Each of the six planes bounds x on that row: a point (x, y, z) of the row passes
 // plane k only if a x + min over the row's y/z extent of (b y + c z) + d <= 0, which is a half-line in x.  The frustum
@@ -200,11 +184,9 @@ __device__ __noinline__ void view_row_range(const ViewRec* __restrict__ Rg, cons
 // count pass stores its ballots there and the fill pass reads them back instead of loading the points and running
 // the six-plane test a second time.  One warp per viewpoint, one lane per row.
 __global__ void __launch_bounds__(256) k_view_bound(const ViewRec* __restrict__ views, int nv, PointGrid g,
-                                                    const int* __restrict__ cell_start, const int* __restrict__ order,
-                                                    int* __restrict__ words) {
-  const int slot = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
-  if (slot >= nv) return;
-  const int w = order[slot];
+                                                    const int* __restrict__ cell_start, int* __restrict__ words) {
+  const int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (w >= nv) return;
   const ViewRec& R = views[w];
   const int nyr = R.c1[1] - R.c0[1] + 1, nrows = nyr * (R.c1[2] - R.c0[2] + 1);
   int n = 0;
@@ -229,11 +211,10 @@ __global__ void __launch_bounds__(256, GATHER_MIN_BLOCKS) k_view_gather(const Vi
                                                      int* __restrict__ ray_count, const long long* __restrict__ ray_off,
                                                      int* __restrict__ ray_view, int* __restrict__ ray_pt,
                                                      const long long* __restrict__ word_off, uint32_t* __restrict__ mask,
-                                                     long long mask_cap, long long ray_cap, const int* __restrict__ order) {
-  const int slot = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+                                                     long long mask_cap, long long ray_cap) {
+  const int w = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
   int lane = threadIdx.x & 31;
-  if (slot >= nv) return;
-  const int w = order[slot];
+  if (w >= nv) return;
   // the buffers keep their size from call to call; when this call's sizes outgrow them every kernel of
   // the pass returns at once and the host, at its one synchronisation, grows them and repeats the pass
   if (word_off[nv] > mask_cap || (FILL && ray_off[nv] > ray_cap)) return;
