@@ -66,9 +66,9 @@ struct __align__(32) NodeRec {
   double x, y, z;
   long long idx;  // list index of the node
 };
-__device__ __forceinline__ NodeRec load_node(const NodeRec* p) {
-  const double2 a = *reinterpret_cast<const double2*>(p);
-  const double2 b = *(reinterpret_cast<const double2*>(p) + 1);
+__device__ __forceinline__ NodeRec load_node(const NodeRec* p) {  // read-only path: the loads may be hoisted over stores
+  const double2 a = __ldg(reinterpret_cast<const double2*>(p));
+  const double2 b = __ldg(reinterpret_cast<const double2*>(p) + 1);
   NodeRec r;
   r.x = a.x; r.y = a.y; r.z = b.x;
   r.idx = __double_as_longlong(b.y);
@@ -236,16 +236,26 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
       for (int yy = max(cy - 1, 0); yy <= min(cy + 1, a.g.n[1] - 1); ++yy) {
         int base = (zz * a.g.n[1] + yy) * a.g.n[0];
         int b = a.cell_start[base + x0], e = a.cell_start[base + x1 + 1];
-        for (int j = b; j < e; ++j) {
-          if (j == s) continue;
-          const NodeRec o = load_node(a.sn + j);
-          int pc = pair_class(o.x, o.y, o.z, px, py, pz, a.r2max, a.mode);
-          if (FILL) {
-            if (pc) cand[w++] = make_int2(j, (int)o.idx | (pc == 2 ? (int)0x80000000 : 0));
-          } else {
-            if (slots && pc && cnt < a.slot) cand[w + cnt] = make_int2(j, (int)o.idx | (pc == 2 ? (int)0x80000000 : 0));
-            cnt += (pc != 0);
-            tst += (pc == 1);
+        // two candidates per turn: both records are requested before either is looked at (the pass is bound by
+        // the latency of these loads)
+        for (int j = b; j < e; j += 2) {
+          const bool two = j + 1 < e;
+          const NodeRec o0 = load_node(a.sn + j);
+          const NodeRec o1 = load_node(a.sn + (two ? j + 1 : j));
+#pragma unroll
+          for (int u = 0; u < 2; ++u) {
+            if (u == 1 && !two) break;
+            const int jj = j + u;
+            if (jj == s) continue;
+            const NodeRec& o = u ? o1 : o0;
+            int pc = pair_class(o.x, o.y, o.z, px, py, pz, a.r2max, a.mode);
+            if (FILL) {
+              if (pc) cand[w++] = make_int2(jj, (int)o.idx | (pc == 2 ? (int)0x80000000 : 0));
+            } else {
+              if (slots && pc && cnt < a.slot) cand[w + cnt] = make_int2(jj, (int)o.idx | (pc == 2 ? (int)0x80000000 : 0));
+              cnt += (pc != 0);
+              tst += (pc == 1);
+            }
           }
         }
       }
@@ -454,6 +464,8 @@ __device__ __noinline__ int ray_status(const DeviceMap& m, float ox, float oy, f
 }
 
 constexpr int RAY_TABLE_MAX = 256;
+constexpr int START_RAYS_MAX = 128;  // lattices up to this many rays get the row-level start-voxel stage (27, 48, 100 ...)
+inline size_t edge_okey_bytes(int rays) { return (size_t)EDGE_WARPS * 3 * sizeof(int) * (size_t)(rays < START_RAYS_MAX ? rays : START_RAYS_MAX); }
 struct EdgeSmemSort {
   int2 buf[EDGE_WARPS][32];
 };
@@ -463,7 +475,6 @@ struct EdgeSmem {
   EdgeSmemSort sort;
   double far_end[EDGE_WARPS][32][3];  // far-end coordinates of the batch's pairs
   int slots[EDGE_WARPS][32];          // batch slots that still need rays, compacted
-  int okey[EDGE_WARPS][32][3];        // origin keys of the first 32 rays of the row (they do not depend on the pair)
 };
 
 __device__ __forceinline__ void ray_offset(const EdgeSmem& sm, int q, double& ox, double& oy, double& oz) {
@@ -544,11 +555,13 @@ __global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long l
   if (lane == 0) deg[r] = n;
 }
 
-template <bool COUNT>
-__device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& m, EdgeSmem& sm, const int warp, const int lane,
+// NW: 32-ray words of the start-voxel stage the kernel is compiled for (1: lattices up to 32 rays, the common
+// case, with the mask in one register; 4: up to START_RAYS_MAX)
+template <bool COUNT, int NW>
+__device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& m, EdgeSmem& sm, int* okey, const int warp, const int lane,
                                          const int t, const long long* __restrict__ cand_off,
                                          const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
-                                         int* __restrict__ deg, unsigned long long* counters) {
+                                         int* __restrict__ deg, unsigned long long* counters, unsigned& n_box, unsigned& n_lat) {
   const RayLattice& lat = sm.lat;
   const int s = t;  // work lists hold sorted positions
   const NodeRec me = load_node(a.sn + s);
@@ -564,25 +577,34 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
   // Row-level verdicts: every ray starts at p + offset whatever the pair, and the start voxel is the
   // first one a walk tests.  A ray whose start voxel is blocked therefore rejects every pair of this
   // row for which that ray is not empty (its end key differs from its start key).
-  unsigned startmask = 0;
-  if (!COUNT && fast && R <= 32) {
-    bool blk = false;
-    if (lane < R) {
-      double ox, oy, oz;
-      ray_offset(sm, lane, ox, oy, oz);
-      int kx = -1, ky = -1, kz = -1;
-      if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
-          coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz))
-        blk = map_blocked(m, kx, ky, kz) != 0;
-      else
-        kx = -1;
-      sm.okey[warp][lane][0] = kx; sm.okey[warp][lane][1] = ky; sm.okey[warp][lane][2] = kz;
+  unsigned startmask[NW];
+#pragma unroll
+  for (int c = 0; c < NW; ++c) startmask[c] = 0;
+  bool any_start = false;
+  const bool start_stage = !COUNT && fast && R <= NW * 32;
+  if (start_stage) {
+#pragma unroll
+    for (int c = 0; c < NW; ++c) {
+      if (c * 32 >= R) break;
+      const int q = c * 32 + lane;
+      bool blk = false;
+      if (q < R) {
+        double ox, oy, oz;
+        ray_offset(sm, q, ox, oy, oz);
+        int kx = -1, ky = -1, kz = -1;
+        if (coord_to_key(m.ks, (double)d2f(d_add(px, ox)), kx) && coord_to_key(m.ks, (double)d2f(d_add(py, oy)), ky) &&
+            coord_to_key(m.ks, (double)d2f(d_add(pz, oz)), kz))
+          blk = map_blocked(m, kx, ky, kz) != 0;
+        else
+          kx = -1;
+        okey[3 * q] = kx; okey[3 * q + 1] = ky; okey[3 * q + 2] = kz;
+      }
+      startmask[c] = __ballot_sync(0xffffffffu, blk);
+      any_start |= startmask[c] != 0;
     }
-    startmask = __ballot_sync(0xffffffffu, blk);
     __syncwarp();
   }
   int nacc = 0;
-  unsigned n_box = 0, n_lat = 0;
   unsigned long long nsteps = 0;
   for (int base = 0; base < n; base += 32) {
     const int nb = min(32, n - base);
@@ -595,18 +617,20 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     bool rejected = false;
     bool needs = mine_valid && !same;
     // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
-    if (needs && startmask) {
-      for (unsigned mb = startmask; mb; mb &= mb - 1) {
-        const int q = __ffs(mb) - 1;
-        double ox, oy, oz;
-        ray_offset(sm, q, ox, oy, oz);
-        int ekx, eky, ekz;
-        if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
-            coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
-            (ekx != sm.okey[warp][q][0] || eky != sm.okey[warp][q][1] || ekz != sm.okey[warp][q][2])) {
-          needs = false;
-          rejected = true;
-          break;
+    if (needs && any_start) {
+#pragma unroll
+      for (int c = 0; c < NW; ++c) {
+        for (unsigned mb = startmask[c]; mb && needs; mb &= mb - 1) {
+          const int q = c * 32 + __ffs(mb) - 1;
+          double ox, oy, oz;
+          ray_offset(sm, q, ox, oy, oz);
+          int ekx, eky, ekz;
+          if (coord_to_key(m.ks, (double)d2f(d_add(qx, ox)), ekx) && coord_to_key(m.ks, (double)d2f(d_add(qy, oy)), eky) &&
+              coord_to_key(m.ks, (double)d2f(d_add(qz, oz)), ekz) &&
+              (ekx != okey[3 * q] || eky != okey[3 * q + 1] || ekz != okey[3 * q + 2])) {
+            needs = false;
+            rejected = true;
+          }
         }
       }
     }
@@ -660,7 +684,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
       __syncwarp();
       const int W = __popc(need) * R;
-      const bool have_okey = !COUNT && fast && R <= 32;  // the start stage above ran for this row
+      const bool have_okey = start_stage;  // the start stage above ran for this row
       unsigned blockedmask = 0;
       for (int w0 = 0; w0 < W; w0 += 32) {
         const int w = w0 + lane;
@@ -672,7 +696,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
             ray_offset(sm, q, ox, oy, oz);
             const double* f = sm.far_end[warp][k];
             const int st = ray_status(m, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
-                                      d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? sm.okey[warp][q] : nullptr);
+                                      d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? okey + 3 * q : nullptr);
             if (st != CELL_FREE) bit = 1u << k;
           }
         }
@@ -686,8 +710,6 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
   }
   if (lane == 0) {
     deg[r] = nacc;
-    if (n_box) atomicAdd(counters + 5, (unsigned long long)n_box);
-    if (n_lat) atomicAdd(counters + 6, (unsigned long long)n_lat);
   }
   if (COUNT) {
     for (int o = 16; o; o >>= 1) nsteps += __shfl_xor_sync(0xffffffffu, nsteps, o);
@@ -698,12 +720,15 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
 
 // Persistent edge kernel: a fixed grid (EDGE_MIN_BLOCKS CTAs per SM); every warp draws the next work
 // row with a ticket, so a row that needs many walks does not hold seven finished warps hostage.
-template <bool COUNT>
+template <bool COUNT, int NW>
 __global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
 k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
         const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
         int* __restrict__ deg, unsigned long long* counters, long long pair_cap, int chunk) {
   __shared__ EdgeSmem sm;
+  // origin keys of the row's rays (they do not depend on the pair), 3 ints per ray and warp: dynamic, sized by the
+  // lattice (edge_okey_bytes), so that the common 27-ray lattice leaves the space to L1
+  extern __shared__ int okey_all[];
   if (pairs_unusable(a, cand_off, counters, pair_cap)) return;
   RayLattice& lat = sm.lat;
   for (int i = threadIdx.x; i < (int)(sizeof(RayLattice) / 4); i += blockDim.x) ((uint32_t*)&lat)[i] = ((const uint32_t*)lat_g)[i];
@@ -719,13 +744,20 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned long long n_work = counters[16 + chunk];
+  unsigned n_box = 0, n_lat = 0;
   work_rows += a.chunk_lo[chunk];
   for (;;) {
     unsigned long long i = 0;
     if (lane == 0) i = atomicAdd(counters + 32 + chunk, 1ull);
     i = __shfl_sync(0xffffffffu, i, 0);
     if (i >= n_work) break;
-    edge_row<COUNT>(a, m, sm, warp, lane, work_rows[i], cand_off, candA, candB, acc, deg, counters);
+    edge_row<COUNT, NW>(a, m, sm, okey_all + warp * 3 * min(lat.rays, START_RAYS_MAX), warp, lane, work_rows[i], cand_off, candA, candB, acc,
+                    deg, counters, n_box, n_lat);
+  }
+  // statistics: one atomic per warp and kernel, not per row
+  if (lane == 0) {
+    if (n_box) atomicAdd(counters + 5, (unsigned long long)n_box);
+    if (n_lat) atomicAdd(counters + 6, (unsigned long long)n_lat);
   }
 }
 

@@ -766,16 +766,14 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
           if (const char* env = getenv("SSPP_PUSH_ROOM")) room = std::max(0, atoi(env));
         }
         const int blocks = std::max(ctx->sm_count, ctx->sm_count * EDGE_MIN_BLOCKS - room);
-        if (count_steps)
-          k_edges<true><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
-                                                            ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
-                                                            ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
-                                                            ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c);
-        else
-          k_edges<false><<<blocks, EDGE_WARPS * 32, 0, st>>>(a, ctx->map, ctx->lattice.as<RayLattice>(),
-                                                             ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(),
-                                                             ctx->candA.as<int2>(), ctx->candB.as<int2>(), ctx->acc.as<int>(),
-                                                             ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c);
+#define SSPP_LAUNCH_EDGES(COUNT, NW)                                                                                         \
+  k_edges<COUNT, NW><<<blocks, EDGE_WARPS * 32, edge_okey_bytes(lat.rays), st>>>(                                           \
+      a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(), ctx->candA.as<int2>(), \
+      ctx->candB.as<int2>(), ctx->acc.as<int>(), ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c)
+        if (count_steps) SSPP_LAUNCH_EDGES(true, 1);  // the instrumented variant has no start stage
+        else if (lat.rays <= 32) SSPP_LAUNCH_EDGES(false, 1);
+        else SSPP_LAUNCH_EDGES(false, START_RAYS_MAX / 32);
+#undef SSPP_LAUNCH_EDGES
         LAUNCHED(ctx);
       }
       if (c == K - 1) CK(cudaEventRecord(ctx->ev[3], st));
