@@ -226,7 +226,7 @@ int sspp_gpu_connect_result_device(sspp_gpu_ctx* ctx, const int64_t** row_ptr_de
 int sspp_gpu_connect_nodes_host(sspp_gpu_ctx* ctx, const double* xyz, int64_t n, const sspp_connect_params* params,
                                 int64_t* row_ptr, int32_t* col_idx, int64_t col_capacity, sspp_connect_stats* stats);
 /* The same on the nodes already set (sspp_gpu_set_nodes / _device): connect + host CSR out.  Above 65 536
- * rows the edge test and the compaction run in row chunks (sizes 4:3:2:1) and every finished chunk is
+ * rows the edge test and the compaction run in six row chunks of falling size and every finished chunk is
  * copied to the host buffers (pin them for the copies to be asynchronous) while the next one runs. */
 int sspp_gpu_connect_to_host(sspp_gpu_ctx* ctx, const sspp_connect_params* params, int64_t* row_ptr, int32_t* col_idx,
                              int64_t col_capacity, sspp_connect_stats* stats);

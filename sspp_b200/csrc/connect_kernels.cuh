@@ -440,11 +440,13 @@ __device__ __forceinline__ void lane_offset(const RayLattice& lat, int lig, doub
 // bound the rest: start keys in [key(f(t+first)), key(f(t+last))], end keys likewise for s; plus the
 // one-voxel overshoot beyond the end on the side the pair travels to (none when s == t: then every
 // ray has a zero direction component on this axis).  False when a key leaves the 16-bit space.
-__device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, double s, double off_first, double off_last,
-                                             int& lo, int& hi) {
-  int o_lo, o_hi, e_lo, e_hi;
-  if (!coord_to_key(ks, (double)d2f(d_add(t, off_first)), o_lo) || !coord_to_key(ks, (double)d2f(d_add(t, off_last)), o_hi) ||
-      !coord_to_key(ks, (double)d2f(d_add(s, off_first)), e_lo) || !coord_to_key(ks, (double)d2f(d_add(s, off_last)), e_hi))
+// o_lo / o_hi: the keys of the row's own end of the box (f(t + off_first), f(t + off_last)), the same for every pair of
+// the row and computed once per row; -1 = outside the key space.
+__device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, double s, double off_first, double off_last, int o_lo,
+                                             int o_hi, int& lo, int& hi) {
+  int e_lo, e_hi;
+  if (o_lo < 0 || o_hi < 0 || !coord_to_key(ks, (double)d2f(d_add(s, off_first)), e_lo) ||
+      !coord_to_key(ks, (double)d2f(d_add(s, off_last)), e_hi))
     return false;
   if (s > t) { lo = o_lo; hi = e_hi + 1; }
   else if (s < t) { lo = e_lo - 1; hi = o_hi; }
@@ -604,6 +606,19 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     }
     __syncwarp();
   }
+  // the row's own end of every pair key box: six keys (low / high lattice offset per axis), one lane each
+  int rk[6] = {-1, -1, -1, -1, -1, -1};
+  if (!COUNT && fast) {
+    int mine = -1;
+    if (lane < 6) {
+      const int ax = lane >> 1;
+      const double pv = ax == 0 ? px : (ax == 1 ? py : pz);
+      const double ov = (lane & 1) ? lat.off[ax][lat.n[ax] - 1] : lat.off[ax][0];
+      if (!coord_to_key(m.ks, (double)d2f(d_add(pv, ov)), mine)) mine = -1;
+    }
+#pragma unroll
+    for (int i = 0; i < 6; ++i) rk[i] = __shfl_sync(0xffffffffu, mine, i);
+  }
   int nacc = 0;
   unsigned long long nsteps = 0;
   for (int base = 0; base < n; base += 32) {
@@ -637,9 +652,9 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     // stage 2b: the pair's key box (one lane per pair)
     if (!COUNT && fast && needs) {
       int lox, hix, loy, hiy, loz, hiz;
-      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
-          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
-          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
+      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], rk[0], rk[1], lox, hix) &&
+          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], rk[2], rk[3], loy, hiy) &&
+          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], rk[4], rk[5], loz, hiz) &&
           ((SSPP_PAIR_COARSE && !box_maybe_blocked_coarse(m, lox, hix, loy, hiy, loz, hiz)) || !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)))
         needs = false;
     }
@@ -765,6 +780,32 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
 // the accepted prefix k_edges left in acc[].  Slot mode, rows that needed no ray: all pairs of the slot
 // are edges — rank-sorted by list index straight from the pair slot (the row never went through acc[]).
 constexpr int COMPACT_LANES = 8;
+// Rank sort of one row inside its eight lanes: every lane keeps its NI keys (d <= 8 NI; slot <= 64, so NI <= 8) in
+// registers and the group passes all keys round by shuffle, so the slot is read once.  List indices are distinct:
+// the rank of a key is the number of smaller keys.
+template <int NI>
+__device__ __forceinline__ void compact_rank_sort(const int2* __restrict__ pairs, int d, int sub, int* __restrict__ out) {
+  const unsigned gmask = 0xffu << ((threadIdx.x & 31) & ~7);
+  int keys[NI], rank[NI];
+#pragma unroll
+  for (int i = 0; i < NI; ++i) {
+    const int e = sub + COMPACT_LANES * i;
+    keys[i] = e < d ? (pairs[e].y & 0x7fffffff) : 0x7fffffff;
+    rank[i] = 0;
+  }
+#pragma unroll
+  for (int i = 0; i < NI; ++i) {
+#pragma unroll
+    for (int l = 0; l < COMPACT_LANES; ++l) {
+      const int v = __shfl_sync(gmask, keys[i], l, COMPACT_LANES);
+#pragma unroll
+      for (int j = 0; j < NI; ++j) rank[j] += (v < keys[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NI; ++j)
+    if (sub + COMPACT_LANES * j < d) out[rank[j]] = keys[j];
+}
 __global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off, const int* __restrict__ deg,
                           const long long* __restrict__ row_ptr, const int* __restrict__ acc, const int2* __restrict__ candA,
                           const uint8_t* __restrict__ row_free, int* __restrict__ col, const unsigned long long* counters,
@@ -777,11 +818,16 @@ __global__ void k_compact(ConnectArgs a, const long long* __restrict__ cand_off,
   const long long src = a.slot ? (long long)r * a.slot : cand_off[r], dst = row_ptr[r];
   const int d = deg[r];
   if (a.slot && !(a.use_map && !row_free[r])) {
-    for (int e = sub; e < d; e += COMPACT_LANES) {
-      const int key = candA[src + e].y & 0x7fffffff;
-      int rank = 0;
-      for (int k = 0; k < d; ++k) rank += ((candA[src + k].y & 0x7fffffff) < key);
-      col[dst + rank] = key;
+    switch ((d + COMPACT_LANES - 1) / COMPACT_LANES) {
+      case 0: break;
+      case 1: compact_rank_sort<1>(candA + src, d, sub, col + dst); break;
+      case 2: compact_rank_sort<2>(candA + src, d, sub, col + dst); break;
+      case 3: compact_rank_sort<3>(candA + src, d, sub, col + dst); break;
+      case 4: compact_rank_sort<4>(candA + src, d, sub, col + dst); break;
+      case 5: compact_rank_sort<5>(candA + src, d, sub, col + dst); break;
+      case 6: compact_rank_sort<6>(candA + src, d, sub, col + dst); break;
+      case 7: compact_rank_sort<7>(candA + src, d, sub, col + dst); break;
+      default: compact_rank_sort<8>(candA + src, d, sub, col + dst); break;
     }
     return;
   }

@@ -218,20 +218,25 @@ SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float di
   // squared distance of the current voxel centre from the origin, one term per axis: upstream rebuilds
   // all three every step; only the axis that moved changes, so the other two terms are kept
   // (each term is the float product (c - o)^2 widened to double; the sum keeps upstream's order).
-  // The test cannot fire during the first steps: the origin lies in the start voxel (its centre is
-  // within res/2 per axis) and every step moves the centre by res along one axis, so after n steps
-  // the centre is within (n + 1.5) res of the origin; while that stays half a voxel below max_range
-  // the bookkeeping is skipped, and the three terms are rebuilt from the current keys when it starts
-  // (each term depends on the current key of its axis only, so nothing is lost).
-  int safe = 0;  // steps during which the range test is known not to fire
-  if (max_range_set) {
-    const double v = floor(d_sub(d_div(max_range, ks.res), 2.0));
-    safe = v > 0.0 ? (v < 262144.0 ? (int)v : 262144) : 0;
-  }
+  // The test cannot fire while the ray is still well short of its range: a step crosses a voxel face at ray
+  // parameter t (the tMax it picks; the direction is normalised, so t is a distance from the origin), the voxel
+  // it enters holds that crossing point, and a voxel's centre is never more than 0.87 res from a point of the
+  // voxel - so the centre is within t + 0.87 res of the origin.  While t <= max_range - res the bookkeeping is
+  // skipped (the 0.13 res left over dwarfs every rounding error involved), and the three terms are rebuilt from
+  // the current keys when it starts (each term depends on the current key of its axis only, so nothing is lost;
+  // t never decreases, so once started it stays on).
+  const double range_guard = d_sub(max_range, ks.res);
   bool ranged = false;  // qx, qy, qz hold the terms of the current voxel
   double qx = 0.0, qy = 0.0, qz = 0.0;
   for (int it = 0; it < 262144; ++it) {
-    const bool check = max_range_set && it >= safe;
+    // upstream's tie rule: x only if strictly below both, y only if strictly below z, else z.  The
+    // three per-axis branches are written as selects: the lanes of a warp step along different axes,
+    // and three divergent branches would each run at a third of the warp.
+    const bool d0 = (tx < ty) && (tx < tz);
+    const bool d1 = !(tx < ty) && (ty < tz);
+    const bool d2 = !d0 && !d1;
+    const double tcur = d0 ? tx : (d1 ? ty : tz);  // == min(tx, ty, tz): where the ray leaves the current voxel
+    const bool check = max_range_set && (ranged || tcur > range_guard);
     if (check && !ranged) {
       float ddx = f_sub(d2f(key_to_coord(ks, kx)), ox), ddy = f_sub(d2f(key_to_coord(ks, ky)), oy),
             ddz = f_sub(d2f(key_to_coord(ks, kz)), oz);
@@ -240,17 +245,11 @@ SSPP_HD bool cast_ray(const KeySpace& ks, float ox, float oy, float oz, float di
       qz = (double)f_mul(ddz, ddz);
       ranged = true;
     }
-    // upstream's tie rule: x only if strictly below both, y only if strictly below z, else z.  The
-    // three per-axis branches are written as selects: the lanes of a warp step along different axes,
-    // and three divergent branches would each run at a third of the warp.
-    const bool d0 = (tx < ty) && (tx < tz);
-    const bool d1 = !(tx < ty) && (ty < tz);
-    const bool d2 = !d0 && !d1;
     const int ksel = d0 ? kx : (d1 ? ky : kz);
     const int ssel = d0 ? sx : (d1 ? sy : sz);
     if (EDGE && ((ssel < 0 && ksel == 0) || (ssel > 0 && ksel == 65535))) return false;  // leaving the key space
     const int kn = ksel + ssel;
-    const double tn = d_add(d0 ? tx : (d1 ? ty : tz), d0 ? dtx : (d1 ? dty : dtz));
+    const double tn = d_add(tcur, d0 ? dtx : (d1 ? dty : dtz));
     kx = d0 ? kn : kx;
     ky = d1 ? kn : ky;
     kz = d2 ? kn : kz;

@@ -632,16 +632,21 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   // row chunks: only when the CSR goes straight to host buffers and the pass is large enough to pipeline
   int K = 1;
   if (sink && nrows >= (1 << 16)) {
-    K = 4;
+    // host sink: with the edge test at ~1.2 ms the call is bound by the D2H copy of the CSR (71 MB at S4a), so the sooner
+    // the first chunk is final the better: six chunks (6:5:4:3:2:1) measured best (1 / 2 / 4 / 6 / 8: 3.61 / 3.17 / 2.90 /
+    // 2.82 / 2.89 ms end to end); the peer variant keeps four
+    K = sink->peers ? 4 : 6;
     if (const char* env = getenv("SSPP_HOST_CHUNKS")) K = std::min(std::max(atoi(env), 1), (int)SSPP_MAX_CHUNKS);
   }
   const bool chunked = K > 1 || (sink && sink->peers);  // the peer variant always delivers through the chunk path
   a.nchunks = K;
   // chunk sizes fall off linearly (4:3:2:1 for four chunks): the copy of the last chunk is the only one
   // nothing overlaps, so it is the smallest; the earlier copies have the later chunks' kernels to hide behind
+  const char* shape_env = getenv("SSPP_HOST_CHUNK_SHAPE");  // tuning: "equal" = chunks of equal size
+  const bool equal_chunks = shape_env && shape_env[0] == 'e';
   for (int c = 0; c <= SSPP_MAX_CHUNKS; ++c) {
     const int64_t done = (int64_t)c * (2 * K - c + 1) / 2, all = (int64_t)K * (K + 1) / 2;  // sum of (K - j), j < c
-    a.chunk_lo[c] = (int)(c >= K ? nrows : (nrows * done) / all);
+    a.chunk_lo[c] = (int)(c >= K ? nrows : (equal_chunks ? (nrows * c) / K : (nrows * done) / all));
   }
   const bool to_peers = sink && sink->peers;
   if (to_peers && !ctx->push_stream) {
