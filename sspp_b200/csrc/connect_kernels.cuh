@@ -440,13 +440,11 @@ __device__ __forceinline__ void lane_offset(const RayLattice& lat, int lig, doub
 // bound the rest: start keys in [key(f(t+first)), key(f(t+last))], end keys likewise for s; plus the
 // one-voxel overshoot beyond the end on the side the pair travels to (none when s == t: then every
 // ray has a zero direction component on this axis).  False when a key leaves the 16-bit space.
-// o_lo / o_hi: the keys of the row's own end of the box (f(t + off_first), f(t + off_last)), the same for every pair of
-// the row and computed once per row; -1 = outside the key space.
-__device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, double s, double off_first, double off_last, int o_lo,
-                                             int o_hi, int& lo, int& hi) {
-  int e_lo, e_hi;
-  if (o_lo < 0 || o_hi < 0 || !coord_to_key(ks, (double)d2f(d_add(s, off_first)), e_lo) ||
-      !coord_to_key(ks, (double)d2f(d_add(s, off_last)), e_hi))
+__device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, double s, double off_first, double off_last,
+                                             int& lo, int& hi) {
+  int o_lo, o_hi, e_lo, e_hi;
+  if (!coord_to_key(ks, (double)d2f(d_add(t, off_first)), o_lo) || !coord_to_key(ks, (double)d2f(d_add(t, off_last)), o_hi) ||
+      !coord_to_key(ks, (double)d2f(d_add(s, off_first)), e_lo) || !coord_to_key(ks, (double)d2f(d_add(s, off_last)), e_hi))
     return false;
   if (s > t) { lo = o_lo; hi = e_hi + 1; }
   else if (s < t) { lo = e_lo - 1; hi = o_hi; }
@@ -606,19 +604,6 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     }
     __syncwarp();
   }
-  // the row's own end of every pair key box: six keys (low / high lattice offset per axis), one lane each
-  int rk[6] = {-1, -1, -1, -1, -1, -1};
-  if (!COUNT && fast) {
-    int mine = -1;
-    if (lane < 6) {
-      const int ax = lane >> 1;
-      const double pv = ax == 0 ? px : (ax == 1 ? py : pz);
-      const double ov = (lane & 1) ? lat.off[ax][lat.n[ax] - 1] : lat.off[ax][0];
-      if (!coord_to_key(m.ks, (double)d2f(d_add(pv, ov)), mine)) mine = -1;
-    }
-#pragma unroll
-    for (int i = 0; i < 6; ++i) rk[i] = __shfl_sync(0xffffffffu, mine, i);
-  }
   int nacc = 0;
   unsigned long long nsteps = 0;
   for (int base = 0; base < n; base += 32) {
@@ -652,9 +637,9 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     // stage 2b: the pair's key box (one lane per pair)
     if (!COUNT && fast && needs) {
       int lox, hix, loy, hiy, loz, hiz;
-      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], rk[0], rk[1], lox, hix) &&
-          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], rk[2], rk[3], loy, hiy) &&
-          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], rk[4], rk[5], loz, hiz) &&
+      if (pair_key_box(m.ks, px, qx, lat.off[0][0], lat.off[0][lat.n[0] - 1], lox, hix) &&
+          pair_key_box(m.ks, py, qy, lat.off[1][0], lat.off[1][lat.n[1] - 1], loy, hiy) &&
+          pair_key_box(m.ks, pz, qz, lat.off[2][0], lat.off[2][lat.n[2] - 1], loz, hiz) &&
           ((SSPP_PAIR_COARSE && !box_maybe_blocked_coarse(m, lox, hix, loy, hiy, loz, hiz)) || !box_maybe_blocked(m, lox, hix, loy, hiy, loz, hiz)))
         needs = false;
     }
