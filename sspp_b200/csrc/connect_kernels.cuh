@@ -503,9 +503,10 @@ __device__ __forceinline__ int2 sort_row_pairs(EdgeSmemSort& sb, int warp, int l
   int2 c0 = make_int2(0, 0);
   if (n <= 32) {
     int2 mine = (lane < n) ? candA[off + lane] : make_int2(0, 0x7fffffff);
-    int key = mine.y & 0x7fffffff;
+    const int key = mine.y & 0x7fffffff;
     int rank = 0;
-    for (int k = 0; k < n; ++k) rank += ((__shfl_sync(0xffffffffu, mine.y, k) & 0x7fffffff) < key);
+#pragma unroll 4
+    for (int k = 0; k < n; ++k) rank += (__shfl_sync(0xffffffffu, key, k) < key);
     if (lane < n) sb.buf[warp][rank] = mine;
     __syncwarp();
     if (lane < n) c0 = sb.buf[warp][lane];
@@ -684,13 +685,17 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
       __syncwarp();
       const int W = __popc(need) * R;
+      // w / R without a division per item: umulhi(w, 2^32 / R + 1), exact for 2 <= R < 8192 (w < 32 R < 2^32 / R);
+      // other lattice sizes divide
+      const bool use_magic = NW == 1 || (R > 1 && R < 8192);  // the NW == 1 kernel is only launched for 2 <= R <= 32
+      const unsigned rmagic = use_magic ? 0xffffffffu / (unsigned)R + 1u : 0u;
       const bool have_okey = start_stage;  // the start stage above ran for this row
       unsigned blockedmask = 0;
       for (int w0 = 0; w0 < W; w0 += 32) {
         const int w = w0 + lane;
         unsigned bit = 0;
         if (w < W) {
-          const int p = w / R, q = w - p * R, k = sm.slots[warp][p];
+          const int p = use_magic ? (int)__umulhi((unsigned)w, rmagic) : w / R, q = w - p * R, k = sm.slots[warp][p];
           if (!((blockedmask >> k) & 1u)) {
             double ox, oy, oz;
             ray_offset(sm, q, ox, oy, oz);

@@ -776,7 +776,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(), ctx->candA.as<int2>(), \
       ctx->candB.as<int2>(), ctx->acc.as<int>(), ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c)
         if (count_steps) SSPP_LAUNCH_EDGES(true, 1);  // the instrumented variant has no start stage
-        else if (lat.rays <= 32) SSPP_LAUNCH_EDGES(false, 1);
+        else if (lat.rays >= 2 && lat.rays <= 32) SSPP_LAUNCH_EDGES(false, 1);
         else SSPP_LAUNCH_EDGES(false, START_RAYS_MAX / 32);
 #undef SSPP_LAUNCH_EDGES
         LAUNCHED(ctx);
