@@ -61,6 +61,8 @@ struct sspp_gpu_ctx {
   // connect scratch + result
   DevBuf bbox, cell_of, cell_start, cell_cursor, sorted_idx, sx, sy, sz, rows, row_flag, row_free, row_class;
   DevBuf cand_count, cand_off, candA, candB, acc, deg, row_ptr, col_idx, counters, scan_tmp, lattice, work_rows;
+  RayLattice lattice_host;     // what ctx->lattice holds on the device (valid: lattice_valid)
+  bool lattice_valid = false;
   int sm_count = 148;
   bool has_result = false;
   int64_t res_rows = 0, res_edges = 0;

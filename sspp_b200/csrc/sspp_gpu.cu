@@ -81,10 +81,15 @@ int build_lattice(sspp_gpu_ctx* ctx, const double box[3], RayLattice& lat) {
 }
 
 int upload_lattice(sspp_gpu_ctx* ctx, const RayLattice& lat) {
+  // the table only changes with the box or the resolution: a repeated pass finds it on the device already
+  if (ctx->lattice_valid && ctx->lattice.p && memcmp(&ctx->lattice_host, &lat, sizeof(RayLattice)) == 0) return SSPP_OK;
+  ctx->lattice_valid = false;
   CK(ctx->lattice.reserve(sizeof(RayLattice)));
   // `lat` is pageable host memory: the call returns once it has been copied to the driver's staging
   // buffer, so the caller's stack object may go away afterwards
   CK(cudaMemcpyAsync(ctx->lattice.p, &lat, sizeof(RayLattice), cudaMemcpyHostToDevice, ctx->stream));
+  memcpy(&ctx->lattice_host, &lat, sizeof(RayLattice));
+  ctx->lattice_valid = true;
   return SSPP_OK;
 }
 
