@@ -602,7 +602,7 @@ def main():
     ap.add_argument("--no-s5", action="store_true", help="N>1: skip the strong-scaling object of BASELINE configs[4] (S5)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = one S4a region per GPU in one map / one search space (default); strong = S4a split over the GPUs")
-    ap.add_argument("--assembler", default="peer", choices=["streamed", "peer", "nccl"],
+    ap.add_argument("--assembler", default="peer", choices=["fused", "streamed", "peer", "nccl"],
                     help="N>1: CSR assembly overlapped with the edge test (chunks copied to all ranks over NVLink while the next "
                          "chunk is computed), by one push kernel over NVLink peer memory after the pass (default: the fastest "
                          "at 2, 4 and 8 GPUs), or by NCCL all-gather + packing")
@@ -684,7 +684,11 @@ def main():
     if distributed:
         from sspp_b200 import sharded
         dev = torch.device("cuda", local_rank)
-        if args.assembler == "streamed":
+        if args.assembler == "fused":
+            # exchange fused into the edge kernel (rows stored into all ranks' slot-format images as they finish)
+            streamed = sharded.FusedPeerAssembler(eng, n, dev)
+            assembler = sharded.PeerCsrAssembler(eng, n, dev)  # the e2e leg (host buffers in) assembles after its pass
+        elif args.assembler == "streamed":
             streamed = sharded.StreamedPeerAssembler(eng, n, dev)
             assembler = sharded.PeerCsrAssembler(eng, n, dev)  # the e2e leg (host buffers in) assembles after its pass
         elif args.assembler == "peer":

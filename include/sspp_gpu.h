@@ -209,6 +209,34 @@ typedef struct sspp_peer_blocks {
 } sspp_peer_blocks;
 int sspp_gpu_connect_to_peers(sspp_gpu_ctx* ctx, const sspp_connect_params* params, const sspp_peer_blocks* peers,
                               sspp_connect_stats* stats);
+/* Multi-GPU, exchange FUSED into the edge kernel (no counterpart in the reference; SURVEY.md §8 e's exchange step done
+ * while the edge test is still running).  Every rank owns, per buffer set, a slot-format image of the WHOLE graph that
+ * its peers can address: `slots` (total_rows x slot int32) and `deg` (total_rows int32).  sspp_gpu_connect_fused runs this
+ * rank's rows of connectNodes with every row — rows whose reach is free in the pyramid included — going through the
+ * edge kernel, whose warps store each finished row (accepted columns, already in list order, and the row's degree)
+ * straight into row first_row + r of ALL ranks' images through NVLink peer pointers.  The transfer so rides along
+ * with the computation row by row; nothing is left to send when the pass ends, and no local CSR is built
+ * (sspp_gpu_connect_fetch is not available after it; stats->edges is the shard's edge count).  After a barrier over
+ * the ranks, sspp_gpu_pack_slots turns a complete image into the whole-graph CSR (scan of the degrees + copy), which is
+ * byte-identical to the CSR of a one-GPU connect.  Needs use_map = 1 and the pair-slot layout: SSPP_ERR_RANGE when a
+ * row of this shard holds more than `slot` in-radius pairs (fall back to sspp_gpu_connect + sspp_gpu_connect_push_csr).
+ * Alternate two buffer sets from call to call: a rank may already be writing the next graph into its peers' images
+ * while they still pack the last one. */
+typedef struct sspp_fused_peers {
+  int32_t world, rank;
+  int32_t slot;      /* 32 or 64: ints per row in the images (the same on every rank) */
+  int32_t reserved;  /* 0 */
+  int64_t first_row; /* global index of this rank's row 0 (= params->row_begin when the ranks share one node list) */
+  int32_t* const* slot_peers; /* host array of `world` device addresses: rank p's `slots` image */
+  int32_t* const* deg_peers;  /* likewise, rank p's `deg` image */
+} sspp_fused_peers;
+int sspp_gpu_connect_fused(sspp_gpu_ctx* ctx, const sspp_connect_params* params, const sspp_fused_peers* peers,
+                           sspp_connect_stats* stats);
+/* slots_device / deg_device: a complete image (all ranks have passed the barrier); row_ptr_out_device: n_rows + 1 int64;
+ * col_out_device: col_capacity int32.  If the graph has more edges than col_capacity nothing is copied and
+ * *overflow_device receives the edge count.  Runs on the context's stream. */
+int sspp_gpu_pack_slots(sspp_gpu_ctx* ctx, const int32_t* slots_device, const int32_t* deg_device, int64_t n_rows, int32_t slot,
+                        int64_t* row_ptr_out_device, int32_t* col_out_device, int64_t col_capacity, int64_t* overflow_device);
 /* Candidate-balanced row partition (SURVEY.md §8 e "Partitioning"; the outer loop being split is
  * src/pathplanner.cpp:536): `world` + 1 cut points over the list indices, cuts[0] = 0, cuts[world] = n, such that
  * every block [cuts[g], cuts[g+1]) carries about the same WORK rather than the same number of rows.  Work of a

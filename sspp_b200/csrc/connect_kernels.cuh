@@ -177,6 +177,15 @@ struct ConnectArgs {
   // (a chunk never has more work rows than rows), its length in counters[16 + c], its ticket in [32 + c].
   int nchunks;
   int chunk_lo[SSPP_MAX_CHUNKS + 1];
+  // Exchange fused into the pass (sspp_gpu_connect_fused; slot mode only): every row of the shard goes through the edge
+  // kernel, which stores the row's accepted columns, sorted, and its degree straight into the slot-format buffers of ALL
+  // ranks (fslot[k] / fdeg[k], indexed by GLOBAL row: frow0 + local row) through NVLink peer pointers, row by row, while
+  // the rest of the pass is still running.  Rows whose reach is free in the pyramid take the accept-all path there.
+  int fused, fworld;
+  long long frow0;
+  int* fslot[SSPP_MAX_PEERS];
+  int* fdeg[SSPP_MAX_PEERS];
+  const uint8_t* row_free_dev;
   // Diagnostics (sspp_gpu_connect_row_classes): how every row was answered — 0 no pair, 1 reach free in the
   // coarse pyramid (k_count), 3 pair by pair in k_edges (2 is reserved)
   uint8_t* row_class;
@@ -266,7 +275,7 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
       if (a.use_map && a.use_pyramid && tst > 0) fr = row_reach_is_free(m, px, py, pz, a.ts.reach) ? 1 : 0;
       row_free[r] = fr;
       inr = cnt; tested = tst; pyr = fr;
-      is_work = a.use_map && !fr && cnt > 0;
+      is_work = a.fused ? true : (a.use_map && !fr && cnt > 0);
       a.row_class[r] = cnt == 0 ? 0 : (fr || !a.use_map ? 1 : 3);
       while (chunk + 1 < a.nchunks && r >= a.chunk_lo[chunk + 1]) ++chunk;
       // slot mode: a row that needs no ray keeps all its pairs; k_compact orders them on the way out
@@ -558,11 +567,11 @@ __global__ void __launch_bounds__(256) k_rows_accept(ConnectArgs a, const long l
 
 // NW: 32-ray words of the start-voxel stage the kernel is compiled for (1: lattices up to 32 rays, the common
 // case, with the mask in one register; 4: up to START_RAYS_MAX)
-template <bool COUNT, int NW>
+template <bool COUNT, int NW, bool FUSED>
 __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& m, EdgeSmem& sm, int* okey, const int warp, const int lane,
                                          const int t, const long long* __restrict__ cand_off,
                                          const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
-                                         int* __restrict__ deg, unsigned long long* counters, unsigned& n_box, unsigned& n_lat) {
+                                         int* __restrict__ deg, unsigned long long* counters, unsigned& n_box, unsigned& n_lat, unsigned long long& n_edges) {
   const RayLattice& lat = sm.lat;
   const int s = t;  // work lists hold sorted positions
   const NodeRec me = load_node(a.sn + s);
@@ -574,7 +583,8 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
 
   const double px = me.x, py = me.y, pz = me.z;
   const int R = lat.rays;
-  const bool fast = a.use_pyramid != 0;
+  const bool accept_all = FUSED && (!a.use_map || a.row_free_dev[r] != 0);  // nothing to test: every pair is an edge
+  const bool fast = a.use_pyramid != 0 && !accept_all;
   // Row-level verdicts: every ray starts at p + offset whatever the pair, and the start voxel is the
   // first one a walk tests.  A ray whose start voxel is blocked therefore rejects every pair of this
   // row for which that ray is not empty (its end key differs from its start key).
@@ -582,7 +592,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
 #pragma unroll
   for (int c = 0; c < NW; ++c) startmask[c] = 0;
   bool any_start = false;
-  const bool start_stage = !COUNT && fast && R <= NW * 32;
+  const bool start_stage = !COUNT && fast && R <= NW * 32 && !accept_all;
   if (start_stage) {
 #pragma unroll
     for (int c = 0; c < NW; ++c) {
@@ -616,7 +626,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     double qx = 0, qy = 0, qz = 0;
     if (mine_valid) { const NodeRec o = load_node(a.sn + c.x); qx = o.x; qy = o.y; qz = o.z; }
     bool rejected = false;
-    bool needs = mine_valid && !same;
+    bool needs = mine_valid && !same && !accept_all;
     // stage 2a: a ray of this pair that starts in a blocked voxel and is not empty rejects the pair
     if (needs && any_start) {
 #pragma unroll
@@ -646,7 +656,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
     }
     unsigned need = __ballot_sync(0xffffffffu, needs);
     unsigned accmask = __ballot_sync(0xffffffffu, mine_valid && !needs && !rejected);  // same-position or box-free pairs
-    n_box += __popc(accmask & ~__ballot_sync(0xffffffffu, same));
+    if (!accept_all) n_box += __popc(accmask & ~__ballot_sync(0xffffffffu, same));
     n_lat += __popc(need);
     if (COUNT) {
       // instrumented run: every ray through the exact walk, counted with the reference's
@@ -710,8 +720,19 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       __syncwarp();
       accmask |= need & ~blockedmask;
     }
-    if ((accmask >> lane) & 1u) acc[off + nacc + __popc(accmask & ((1u << lane) - 1u))] = c.y & 0x7fffffff;
+    if ((accmask >> lane) & 1u) {
+      const int pos = nacc + __popc(accmask & ((1u << lane) - 1u)), v = c.y & 0x7fffffff;
+      acc[off + pos] = v;
+      if (FUSED) {
+        const long long g = (a.frow0 + r) * (long long)a.slot + pos;
+        for (int k = 0; k < a.fworld; ++k) a.fslot[k][g] = v;
+      }
+    }
     nacc += __popc(accmask);
+  }
+  if (FUSED) {
+    if (lane < a.fworld) a.fdeg[lane][a.frow0 + r] = nacc;
+    n_edges += (unsigned)nacc;
   }
   if (lane == 0) {
     deg[r] = nacc;
@@ -725,7 +746,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
 
 // Persistent edge kernel: a fixed grid (EDGE_MIN_BLOCKS CTAs per SM); every warp draws the next work
 // row with a ticket, so a row that needs many walks does not hold seven finished warps hostage.
-template <bool COUNT, int NW>
+template <bool COUNT, int NW, bool FUSED>
 __global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
 k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
         const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
@@ -750,19 +771,21 @@ k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned long long n_work = counters[16 + chunk];
   unsigned n_box = 0, n_lat = 0;
+  unsigned long long n_edges = 0;
   work_rows += a.chunk_lo[chunk];
   for (;;) {
     unsigned long long i = 0;
     if (lane == 0) i = atomicAdd(counters + 32 + chunk, 1ull);
     i = __shfl_sync(0xffffffffu, i, 0);
     if (i >= n_work) break;
-    edge_row<COUNT, NW>(a, m, sm, okey_all + warp * 3 * min(lat.rays, START_RAYS_MAX), warp, lane, work_rows[i], cand_off, candA, candB, acc,
-                    deg, counters, n_box, n_lat);
+    edge_row<COUNT, NW, FUSED>(a, m, sm, okey_all + warp * 3 * min(lat.rays, START_RAYS_MAX), warp, lane, work_rows[i], cand_off, candA,
+                               candB, acc, deg, counters, n_box, n_lat, n_edges);
   }
   // statistics: one atomic per warp and kernel, not per row
   if (lane == 0) {
     if (n_box) atomicAdd(counters + 5, (unsigned long long)n_box);
     if (n_lat) atomicAdd(counters + 6, (unsigned long long)n_lat);
+    if (FUSED && n_edges) atomicAdd(counters + 9, n_edges);  // [9] edges of this shard (no local CSR in fused mode)
   }
 }
 
@@ -974,6 +997,24 @@ __global__ void k_find_cuts(const long long* __restrict__ prefix, int64_t n, int
     if (prefix[mid] >= target) hi = mid; else lo = mid + 1;
   }
   cuts[g] = lo;
+}
+
+// After the fused exchange: the slot-format rows of ALL ranks (n rows of `slot` ints, deg[r] of them valid and sorted)
+// become the whole-graph CSR — row_ptr from a scan of the degrees, eight lanes per row copy the columns.
+__global__ void k_pack_slots(const int* __restrict__ slots, const int* __restrict__ deg, const long long* __restrict__ row_ptr,
+                             long long n, int slot, int* __restrict__ col, long long col_capacity, long long* __restrict__ overflow) {
+  if (row_ptr[n] > col_capacity) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicMax((unsigned long long*)overflow, (unsigned long long)row_ptr[n]);
+    return;
+  }
+  const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long r = gt / COMPACT_LANES;
+  const int sub = (int)(gt % COMPACT_LANES);
+  if (r >= n) return;
+  const int d = deg[r];
+  const int* src = slots + r * (long long)slot;
+  int* dst = col + row_ptr[r];
+  for (int e = sub; e < d; e += COMPACT_LANES) dst[e] = src[e];
 }
 
 }  // namespace

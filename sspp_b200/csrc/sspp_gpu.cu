@@ -466,6 +466,8 @@ struct HostSink {
   // multi-GPU variant (sspp_gpu_connect_to_peers): the chunks go to slot [rank] of every rank's block
   // buffers over NVLink (copy engines) instead of to the host; col_capacity = the slot size then
   const sspp_peer_blocks* peers;
+  // exchange fused into the pass (sspp_gpu_connect_fused): rows go to all ranks' slot-format buffers from the edge kernel
+  const sspp_fused_peers* fused;
 };
 int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect_stats* stats, HostSink* sink);
 }  // namespace
@@ -635,8 +637,17 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   CK(ctx->counters.reserve(48 * 8));
   CK(cudaMemsetAsync(ctx->counters.p, 0, 48 * 8, st));
   // row chunks: only when the CSR goes straight to host buffers and the pass is large enough to pipeline
+  const sspp_fused_peers* fz = sink ? sink->fused : nullptr;
+  a.fused = fz ? 1 : 0;
+  a.fworld = fz ? fz->world : 0;
+  a.frow0 = fz ? (long long)fz->first_row : 0;
+  a.row_free_dev = ctx->row_free.as<uint8_t>();
+  for (int k = 0; k < SSPP_MAX_PEERS; ++k) {
+    a.fslot[k] = (fz && k < fz->world) ? fz->slot_peers[k] : nullptr;
+    a.fdeg[k] = (fz && k < fz->world) ? fz->deg_peers[k] : nullptr;
+  }
   int K = 1;
-  if (sink && nrows >= (1 << 16)) {
+  if (sink && !fz && nrows >= (1 << 16)) {
     // host sink: with the edge test at ~1.2 ms the call is bound by the D2H copy of the CSR (71 MB at S4a), so the sooner
     // the first chunk is final the better: six chunks (6:5:4:3:2:1) measured best (1 / 2 / 4 / 6 / 8: 3.61 / 3.17 / 2.90 /
     // 2.82 / 2.89 ms end to end); the peer variant keeps four
@@ -691,6 +702,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     a.slot = lambda <= 10.0 ? 32 : (lambda <= 28.0 ? 64 : 0);
     if (const char* env = getenv("SSPP_CONNECT_SLOT")) a.slot = std::max(0, atoi(env));
     if (a.slot && (double)nrows * a.slot > 3.0e9) a.slot = 0;  // slots beyond ~36 GB of pair buffers: scan instead
+    if (fz) a.slot = fz->slot;  // the fused exchange works on the slot layout the ranks agreed on
     if (a.slot) CK(reserve_pairs((long long)nrows * a.slot));
   }
   k_count<false><<<ceil_div(n, 256), 256, 0, st>>>(a, ctx->map, ctx->cand_count.as<int>(), ctx->row_free.as<uint8_t>(),
@@ -730,7 +742,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
     CK(cudaStreamSynchronize(st));
     CK(reserve_pairs(C + C / 16 + 1024));
   }
-  unsigned long long hc[9];
+  unsigned long long hc[10];
   long long E = 0;
   bool range_error = false;
   for (int attempt = 0;; ++attempt) {
@@ -776,18 +788,21 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
           if (const char* env = getenv("SSPP_PUSH_ROOM")) room = std::max(0, atoi(env));
         }
         const int blocks = std::max(ctx->sm_count, ctx->sm_count * EDGE_MIN_BLOCKS - room);
-#define SSPP_LAUNCH_EDGES(COUNT, NW)                                                                                         \
-  k_edges<COUNT, NW><<<blocks, EDGE_WARPS * 32, edge_okey_bytes(lat.rays), st>>>(                                           \
+#define SSPP_LAUNCH_EDGES(COUNT, NW, FUSED)                                                                                  \
+  k_edges<COUNT, NW, FUSED><<<blocks, EDGE_WARPS * 32, edge_okey_bytes(lat.rays), st>>>(                                    \
       a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(), ctx->candA.as<int2>(), \
       ctx->candB.as<int2>(), ctx->acc.as<int>(), ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c)
-        if (count_steps) SSPP_LAUNCH_EDGES(true, 1);  // the instrumented variant has no start stage
-        else if (lat.rays >= 2 && lat.rays <= 32) SSPP_LAUNCH_EDGES(false, 1);
-        else SSPP_LAUNCH_EDGES(false, START_RAYS_MAX / 32);
+        if (count_steps) SSPP_LAUNCH_EDGES(true, 1, false);  // the instrumented variant has no start stage
+        else if (fz && lat.rays >= 2 && lat.rays <= 32) SSPP_LAUNCH_EDGES(false, 1, true);
+        else if (fz) SSPP_LAUNCH_EDGES(false, START_RAYS_MAX / 32, true);
+        else if (lat.rays >= 2 && lat.rays <= 32) SSPP_LAUNCH_EDGES(false, 1, false);
+        else SSPP_LAUNCH_EDGES(false, START_RAYS_MAX / 32, false);
 #undef SSPP_LAUNCH_EDGES
         LAUNCHED(ctx);
       }
       if (c == K - 1) CK(cudaEventRecord(ctx->ev[3], st));
       const int r0 = a.chunk_lo[c], r1 = a.chunk_lo[c + 1];
+      if (fz) continue;  // fused exchange: the rows are already on every rank, in slot format; no local CSR
       if (!chunked) {
         int rc = scan_exclusive<long long>(ctx, ctx->deg.as<int>(), nrows, ctx->row_ptr.as<long long>());
         if (rc) return rc;
@@ -840,9 +855,15 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
       int rc = drain(K - 1);
       if (rc) return rc;
     }
-    CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
+    if (!fz) CK(cudaMemcpyAsync(&E, ctx->row_ptr.as<long long>() + nrows, 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hc, ctx->counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    if (fz) {
+      E = (long long)hc[9];
+      if (hc[8] != 0) return fail(ctx, SSPP_ERR_RANGE, "connect_fused: a row holds more pairs than the exchange's slot");
+      sink->delivered = true;
+      break;
+    }
     if (to_peers) {
       CK(cudaStreamSynchronize(ctx->push_stream));  // this rank's stores have been issued and retired
       const bool usable = a.slot ? (hc[8] == 0) : ((long long)hc[0] <= cap);
@@ -890,7 +911,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   cudaEventElapsedTime(&ctx->timings[3], ctx->ev[2], ctx->ev[3]);
   cudaEventElapsedTime(&ctx->timings[4], ctx->ev[3], ctx->ev[4]);
   cudaEventElapsedTime(&ctx->timings[5], ctx->ev[5], ctx->ev[3]);
-  ctx->has_result = true;
+  ctx->has_result = !fz;  // the fused pass leaves no local CSR behind
   ctx->res_rows = nrows;
   ctx->res_edges = E;
   if (range_error)
@@ -1099,7 +1120,7 @@ int sspp_gpu_connect_to_host(sspp_gpu_ctx* ctx, const sspp_connect_params* param
   if (!ctx) return SSPP_ERR_INVALID;
   if (!row_ptr || (col_capacity > 0 && !col_idx) || col_capacity < 0)
     return fail(ctx, SSPP_ERR_INVALID, "connect_to_host: null argument");
-  HostSink sink = {row_ptr, col_idx, col_capacity, false, nullptr};
+  HostSink sink = {row_ptr, col_idx, col_capacity, false, nullptr, nullptr};
   int rc = connect_impl(ctx, params, stats, &sink);
   if (rc) return rc;
   if (sink.delivered) return SSPP_OK;  // the chunks were sent home while the pass was still running
@@ -1131,7 +1152,7 @@ int sspp_gpu_connect_to_peers(sspp_gpu_ctx* ctx, const sspp_connect_params* para
   if (lo == 0 && hi == 0) hi = ctx->n_nodes;
   if (peers->row_stride < hi - lo + 1 || peers->col_stride < 0)
     return fail(ctx, SSPP_ERR_INVALID, "connect_to_peers: row_stride must hold rows + 1 entries");
-  HostSink sink = {nullptr, nullptr, peers->col_stride, false, peers};
+  HostSink sink = {nullptr, nullptr, peers->col_stride, false, peers, nullptr};
   int rc = connect_impl(ctx, params, stats, &sink);
   if (rc) return rc;
   if (sink.delivered) return SSPP_OK;
@@ -1146,6 +1167,42 @@ int sspp_gpu_connect_to_peers(sspp_gpu_ctx* ctx, const sspp_connect_params* para
                        (size_t)(stats->rows + 1) * 8, cudaMemcpyDefault, ctx->stream));
   }
   CK(cudaStreamSynchronize(ctx->stream));
+  return SSPP_OK;
+}
+
+int sspp_gpu_connect_fused(sspp_gpu_ctx* ctx, const sspp_connect_params* params, const sspp_fused_peers* fp, sspp_connect_stats* stats) {
+  sspp_connect_stats local;
+  if (!stats) stats = &local;
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!params || !fp || !fp->slot_peers || !fp->deg_peers) return fail(ctx, SSPP_ERR_INVALID, "connect_fused: null argument");
+  if (fp->world < 1 || fp->world > SSPP_MAX_PEERS || fp->world > 32 || fp->rank < 0 || fp->rank >= fp->world)
+    return fail(ctx, SSPP_ERR_INVALID, "connect_fused: world must be 1..SSPP_MAX_PEERS and rank inside it");
+  if (fp->slot != 32 && fp->slot != 64) return fail(ctx, SSPP_ERR_INVALID, "connect_fused: slot must be 32 or 64");
+  if (!params->use_map) return fail(ctx, SSPP_ERR_INVALID, "connect_fused: needs use_map (without a map there is no edge test to fuse with)");
+  if (params->count_steps || params->count_only) return fail(ctx, SSPP_ERR_INVALID, "connect_fused: not for instrumented passes");
+  if (fp->first_row < 0) return fail(ctx, SSPP_ERR_INVALID, "connect_fused: first_row must be >= 0");
+  for (int p = 0; p < fp->world; ++p)
+    if (!fp->slot_peers[p] || !fp->deg_peers[p]) return fail(ctx, SSPP_ERR_INVALID, "connect_fused: null peer buffer");
+  HostSink sink = {nullptr, nullptr, 0, false, nullptr, fp};
+  return connect_impl(ctx, params, stats, &sink);
+}
+
+int sspp_gpu_pack_slots(sspp_gpu_ctx* ctx, const int32_t* slots_device, const int32_t* deg_device, int64_t n_rows, int32_t slot,
+                        int64_t* row_ptr_out_device, int32_t* col_out_device, int64_t col_capacity, int64_t* overflow_device) {
+  if (!ctx) return SSPP_ERR_INVALID;
+  if (!slots_device || !deg_device || !row_ptr_out_device || !col_out_device || !overflow_device || n_rows < 0 || col_capacity < 0 ||
+      (slot != 32 && slot != 64))
+    return fail(ctx, SSPP_ERR_INVALID, "pack_slots: bad argument");
+  CK(cudaSetDevice(ctx->device));
+  int rc = scan_exclusive<long long>(ctx, (const int*)deg_device, n_rows, (long long*)row_ptr_out_device);
+  if (rc) return rc;
+  if (n_rows) {
+    k_pack_slots<<<ceil_div(n_rows * COMPACT_LANES, 256), 256, 0, ctx->stream>>>((const int*)slots_device, (const int*)deg_device,
+                                                                              (const long long*)row_ptr_out_device, (long long)n_rows,
+                                                                              slot, col_out_device, (long long)col_capacity,
+                                                                              (long long*)overflow_device);
+    LAUNCHED(ctx);
+  }
   return SSPP_OK;
 }
 

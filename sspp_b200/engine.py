@@ -38,6 +38,11 @@ class PeerBlocks(ctypes.Structure):
                 ("row_stride", c_i64), ("col_stride", c_i64)]
 
 
+class FusedPeers(ctypes.Structure):
+    _fields_ = [("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("slot", ctypes.c_int32), ("reserved", ctypes.c_int32),
+                ("first_row", c_i64), ("slot_peers", c_vp), ("deg_peers", c_vp)]
+
+
 class Frustum(ctypes.Structure):
     _fields_ = [("hfov_deg", ctypes.c_double), ("vfov_deg", ctypes.c_double), ("near_dist", ctypes.c_double),
                 ("far_dist", ctypes.c_double), ("count_steps", ctypes.c_int32), ("reserved", ctypes.c_int32)]
@@ -94,6 +99,9 @@ def load_library():
         "sspp_gpu_connect_to_peers": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), ctypes.POINTER(PeerBlocks),
                                                      ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_result_device": (ctypes.c_int, [c_vp, ctypes.POINTER(c_vp), ctypes.POINTER(c_vp)]),
+        "sspp_gpu_connect_fused": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), ctypes.POINTER(FusedPeers),
+                                                  ctypes.POINTER(ConnectStats)]),
+        "sspp_gpu_pack_slots": (ctypes.c_int, [c_vp, c_vp, c_vp, c_i64, ctypes.c_int32, c_vp, c_vp, c_i64, c_vp]),
         "sspp_gpu_connect_nodes_host": (ctypes.c_int, [c_vp, c_vp, c_i64, ctypes.POINTER(ConnectParams), c_vp, c_vp,
                                                        c_i64, ctypes.POINTER(ConnectStats)]),
         "sspp_gpu_connect_to_host": (ctypes.c_int, [c_vp, ctypes.POINTER(ConnectParams), c_vp, c_vp, c_i64,
@@ -299,6 +307,23 @@ class Engine:
             e.needed_edges = int(s.edges)
             raise e
         return s
+
+    def connect_fused(self, world, rank, slot, first_row, slot_peers, deg_peers, **kw):
+        """this rank's rows with the exchange fused into the edge kernel: every finished row goes straight into the slot-format
+        images of all ranks (lists of `world` device addresses).  Returns the stats (edges = this shard's); raises SsppError
+        (code 4) when a row outgrows the slot."""
+        p = self.params(**kw)
+        s = ConnectStats()
+        a = (c_vp * world)(*[c_vp(int(x)) for x in slot_peers])
+        b = (c_vp * world)(*[c_vp(int(x)) for x in deg_peers])
+        fp = FusedPeers(world, rank, int(slot), 0, int(first_row), ctypes.cast(a, c_vp), ctypes.cast(b, c_vp))
+        self._ck(self.L.sspp_gpu_connect_fused(self.h, ctypes.byref(p), ctypes.byref(fp), ctypes.byref(s)))
+        return s
+
+    def pack_slots(self, slots, deg, n_rows, slot, row_ptr_out, col_out, col_capacity, overflow):
+        """raw device addresses: a complete slot-format image -> whole-graph CSR on the engine's stream"""
+        self._ck(self.L.sspp_gpu_pack_slots(self.h, c_vp(slots), c_vp(deg), int(n_rows), int(slot), c_vp(row_ptr_out), c_vp(col_out),
+                                            int(col_capacity), c_vp(overflow)))
 
     def connect_result_device(self):
         a, b = c_vp(), c_vp()

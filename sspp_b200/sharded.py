@@ -360,3 +360,85 @@ class StreamedPeerAssembler:
 
     def close(self):
         self._release_sets()
+
+
+class FusedUnavailable(RuntimeError):
+    """The fused exchange cannot serve this graph (a row outgrows the slot, or the pass runs without a map).  Raised on
+    EVERY rank together, so the callers can switch to PeerCsrAssembler without a collective mismatch."""
+
+
+class FusedPeerAssembler:
+    """connect + whole-graph CSR on every rank with the exchange fused INTO the edge kernel (sspp_gpu_connect_fused):
+    every rank owns two slot-format images of the whole graph (rows x slot int32 + rows int32 degrees) that its peers
+    can address; the edge kernel's warps store each finished row into all ranks' images over NVLink while the pass is
+    still running, so when the pass ends nothing is left to send.  What follows is one all-reduce (the barrier, and the
+    edge total / "did every rank succeed" in the same message) and the local packing of the image into the CSR.
+    The two images alternate from call to call: a rank may already be writing the next graph into its peers while they
+    still pack the last one (the barrier of the call in between orders the reuse)."""
+
+    def __init__(self, eng, n_nodes, device, cuts=None, slot=32):
+        self.eng = eng
+        self.world = dist.get_world_size()
+        self.rank = dist.get_rank()
+        self.device = device
+        self.n = n_nodes
+        self.slot = slot
+        base = row_cuts(n_nodes, self.world, cuts)
+        self.rows = (base[self.rank], base[self.rank + 1])
+        self.ext_stream = torch.cuda.ExternalStream(eng.stream(), device=device)
+        self.out_rp = torch.empty(n_nodes + 1, dtype=torch.int64, device=device)
+        self.out_col, self.col_cap = None, 0
+        self.overflow = torch.zeros(1, dtype=torch.int64, device=device)
+        self.msg = torch.zeros(2, dtype=torch.int64, device=device)  # [ranks that failed, edges]
+        self.sets = []
+        for _ in range(2):
+            sl_ptr, sl_peers = exchange_peer_buffer(eng, max(n_nodes, 1) * slot * 4, device)
+            dg_ptr, dg_peers = exchange_peer_buffer(eng, max(n_nodes, 1) * 4, device)
+            self.sets.append((sl_ptr, sl_peers, dg_ptr, dg_peers))
+        self.turn = 0
+        dist.barrier()
+
+    def connect(self, **kw):
+        """This rank's rows of sspp_gpu_connect_fused + barrier + packing.  Returns (stats, row_ptr, col_idx): the stats
+        of this rank's shard and device tensors of the whole graph (col_idx is the buffer; row_ptr[-1] entries are valid)."""
+        from .engine import SsppError
+        for attempt in range(2):
+            sl_ptr, sl_peers, dg_ptr, dg_peers = self.sets[self.turn % 2]
+            self.turn += 1
+            st, failed = None, 0
+            try:
+                st = self.eng.connect_fused(self.world, self.rank, self.slot, self.rows[0], sl_peers, dg_peers, rows=self.rows, **kw)
+            except SsppError as e:
+                if e.code not in (1, 4):
+                    raise
+                failed = 1
+            # barrier: every rank's rows have landed (connect_fused returns after its own stores have retired); the same
+            # message carries the edge total and whether some rank could not run the fused pass
+            self.msg[0] = failed
+            self.msg[1] = int(st.edges) if st is not None else 0
+            dist.all_reduce(self.msg, op=dist.ReduceOp.SUM)
+            nfail, total = int(self.msg[0].item()), int(self.msg[1].item())
+            if nfail:
+                raise FusedUnavailable("%d rank(s) could not run the fused pass (a row outgrows the %d-pair slot?)" % (nfail, self.slot))
+            if total > self.col_cap:
+                self.col_cap = ((int(total * 1.1) + 1024 + 3) // 4) * 4
+                self.out_col = torch.empty(self.col_cap, dtype=torch.int32, device=self.device)
+            self.ext_stream.wait_event(torch.cuda.current_stream().record_event())
+            self.eng.pack_slots(sl_ptr, dg_ptr, self.n, self.slot, self.out_rp.data_ptr(), self.out_col.data_ptr(), self.col_cap,
+                                self.overflow.data_ptr())
+            self.eng.synchronize()
+            return st, self.out_rp, self.out_col
+        raise RuntimeError("unreachable")
+
+    def close(self):
+        torch.cuda.synchronize()
+        for sl_ptr, sl_peers, dg_ptr, dg_peers in self.sets:
+            for g in range(self.world):
+                if g != self.rank:
+                    self.eng.peer_buffer_release(sl_peers[g])
+                    self.eng.peer_buffer_release(dg_peers[g])
+        dist.barrier()  # every importer has closed its mappings before the owners free the memory
+        for sl_ptr, sl_peers, dg_ptr, dg_peers in self.sets:
+            self.eng.peer_buffer_release(sl_ptr)
+            self.eng.peer_buffer_release(dg_ptr)
+        self.sets = []

@@ -246,6 +246,76 @@ def test_balanced_cuts_split_the_work_not_the_rows(eng):
     assert list(eng.balanced_cuts(1, 8, radius=1.5, box=BOX)) == [0, n]
 
 
+@pytest.mark.parametrize("kind,world", [("lattice", 2), ("lattice", 3), ("random", 3), ("big", 2)])
+def test_fused_exchange_packs_to_one_gpu_csr(eng, kind, world):
+    """sspp_gpu_connect_fused: the edge kernel of every rank stores its finished rows straight into the slot-format images
+    of all ranks (here: several contexts on one GPU share the images), and sspp_gpu_pack_slots turns a complete image
+    into the CSR of one connect over all rows, byte for byte — rows answered by the pyramid, rows without any pair and
+    rows decided ray by ray alike; uneven cuts; both pyramid settings."""
+    import torch
+    dev = torch.device("cuda", 0)
+    if kind == "big":
+        km, dm, occ, known = scenes.synthetic_map(n_vox=224, res=0.3, seed=12, n_boxes=60, n_spheres=40, region=56.0)
+        nodes = scenes.lattice_nodes(56, 1.0)
+    else:
+        km, dm, occ, known = scenes.synthetic_map(n_vox=64, res=0.3, seed=5, n_boxes=8, n_spheres=6, region=64 * 0.3 * 0.75)
+        nodes = scenes.lattice_nodes(14, 1.0) if kind == "lattice" else np.concatenate(
+            [scenes.uniform_nodes(1500, extent=13.0, seed=9), np.array([[40.0, 40.0, 40.0], [0.1, 0.2, 0.3], [0.1, 0.2, 0.3]])])
+    n, slot = len(nodes), 32
+    eng.map_create(0.3, km, dm, True)
+    eng.map_upload_dense(occ, known)
+    eng.set_nodes(nodes)
+    bounds = [0] + sorted(int(x) for x in np.random.RandomState(3).choice(np.arange(1, n), world - 1, replace=False)) + [n]
+    ranks = [Engine(0) for _ in range(world)]
+    try:
+        for e in ranks:
+            e.map_create(0.3, km, dm, True)
+            e.map_upload_dense(occ, known)
+            e.set_nodes(nodes)
+        for pyramid in (True, False):
+            st = eng.connect(radius=1.5, box=BOX, use_pyramid=pyramid)
+            rp_full, col_full = eng.connect_fetch(st)
+            images = [(torch.full((n * slot,), -7, dtype=torch.int32, device=dev), torch.full((n,), -7, dtype=torch.int32, device=dev))
+                      for _ in range(world)]
+            torch.cuda.synchronize()
+            edges = 0
+            for g, e in enumerate(ranks):
+                s = e.connect_fused(world, g, slot, bounds[g], [im[0].data_ptr() for im in images], [im[1].data_ptr() for im in images],
+                                    radius=1.5, box=BOX, rows=(bounds[g], bounds[g + 1]), use_pyramid=pyramid)
+                edges += s.edges
+                assert s.rows == bounds[g + 1] - bounds[g]
+            assert edges == st.edges
+            for k in range(world):
+                assert np.array_equal(images[k][1].cpu().numpy(), np.diff(rp_full)), "degrees in the image of rank %d" % k
+                out_rp = torch.empty(n + 1, dtype=torch.int64, device=dev)
+                out_col = torch.full((st.edges + 8,), -1, dtype=torch.int32, device=dev)
+                over = torch.zeros(1, dtype=torch.int64, device=dev)
+                ranks[k].pack_slots(images[k][0].data_ptr(), images[k][1].data_ptr(), n, slot, out_rp.data_ptr(), out_col.data_ptr(),
+                                    st.edges + 8, over.data_ptr())
+                ranks[k].synchronize()
+                assert int(over.item()) == 0
+                assert np.array_equal(out_rp.cpu().numpy(), rp_full), "row_ptr on rank %d differs" % k
+                c = out_col.cpu().numpy()
+                assert np.array_equal(c[: st.edges], col_full) and (c[st.edges:] == -1).all(), "col_idx on rank %d differs" % k
+            # a column buffer that is too small: nothing copied, the total reported
+            over = torch.zeros(1, dtype=torch.int64, device=dev)
+            out_col = torch.full((st.edges,), -1, dtype=torch.int32, device=dev)
+            ranks[0].pack_slots(images[0][0].data_ptr(), images[0][1].data_ptr(), n, slot, out_rp.data_ptr(), out_col.data_ptr(),
+                                st.edges - 1, over.data_ptr())
+            ranks[0].synchronize()
+            assert int(over.item()) == st.edges and (out_col == -1).all()
+        with pytest.raises(SsppError):  # the fused pass needs the map
+            ranks[0].connect_fused(world, 0, slot, 0, [im[0].data_ptr() for im in images], [im[1].data_ptr() for im in images],
+                                   radius=1.5, use_map=False, rows=(0, bounds[1]))
+        with pytest.raises(SsppError) as ei:  # rows with more pairs than a slot: refused, the caller falls back
+            ranks[0].connect_fused(world, 0, slot, 0, [im[0].data_ptr() for im in images], [im[1].data_ptr() for im in images],
+                                   radius=4.0, box=BOX, rows=(0, bounds[1]))
+        assert ei.value.code == 4
+    finally:
+        for e in ranks:
+            e.close()
+
+
 def _ipc_rank(rank, world, port, q):
     import torch
     import torch.distributed as dist
@@ -282,6 +352,24 @@ def _ipc_rank(rank, world, port, q):
             ok = ok and np.array_equal(rp, rpf) and np.array_equal(col[: sf.edges], colf)
             dist.barrier()
         sasm.close()
+        # the exchange fused into the edge kernel (two buffer sets: three graphs in a row), then a graph it cannot serve
+        sparse = scenes.uniform_nodes(3000, extent=13.0, seed=10)  # few enough pairs per row for the 32-pair slots
+        e.set_nodes(sparse)
+        fasm = sharded.FusedPeerAssembler(e, len(sparse), dev)
+        for radius in (0.9, 1.2, 0.9):
+            st, rp, col = fasm.connect(radius=radius, box=BOX)
+            sf = e.connect(radius=radius, box=BOX)
+            rpf, colf = e.connect_fetch(sf)
+            ok = ok and sf.edges > 0 and np.array_equal(rp.cpu().numpy(), rpf) and np.array_equal(col.cpu().numpy()[: sf.edges], colf)
+            dist.barrier()
+        try:
+            fasm.connect(radius=4.0, box=BOX)
+            ok = False
+        except sharded.FusedUnavailable:
+            pass
+        dist.barrier()
+        fasm.close()
+        e.set_nodes(nodes)
         # rows cut by work (every rank computes the same cuts from the same nodes and map) ...
         cuts = e.balanced_cuts(world, 8, radius=1.5, box=BOX)
         basm = sharded.PeerCsrAssembler(e, n, dev, cuts=cuts)
