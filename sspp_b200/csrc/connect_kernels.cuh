@@ -181,6 +181,7 @@ struct ConnectArgs {
   // kernel, which stores the row's accepted columns, sorted, and its degree straight into the slot-format buffers of ALL
   // ranks (fslot[k] / fdeg[k], indexed by GLOBAL row: frow0 + local row) through NVLink peer pointers, row by row, while
   // the rest of the pass is still running.  Rows whose reach is free in the pyramid take the accept-all path there.
+  int ray_stride;  // order in which k_edges takes the rays of a pair: ray (t * ray_stride) % rays at turn position t; 1 = lattice order
   int fused, fworld;
   long long frow0;
   int* fslot[SSPP_MAX_PEERS];
@@ -687,35 +688,45 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
         need &= ~took;
       }
     } else if (need) {
-      // stage 3: all (pair, ray) items of the batch flattened over the lanes and walked 32 at a time by the exact
-      // DDA, so the warp stays full whatever the number of rays per pair; a pair found blocked drops the rays it
-      // has left in later turns.  (A key-box test per ray before the walk was measured to cost more than the
-      // walks it saves - S4a 1.57 -> 1.36 ms without it - and is gone.)
-      if (needs) sm.slots[warp][__popc(need & ((1u << lane) - 1u))] = lane;
+      // stage 3: the exact walks.  The pairs still open advance through the ray lattice in lock step: every turn
+      // takes the next k = 32 / (open pairs) rays of each of them (one (pair, ray) item per lane, walked by the exact
+      // DDA), then the pairs a ray found blocked leave and the rest are packed again - the status of a pair is "any ray
+      // not free" (src/distance_heuristic.cpp:104-111 stops at the first such ray), so the order of the rays is free,
+      // and a blocked pair costs one turn instead of its whole lattice.  The rays are taken in a strided order
+      // (a.ray_stride, coprime with the lattice size) so that the first turn samples the whole box rather than one
+      // face of it.  (A key-box test per ray before the walk was measured to cost more than the walks it saves - S4a
+      // 1.57 -> 1.36 ms without it - and is gone.)
       if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
-      __syncwarp();
-      const int W = __popc(need) * R;
-      // w / R without a division per item: umulhi(w, 2^32 / R + 1), exact for 2 <= R < 8192 (w < 32 R < 2^32 / R);
-      // other lattice sizes divide
-      const bool use_magic = NW == 1 || (R > 1 && R < 8192);  // the NW == 1 kernel is only launched for 2 <= R <= 32
-      const unsigned rmagic = use_magic ? 0xffffffffu / (unsigned)R + 1u : 0u;
       const bool have_okey = start_stage;  // the start stage above ran for this row
-      unsigned blockedmask = 0;
-      for (int w0 = 0; w0 < W; w0 += 32) {
-        const int w = w0 + lane;
+      const unsigned smagic = a.ray_stride > 1 ? 0xffffffffu / (unsigned)R + 1u : 0u;  // (x * stride) % R, x * stride < 2^32 / R
+      unsigned open = need, blockedmask = 0;
+      int q0 = 0;
+      while (open) {
+        const int P = __popc(open);
+        if ((open >> lane) & 1u) sm.slots[warp][__popc(open & ((1u << lane) - 1u))] = lane;
+        __syncwarp();
+        const int k = min(R - q0, 32 / P);
+        const unsigned pmagic = 65536u / (unsigned)P + 1u;  // lane / P for lane < 32
         unsigned bit = 0;
-        if (w < W) {
-          const int p = use_magic ? (int)__umulhi((unsigned)w, rmagic) : w / R, q = w - p * R, k = sm.slots[warp][p];
-          if (!((blockedmask >> k) & 1u)) {
-            double ox, oy, oz;
-            ray_offset(sm, q, ox, oy, oz);
-            const double* f = sm.far_end[warp][k];
-            const int st = ray_status(m, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
-                                      d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? okey + 3 * q : nullptr);
-            if (st != CELL_FREE) bit = 1u << k;
+        if (lane < P * k) {
+          const int t = (int)(((unsigned)lane * pmagic) >> 16), kk = sm.slots[warp][lane - t * P];
+          int q = q0 + t;
+          if (smagic) {
+            const unsigned x = (unsigned)q * (unsigned)a.ray_stride;
+            q = (int)(x - (unsigned)R * __umulhi(x, smagic));
           }
+          double ox, oy, oz;
+          ray_offset(sm, q, ox, oy, oz);
+          const double* f = sm.far_end[warp][kk];
+          const int st = ray_status(m, d2f(d_add(px, ox)), d2f(d_add(py, oy)), d2f(d_add(pz, oz)), d2f(d_add(f[0], ox)),
+                                    d2f(d_add(f[1], oy)), d2f(d_add(f[2], oz)), have_okey ? okey + 3 * q : nullptr);
+          if (st != CELL_FREE) bit = 1u << kk;
         }
-        blockedmask |= __reduce_or_sync(0xffffffffu, bit);
+        const unsigned b = __reduce_or_sync(0xffffffffu, bit);
+        blockedmask |= b;
+        open &= ~b;
+        q0 += k;
+        if (q0 >= R) break;
       }
       __syncwarp();
       accmask |= need & ~blockedmask;

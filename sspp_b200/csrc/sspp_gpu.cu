@@ -469,6 +469,23 @@ struct HostSink {
   // exchange fused into the pass (sspp_gpu_connect_fused): rows go to all ranks' slot-format buffers from the edge kernel
   const sspp_fused_peers* fused;
 };
+
+// Order in which the edge kernel takes the rays of a pair (ConnectArgs::ray_stride): position t of a turn is ray
+// (t * stride) % rays.  The stride is about a third of the lattice and coprime with its size, so every ray is taken
+// once and the first few already sample the whole box.  SSPP_RAY_STRIDE=1 keeps the lattice order.
+static int ray_order_stride(int rays) {
+  if (const char* e = getenv("SSPP_RAY_STRIDE")) {
+    int v = atoi(e);
+    if (v == 1) return 1;
+  }
+  if (rays < 3 || rays > 1024) return 1;
+  int s = (rays * 3 + 9) / 10;
+  if (s < 2) s = 2;
+  auto gcd = [](int x, int y) { while (y) { int t = x % y; x = y; y = t; } return x; };
+  while (gcd(s, rays) != 1) ++s;
+  return s < rays ? s : 1;
+}
+
 int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect_stats* stats, HostSink* sink);
 }  // namespace
 
@@ -629,6 +646,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   const bool count_steps = use_map && prm->count_steps;
   a.use_pyramid = (prm->use_pyramid && !count_steps) ? 1 : 0;
   a.ts = ts;
+  a.ray_stride = ray_order_stride(use_map ? lat.rays : 1);
   CK(ctx->cand_count.reserve((size_t)nrows * 4));
   CK(ctx->row_free.reserve((size_t)nrows));
   CK(ctx->row_class.reserve((size_t)nrows));
