@@ -181,6 +181,7 @@ struct ConnectArgs {
   // kernel, which stores the row's accepted columns, sorted, and its degree straight into the slot-format buffers of ALL
   // ranks (fslot[k] / fdeg[k], indexed by GLOBAL row: frow0 + local row) through NVLink peer pointers, row by row, while
   // the rest of the pass is still running.  Rows whose reach is free in the pyramid take the accept-all path there.
+  unsigned ray_magic;  // 2^32 / rays + 1 when ray_stride > 1, else 0
   int ray_stride;  // order in which k_edges takes the rays of a pair: ray (t * ray_stride) % rays at turn position t; 1 = lattice order
   int fused, fworld;
   long long frow0;
@@ -462,6 +463,22 @@ __device__ __forceinline__ bool pair_key_box(const KeySpace& ks, double t, doubl
   return true;
 }
 
+// Turn table of the walk stage: with P pairs open a turn takes rays[P] = 32 / P rays of each; magic[P] = 2^16 / P + 1
+// turns a lane number into (ray of the turn, pair): lane / P == (lane * magic[P]) >> 16 for lane < 32.
+struct TurnTable {
+  unsigned rays[33];
+  unsigned magic[33];
+};
+constexpr TurnTable make_turn_table() {
+  TurnTable t{};
+  for (unsigned p = 1; p <= 32; ++p) {
+    t.rays[p] = 32u / p;
+    t.magic[p] = 65536u / p + 1u;
+  }
+  return t;
+}
+__constant__ TurnTable c_turn = make_turn_table();
+
 // One ray of the lattice stage, out of line (the walk is the bulk of the edge kernel and inlining it would cost the
 // kernel its occupancy).  okey: the ray's origin key, whose voxel the row stage has already found free (kx < 0: origin
 // outside the key space — upstream leaves such a ray empty), or NULL = derive the key and test the start voxel here.
@@ -698,15 +715,15 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       // 1.57 -> 1.36 ms without it - and is gone.)
       if (mine_valid) { sm.far_end[warp][lane][0] = qx; sm.far_end[warp][lane][1] = qy; sm.far_end[warp][lane][2] = qz; }
       const bool have_okey = start_stage;  // the start stage above ran for this row
-      const unsigned smagic = a.ray_stride > 1 ? 0xffffffffu / (unsigned)R + 1u : 0u;  // (x * stride) % R, x * stride < 2^32 / R
+      const unsigned smagic = a.ray_magic;  // 2^32 / R + 1 for (x * stride) % R (x * stride < 2^32 / R), 0 = lattice order
       unsigned open = need, blockedmask = 0;
       int q0 = 0;
       while (open) {
         const int P = __popc(open);
         if ((open >> lane) & 1u) sm.slots[warp][__popc(open & ((1u << lane) - 1u))] = lane;
         __syncwarp();
-        const int k = min(R - q0, 32 / P);
-        const unsigned pmagic = 65536u / (unsigned)P + 1u;  // lane / P for lane < 32
+        const int k = min(R - q0, (int)c_turn.rays[P]);
+        const unsigned pmagic = c_turn.magic[P];  // lane / P for lane < 32
         unsigned bit = 0;
         if (lane < P * k) {
           const int t = (int)(((unsigned)lane * pmagic) >> 16), kk = sm.slots[warp][lane - t * P];

@@ -647,6 +647,7 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
   a.use_pyramid = (prm->use_pyramid && !count_steps) ? 1 : 0;
   a.ts = ts;
   a.ray_stride = ray_order_stride(use_map ? lat.rays : 1);
+  a.ray_magic = a.ray_stride > 1 ? 0xffffffffu / (unsigned)lat.rays + 1u : 0u;
   CK(ctx->cand_count.reserve((size_t)nrows * 4));
   CK(ctx->row_free.reserve((size_t)nrows));
   CK(ctx->row_class.reserve((size_t)nrows));

@@ -7,6 +7,7 @@ python tools/profile_target.py 2>&1 | grep -E "^connect"
 SSPP_RAY_STRIDE=1 python tools/profile_target.py 2>&1 | grep -E "^connect" | sed 's/^/stride1 /'
 python tools/s4b_probe.py 2>&1 | tail -1
 python tools/s5_probe.py 2>&1 | grep -E "connect" | tail -1
+python tools/config2_full.py 2>/dev/null | python -c "import json,sys; d=json.load(sys.stdin); print(\"config2\", d[\"connect_no_map\"][\"device_ms\"], d[\"connect_with_map\"][\"device_ms\"])"
 python bench.py --steps 10 --warmup 3 --no-visibility > gpurun_out/u_bench.json 2> gpurun_out/u_bench.err; echo "bench rc $?"
 python - <<'PY'
 import json
