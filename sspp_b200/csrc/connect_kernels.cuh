@@ -720,6 +720,7 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
       int q0 = 0;
       while (open) {
         const int P = __popc(open);
+        __syncwarp();  // the previous turn has read the list
         if ((open >> lane) & 1u) sm.slots[warp][__popc(open & ((1u << lane) - 1u))] = lane;
         __syncwarp();
         const int k = min(R - q0, (int)c_turn.rays[P]);
