@@ -603,9 +603,10 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="N>1: weak = one S4a region per GPU in one map / one search space (default); strong = S4a split over the GPUs")
     ap.add_argument("--assembler", default="peer", choices=["fused", "streamed", "peer", "nccl"],
-                    help="N>1: CSR assembly overlapped with the edge test (chunks copied to all ranks over NVLink while the next "
-                         "chunk is computed), by one push kernel over NVLink peer memory after the pass (default: the fastest "
-                         "at 2, 4 and 8 GPUs), or by NCCL all-gather + packing")
+                    help="N>1: how every rank gets the whole CSR. fused = the edge kernel stores finished rows into all ranks' "
+                         "images over NVLink as it goes; streamed = finished row chunks pushed to all ranks while the next chunk is "
+                         "computed; peer = one push kernel over NVLink peer memory after the pass (default: the fastest at 2, 4 and "
+                         "8 GPUs); nccl = NCCL all-gather + packing")
     args = ap.parse_args()
     claim_stdout()
     if args.impl == "reference":
