@@ -221,8 +221,11 @@ __device__ __forceinline__ bool pairs_unusable(const ConnectArgs& a, const long 
 // in slot mode also write the pairs into the row's slot (then no FILL pass runs).
 // FILL == true (after the scan of the counts): write the pairs — (sorted position, list index with
 // bit 31 = same position) — to cand[], in cell order; the edge kernel orders them by list index.
+#ifndef COUNT_MIN_BLOCKS
+#define COUNT_MIN_BLOCKS 5  // 48 registers; six (40) and eight (32) measured slower: 0.329 / 0.374 ms against 0.315
+#endif
 template <bool FILL>
-__global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* __restrict__ cand_count,
+__global__ void __launch_bounds__(256, COUNT_MIN_BLOCKS) k_count(ConnectArgs a, DeviceMap m, int* __restrict__ cand_count,
                                                uint8_t* __restrict__ row_free, unsigned long long* counters,
                                                const long long* __restrict__ cand_off, int2* __restrict__ cand,
                                                int* __restrict__ work_rows, int* __restrict__ deg, long long pair_cap) {
@@ -312,7 +315,10 @@ __global__ void __launch_bounds__(256) k_count(ConnectArgs a, DeviceMap m, int* 
 // ------------------------------------------------------------------------------------------------
 // edge test: one warp per source row
 // ------------------------------------------------------------------------------------------------
-constexpr int EDGE_WARPS = 8;
+#ifndef SSPP_EDGE_WARPS
+#define SSPP_EDGE_WARPS 8  // tuning switch: warps per CTA of the edge kernel
+#endif
+constexpr int EDGE_WARPS = SSPP_EDGE_WARPS;
 #ifndef SSPP_PAIR_COARSE
 #define SSPP_PAIR_COARSE 1  // tuning switch: 0 = pair boxes go to the fine plane without asking the 4x4x4 pyramid first
 #endif
@@ -775,8 +781,17 @@ __device__ __forceinline__ void edge_row(const ConnectArgs& a, const DeviceMap& 
 
 // Persistent edge kernel: a fixed grid (EDGE_MIN_BLOCKS CTAs per SM); every warp draws the next work
 // row with a ticket, so a row that needs many walks does not hold seven finished warps hostage.
+#ifndef EDGE_MIN_BLOCKS_SMALL
+#define EDGE_MIN_BLOCKS_SMALL 6
+#endif
+// CTAs per SM: the kernel for lattices of up to 32 rays is compiled for six (40 registers; S4a 1.03 ms at four, 0.98 at
+// five, 0.95 at six, 1.04 / 1.00 at seven / eight: the extra resident warps cover more of the load latency than the
+// tighter register budget costs, until the spills take over); the kernels with the four-word start mask (S5: 9.52 ms
+// at four, 9.60 / 9.57 at five / six; BASELINE configs[1] 0.655 / 0.673 / 0.694), the fused and the instrumented one
+// keep four.
+constexpr int edge_min_blocks(bool count, int nw, bool fused) { return (!count && nw == 1 && !fused) ? EDGE_MIN_BLOCKS_SMALL : EDGE_MIN_BLOCKS; }
 template <bool COUNT, int NW, bool FUSED>
-__global__ void __launch_bounds__(EDGE_WARPS * 32, EDGE_MIN_BLOCKS)
+__global__ void __launch_bounds__(EDGE_WARPS * 32, edge_min_blocks(COUNT, NW, FUSED))
 k_edges(ConnectArgs a, DeviceMap m, const RayLattice* __restrict__ lat_g, const long long* __restrict__ cand_off,
         const int* __restrict__ work_rows, const int2* __restrict__ candA, int2* candB, int* __restrict__ acc,
         int* __restrict__ deg, unsigned long long* counters, long long pair_cap, int chunk) {

@@ -806,9 +806,9 @@ int connect_impl(sspp_gpu_ctx* ctx, const sspp_connect_params* prm, sspp_connect
           room = ctx->sm_count / 2;
           if (const char* env = getenv("SSPP_PUSH_ROOM")) room = std::max(0, atoi(env));
         }
-        const int blocks = std::max(ctx->sm_count, ctx->sm_count * EDGE_MIN_BLOCKS - room);
 #define SSPP_LAUNCH_EDGES(COUNT, NW, FUSED)                                                                                  \
-  k_edges<COUNT, NW, FUSED><<<blocks, EDGE_WARPS * 32, edge_okey_bytes(lat.rays), st>>>(                                    \
+  k_edges<COUNT, NW, FUSED><<<std::max(ctx->sm_count, ctx->sm_count * edge_min_blocks(COUNT, NW, FUSED) - room), EDGE_WARPS * 32, \
+            edge_okey_bytes(lat.rays), st>>>(                                    \
       a, ctx->map, ctx->lattice.as<RayLattice>(), ctx->cand_off.as<long long>(), ctx->work_rows.as<int>(), ctx->candA.as<int2>(), \
       ctx->candB.as<int2>(), ctx->acc.as<int>(), ctx->deg.as<int>(), ctx->counters.as<unsigned long long>(), cap, c)
         if (count_steps) SSPP_LAUNCH_EDGES(true, 1, false);  // the instrumented variant has no start stage
