@@ -1644,7 +1644,7 @@ int sspp_gpu_visibility(sspp_gpu_ctx* ctx, const double* poses, int64_t nv, cons
     CK(cudaEventRecord(ctx->vev[2], st));
     // --- occlusion rays
     {
-      const int blocks = ctx->sm_count * VIEW_RAYS_MIN_BLOCKS * 2;  // two rounds of resident CTAs, handed out grid-stride
+      const int blocks = ctx->sm_count * VIEW_RAYS_RESIDENT * 2;  // two rounds of resident CTAs, handed out grid-stride
       if (count_steps)
         k_view_rays<true><<<blocks, 256, 0, st>>>(ctx->map, views, 0, sp, ray_view, ray_pt, ray_off + nv, ray_cap, vis, vis_count,
                                                   ctx->vis_counters.as<unsigned long long>());

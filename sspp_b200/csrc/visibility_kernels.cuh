@@ -271,11 +271,18 @@ __global__ void __launch_bounds__(256, GATHER_MIN_BLOCKS) k_view_gather(const Vi
 
 // one thread per occlusion ray, blocks of 256 rays handed out grid-stride (the ray count lives on the device:
 // ray_off[nv]).  COUNT: the instrumented variant also counts the cells castRay looks up.
-#ifndef VIEW_RAYS_MIN_BLOCKS
-#define VIEW_RAYS_MIN_BLOCKS 4  // tuning switch: CTAs per SM the ray kernel is compiled for (4 = 64 registers)
+// Tuning switch VIEW_RAYS_MIN_BLOCKS: CTAs per SM the ray kernel is compiled for.  Left undefined the compiler settles on
+// 64 registers = four CTAs per SM by itself, and that build is the one all numbers are from (asking for four explicitly
+// changes the instruction schedule: 4.6 ms against 4.35 on the bench scene; five and six are slower still).
+#ifdef VIEW_RAYS_MIN_BLOCKS
+#define VIEW_RAYS_BOUNDS __launch_bounds__(256, VIEW_RAYS_MIN_BLOCKS)
+#define VIEW_RAYS_RESIDENT VIEW_RAYS_MIN_BLOCKS
+#else
+#define VIEW_RAYS_BOUNDS __launch_bounds__(256)
+#define VIEW_RAYS_RESIDENT 4
 #endif
 template <bool COUNT>
-__global__ void __launch_bounds__(256, VIEW_RAYS_MIN_BLOCKS) k_view_rays(DeviceMap m, const ViewRec* __restrict__ views, int64_t v0,
+__global__ void VIEW_RAYS_BOUNDS k_view_rays(DeviceMap m, const ViewRec* __restrict__ views, int64_t v0,
                                                    const float4* __restrict__ sp, const int* __restrict__ ray_view,
                                                    const int* __restrict__ ray_pt, const long long* __restrict__ ray_total,
                                                    long long ray_cap, uint8_t* __restrict__ vis, int* vis_count,
