@@ -29,14 +29,7 @@ rl, rh = key(nodes - reach) - 2, key(nodes + reach) + 2
 row_free = box_count(rl, rh) == 0
 print("rows with a free reach: %d of %d (engine: 529306 at 4^3 granularity)" % (row_free.sum(), len(nodes)))
 offs = [(dx, dy, dz) for dx in (-1, 0, 1) for dy in (-1, 0, 1) for dz in (-1, 0, 1) if 0 < dx * dx + dy * dy + dz * dz <= 2]
-idx = np.arange(100)
-gx, gy, gz = np.meshgrid(idx, idx, idx, indexing='ij')
-coords = np.stack([gx.ravel(), gy.ravel(), gz.ravel()], 1)
-order = None
-# lattice_nodes ordering: find it from the positions
-pos_key = np.round(nodes + 49.5).astype(int)  # lattice index per axis if centred
-lin = {}
-tot = box_free = clear_ok = clear_ok_aniso = 0
+tot = box_free = clear_ok = 0
 work = ~row_free
 P = nodes[work]
 for d in offs:
