@@ -46,3 +46,16 @@ for d in offs:
     rad = ((hi - lo + 1) // 2).max(axis=1)      # Chebyshev radius that covers the box from its centre voxel
     clear_ok += int((cdt[c[:, 2], c[:, 1], c[:, 0]] > rad).sum())
 print("pairs of work rows %d; key box free %d (%.1f %%); clearance(centre) > half-extent %d (%.1f %%)" % (tot, box_free, 100 * box_free / tot, clear_ok, 100 * clear_ok / tot))
+
+# how many rows a pyramid level of g x g x g blocks clears (reach grown to whole blocks): g = 4 is what k_count reads today
+for g in (4, 2):
+    cb = blocked.reshape(512 // g, g, 512 // g, g, 512 // g, g).any(axis=(1, 3, 5))
+    n = 512 // g
+    J = np.zeros((n + 1,) * 3, dtype=np.int32)
+    J[1:, 1:, 1:] = cb.cumsum(0, dtype=np.int32).cumsum(1, dtype=np.int32).cumsum(2, dtype=np.int32)
+    lo = np.clip(rl, 0, 511) // g
+    hi = np.clip(rh, 0, 511) // g
+    x0, y0, z0 = lo[:, 0], lo[:, 1], lo[:, 2]
+    x1, y1, z1 = hi[:, 0] + 1, hi[:, 1] + 1, hi[:, 2] + 1
+    cnt = J[z1, y1, x1] - J[z0, y1, x1] - J[z1, y0, x1] - J[z1, y1, x0] + J[z0, y0, x1] + J[z0, y1, x0] + J[z1, y0, x0] - J[z0, y0, x0]
+    print("rows cleared by a %d^3 pyramid level: %d" % (g, int((cnt == 0).sum())))
